@@ -1,0 +1,262 @@
+/* oracle/pic_oracle.c -- TEST INFRASTRUCTURE ONLY (checker / reported CPU baseline; never on the product path).
+ *
+ * PARITY UNPINNED for everything in this file: the reference has NO particle code (SURVEY.md F1;
+ * `struct Particle`, Auxiliar_functions.h:16-21, is declared and never used).  This is an AUTHORED scalar FP64
+ * particle loop that extends the reference time loop (PIC_2D.cpp:171-396) in the one place the report says
+ * particles go, and it is the DEFINITION the CUDA kernels are checked against.  It follows:
+ *   - particle fields {tag,q,x,y,px,py,pz}                          Auxiliar_functions.h:16-21
+ *   - Yee stagger of the six components                              Field_update.cpp:3-11
+ *   - tile index gid = (cy/tny)*globalTileCols + cx/tnx              Auxiliar_functions.cpp:44-46, PIC_2D.cpp:97-98
+ *   - time centring: fields at integer time at the top of the step   PIC_2D.cpp:322-396 (2nd half-B + exchange F)
+ *   - equation of motion du/dt = (q/m)(E + u x B / gamma), c = 1     Mini_PIC_2D_Report.pdf p.1; Boris: Birdsall & Langdon
+ *   - the -dt*J term of the E update                                 Report p.5
+ * Its own known-answer tests live in tests/test_pic_oracle.py (gyration, ExB drift, continuity equation,
+ * plasma oscillation).
+ *
+ * ARITHMETIC CONTRACT: every operation below is an IEEE-754 binary64 +,-,*,/,sqrt,floor or an
+ * explicit fma(); the file is built with -ffp-contract=off so the compiler adds no contraction of its own.  The
+ * CUDA kernels are written (independently) to the same operation sequence and built with -fmad=false, so push
+ * and deposit are BIT-EXACT, not merely within tolerance.  Current is accumulated in 64-bit fixed point
+ * (value * 2^52, round-to-nearest-even), which makes the deposit independent of summation order: any tile order,
+ * thread order or atomic interleaving yields the same bits.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+#define ORC_JSCALE 4503599627370496.0            /* 2^52 */
+#define ORC_INV_JSCALE (1.0 / 4503599627370496.0)
+
+typedef struct {
+    int nx, ny, tnx, tny;     /* global cells; tile interior cells */
+    double dx, dy, dt;
+    double inv_dx, inv_dy;    /* 1.0/dx, 1.0/dy, rounded once */
+    double box_x, box_y;      /* nx*dx, ny*dy */
+    double h;                 /* 0.5*dt*(q/m) */
+    double cjx, cjy, cjz;     /* 1/(dy*dt), 1/(dx*dt), 1/(dx*dy) */
+} orc_pic_params;
+
+void orc_pic_make_params(orc_pic_params* p, int nx, int ny, int tnx, int tny, double dx, double dy, double dt, double qm) {
+    p->nx = nx; p->ny = ny; p->tnx = tnx; p->tny = tny; p->dx = dx; p->dy = dy; p->dt = dt;
+    p->inv_dx = 1.0 / dx; p->inv_dy = 1.0 / dy;
+    p->box_x = nx * dx; p->box_y = ny * dy;
+    p->h = 0.5 * dt * qm;
+    p->cjx = 1.0 / (dy * dt); p->cjy = 1.0 / (dx * dt); p->cjz = 1.0 / (dx * dy);
+}
+
+static inline int wrapi(int i, int n) { return i < 0 ? i + n : i >= n ? i - n : i; }
+
+/* bilinear interpolation on a periodic (ny,nx) plane; lattice cell (i,j), weights (wx,wy) */
+static inline double bilerp(const double* F, int nx, int ny, int i, int j, double wx, double wy) {
+    int i0 = wrapi(i, nx), i1 = wrapi(i + 1, nx), j0 = wrapi(j, ny), j1 = wrapi(j + 1, ny);
+    double f00 = F[(size_t)j0 * nx + i0], f10 = F[(size_t)j0 * nx + i1];
+    double f01 = F[(size_t)j1 * nx + i0], f11 = F[(size_t)j1 * nx + i1];
+    double lo = fma(wx, f10 - f00, f00);
+    double hi = fma(wx, f11 - f01, f01);
+    return fma(wy, hi - lo, lo);
+}
+
+static inline void jadd(int64_t* J, int nx, int ny, int i, int j, double c) {
+    int64_t v = (int64_t)llrint(c * ORC_JSCALE);          /* round-to-nearest-even (default rounding mode) */
+    int64_t* p = &J[(size_t)wrapi(j, ny) * nx + wrapi(i, nx)];
+#ifdef _OPENMP
+#pragma omp atomic
+#endif
+    *p += v;
+}
+
+/* tile key of a stored (wrapped) position: SURVEY.md B.2 with reciprocal multiply */
+static inline int tile_key(const orc_pic_params* P, double x, double y) {
+    int cx = (int)floor(x * P->inv_dx), cy = (int)floor(y * P->inv_dy);
+    return (cy / P->tny) * (P->nx / P->tnx) + cx / P->tnx;
+}
+
+static inline double wrap_pos(double xn, double box, double inv_d, int n) {
+    double xw = xn;
+    if (xw < 0.0) xw = xw + box; else if (xw >= box) xw = xw - box;
+    if (!(xw * inv_d < (double)n)) xw = 0.0;               /* upper-edge rounding: keeps floor(x/dx) in [0,n) */
+    return xw;
+}
+
+/* Gather + Boris + move + zigzag deposit for particles [p0,p1).  Fields are (ny,nx) periodic planes at time n.
+ * jx,jy,jz are int64 fixed-point accumulators (NOT zeroed here).  Positions are wrapped into the box on exit. */
+void orc_push_deposit(const orc_pic_params* P, const double* ex, const double* ey, const double* ez,
+                      const double* bx, const double* by, const double* bz,
+                      int64_t* jx, int64_t* jy, int64_t* jz,
+                      double* x, double* y, double* ux, double* uy, double* uz, const double* q, long n) {
+    const int nx = P->nx, ny = P->ny;
+    const double h = P->h, dt = P->dt;
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static)
+#endif
+    for (long p = 0; p < n; p++) {
+        /* ---- gather */
+        double X1 = x[p] * P->inv_dx, Y1 = y[p] * P->inv_dy;
+        double fi1 = floor(X1), fj1 = floor(Y1);
+        int i1 = (int)fi1, j1 = (int)fj1;
+        double wx = X1 - fi1, wy = Y1 - fj1;
+        double Xh = X1 - 0.5, Yh = Y1 - 0.5;
+        double fih = floor(Xh), fjh = floor(Yh);
+        int ih = (int)fih, jh = (int)fjh;
+        double wxh = Xh - fih, wyh = Yh - fjh;
+        double Ex = bilerp(ex, nx, ny, ih, j1, wxh, wy);
+        double Ey = bilerp(ey, nx, ny, i1, jh, wx, wyh);
+        double Ez = bilerp(ez, nx, ny, i1, j1, wx, wy);
+        double Bx = bilerp(bx, nx, ny, i1, jh, wx, wyh);
+        double By = bilerp(by, nx, ny, ih, j1, wxh, wy);
+        double Bz = bilerp(bz, nx, ny, ih, jh, wxh, wyh);
+        /* ---- Boris */
+        double umx = fma(h, Ex, ux[p]), umy = fma(h, Ey, uy[p]), umz = fma(h, Ez, uz[p]);
+        double g2 = fma(umz, umz, fma(umy, umy, fma(umx, umx, 1.0)));
+        double hg = h * (1.0 / sqrt(g2));
+        double tx = hg * Bx, ty = hg * By, tz = hg * Bz;
+        double upx = fma(umy, tz, fma(-umz, ty, umx));
+        double upy = fma(umz, tx, fma(-umx, tz, umy));
+        double upz = fma(umx, ty, fma(-umy, tx, umz));
+        double t2 = fma(tz, tz, fma(ty, ty, tx * tx));
+        double sf = 2.0 / (1.0 + t2);
+        double sx = sf * tx, sy = sf * ty, sz = sf * tz;
+        double uqx = fma(upy, sz, fma(-upz, sy, umx));
+        double uqy = fma(upz, sx, fma(-upx, sz, umy));
+        double uqz = fma(upx, sy, fma(-upy, sx, umz));
+        double unx = fma(h, Ex, uqx), uny = fma(h, Ey, uqy), unz = fma(h, Ez, uqz);
+        double g2n = fma(unz, unz, fma(uny, uny, fma(unx, unx, 1.0)));
+        double ign = 1.0 / sqrt(g2n);
+        double vx = unx * ign, vy = uny * ign, vz = unz * ign;
+        double xn = fma(vx, dt, x[p]), yn = fma(vy, dt, y[p]);      /* unwrapped */
+        /* ---- charge-conserving zigzag deposit (Umeda et al. 2003), grid units */
+        double X2 = xn * P->inv_dx, Y2 = yn * P->inv_dy;
+        double fi2 = floor(X2), fj2 = floor(Y2);
+        int i2 = (int)fi2, j2 = (int)fj2;
+        double xr = fmin(fmin(fi1, fi2) + 1.0, fmax(fmax(fi1, fi2), 0.5 * (X1 + X2)));
+        double yr = fmin(fmin(fj1, fj2) + 1.0, fmax(fmax(fj1, fj2), 0.5 * (Y1 + Y2)));
+        double qjx = q[p] * P->cjx, qjy = q[p] * P->cjy;
+        double Fx1 = qjx * (xr - X1), Fx2 = qjx * (X2 - xr);
+        double Fy1 = qjy * (yr - Y1), Fy2 = qjy * (Y2 - yr);
+        double Wx1 = 0.5 * (X1 + xr) - fi1, Wy1 = 0.5 * (Y1 + yr) - fj1;
+        double Wx2 = 0.5 * (xr + X2) - fi2, Wy2 = 0.5 * (yr + Y2) - fj2;
+        jadd(jx, nx, ny, i1, j1, Fx1 * (1.0 - Wy1));  jadd(jx, nx, ny, i1, j1 + 1, Fx1 * Wy1);
+        jadd(jy, nx, ny, i1, j1, Fy1 * (1.0 - Wx1));  jadd(jy, nx, ny, i1 + 1, j1, Fy1 * Wx1);
+        jadd(jx, nx, ny, i2, j2, Fx2 * (1.0 - Wy2));  jadd(jx, nx, ny, i2, j2 + 1, Fx2 * Wy2);
+        jadd(jy, nx, ny, i2, j2, Fy2 * (1.0 - Wx2));  jadd(jy, nx, ny, i2 + 1, j2, Fy2 * Wx2);
+        /* Jz: CIC of q*vz at the time-centred position on the Ez (node) lattice */
+        double Xm = 0.5 * (X1 + X2), Ym = 0.5 * (Y1 + Y2);
+        double fim = floor(Xm), fjm = floor(Ym);
+        int im = (int)fim, jm = (int)fjm;
+        double wxm = Xm - fim, wym = Ym - fjm;
+        double qz = q[p] * P->cjz * vz;
+        double qa0 = qz * (1.0 - wxm), qa1 = qz * wxm, b0 = 1.0 - wym;
+        jadd(jz, nx, ny, im, jm, qa0 * b0);      jadd(jz, nx, ny, im + 1, jm, qa1 * b0);
+        jadd(jz, nx, ny, im, jm + 1, qa0 * wym); jadd(jz, nx, ny, im + 1, jm + 1, qa1 * wym);
+        /* ---- store, wrapped */
+        ux[p] = unx; uy[p] = uny; uz[p] = unz;
+        x[p] = wrap_pos(xn, P->box_x, P->inv_dx, nx);
+        y[p] = wrap_pos(yn, P->box_y, P->inv_dy, ny);
+    }
+}
+
+/* E <- E - dt*J with J = acc * 2^-52 (applied after the reference E sweep; exact no-op when acc == 0) */
+void orc_apply_current(const orc_pic_params* P, double* ex, double* ey, double* ez,
+                       const int64_t* jx, const int64_t* jy, const int64_t* jz) {
+    size_t n = (size_t)P->nx * P->ny;
+    for (size_t k = 0; k < n; k++) {
+        ex[k] = fma(-P->dt, (double)jx[k] * ORC_INV_JSCALE, ex[k]);
+        ey[k] = fma(-P->dt, (double)jy[k] * ORC_INV_JSCALE, ey[k]);
+        ez[k] = fma(-P->dt, (double)jz[k] * ORC_INV_JSCALE, ez[k]);
+    }
+}
+
+void orc_tile_keys(const orc_pic_params* P, const double* x, const double* y, long n, int* key) {
+    for (long p = 0; p < n; p++) key[p] = tile_key(P, x[p], y[p]);
+}
+
+/* Stable counting sort by tile key.  counts has ntiles entries; perm[new_slot] = old_slot. */
+void orc_sort_perm(const int* key, long n, int ntiles, int* counts, long* perm) {
+    long* off = (long*)calloc((size_t)ntiles + 1, sizeof(long));
+    memset(counts, 0, (size_t)ntiles * sizeof(int));
+    for (long p = 0; p < n; p++) counts[key[p]]++;
+    for (int t = 0; t < ntiles; t++) off[t + 1] = off[t] + counts[t];
+    for (long p = 0; p < n; p++) perm[off[key[p]]++] = p;
+    free(off);
+}
+
+/* rho (charge density at nodes, Ez lattice) by CIC in fixed point: diagnostic only */
+void orc_deposit_rho(const orc_pic_params* P, const double* x, const double* y, const double* q, long n, int64_t* rho) {
+    for (long p = 0; p < n; p++) {
+        double X = x[p] * P->inv_dx, Y = y[p] * P->inv_dy;
+        double fi = floor(X), fj = floor(Y);
+        double wx = X - fi, wy = Y - fj;
+        double qc = q[p] * P->cjz;
+        double qa0 = qc * (1.0 - wx), qa1 = qc * wx, b0 = 1.0 - wy;
+        int i = (int)fi, j = (int)fj;
+        jadd(rho, P->nx, P->ny, i, j, qa0 * b0);     jadd(rho, P->nx, P->ny, i + 1, j, qa1 * b0);
+        jadd(rho, P->nx, P->ny, i, j + 1, qa0 * wy); jadd(rho, P->nx, P->ny, i + 1, j + 1, qa1 * wy);
+    }
+}
+
+/* kinetic energy sum m_p (gamma-1), m_p = |q_p| / |q/m| */
+double orc_kinetic_energy(const double* ux, const double* uy, const double* uz, const double* q, long n, double qm) {
+    double s = 0.0;
+    for (long p = 0; p < n; p++) {
+        double u2 = ux[p] * ux[p] + uy[p] * uy[p] + uz[p] * uz[p];
+        s += fabs(q[p]) * (u2 / (sqrt(1.0 + u2) + 1.0));
+    }
+    return s / fabs(qm);
+}
+
+/* ------------------------------------------------------------------ full PIC steps on global periodic planes
+ * Order: P1/P2 push+deposit -> A half-B -> C E sweep, then -dt*J -> E half-B -> S stable tile sort.
+ * On one global periodic array guard exchanges (B, D, F, P3) are identities.  The Yee sweeps are the strict
+ * (mode 0, scheme 0) ones from yee_oracle.c. */
+void orc_b_sweep_global(const double*, const double*, const double*, double*, double*, double*, int, int, double, double, double, int, int);
+void orc_e_sweep_global(double*, double*, double*, const double*, const double*, const double*, int, int, double, double, double, int);
+
+void orc_pic_steps(const orc_pic_params* P, double* ex, double* ey, double* ez, double* bx, double* by, double* bz,
+                   double* x, double* y, double* ux, double* uy, double* uz, double* q, int* tag, long n,
+                   int steps, int do_sort, int* counts_out, int64_t* j_out /* 3 planes of last step or NULL */) {
+    size_t nc = (size_t)P->nx * P->ny;
+    int ntiles = (P->nx / P->tnx) * (P->ny / P->tny);
+    int64_t* J = (int64_t*)malloc(3 * nc * sizeof(int64_t));
+    int* key = (int*)malloc((size_t)(n > 0 ? n : 1) * sizeof(int));
+    long* perm = (long*)malloc((size_t)(n > 0 ? n : 1) * sizeof(long));
+    double* tmp = (double*)malloc((size_t)(n > 0 ? n : 1) * sizeof(double));
+    int* counts = (int*)calloc((size_t)ntiles, sizeof(int));
+    for (int s = 0; s < steps; s++) {
+        memset(J, 0, 3 * nc * sizeof(int64_t));
+        orc_push_deposit(P, ex, ey, ez, bx, by, bz, J, J + nc, J + 2 * nc, x, y, ux, uy, uz, q, n);
+        orc_b_sweep_global(ex, ey, ez, bx, by, bz, P->nx, P->ny, P->dt, P->dx, P->dy, 0, 0);
+        orc_e_sweep_global(ex, ey, ez, bx, by, bz, P->nx, P->ny, P->dt, P->dx, P->dy, 0);
+        orc_apply_current(P, ex, ey, ez, J, J + nc, J + 2 * nc);
+        orc_b_sweep_global(ex, ey, ez, bx, by, bz, P->nx, P->ny, P->dt, P->dx, P->dy, 0, 0);
+        if (do_sort) {
+            orc_tile_keys(P, x, y, n, key);
+            orc_sort_perm(key, n, ntiles, counts, perm);
+            double* arrs[6] = { x, y, ux, uy, uz, q };
+            for (int a = 0; a < 6; a++) {
+                for (long p = 0; p < n; p++) tmp[p] = arrs[a][perm[p]];
+                memcpy(arrs[a], tmp, (size_t)n * sizeof(double));
+            }
+            int* ti = (int*)tmp;
+            for (long p = 0; p < n; p++) ti[p] = tag[perm[p]];
+            memcpy(tag, ti, (size_t)n * sizeof(int));
+        }
+    }
+    if (counts_out) {
+        if (!do_sort) { orc_tile_keys(P, x, y, n, key); orc_sort_perm(key, n, ntiles, counts, perm); }
+        memcpy(counts_out, counts, (size_t)ntiles * sizeof(int));
+    }
+    if (j_out) memcpy(j_out, J, 3 * nc * sizeof(int64_t));
+    free(J); free(key); free(perm); free(tmp); free(counts);
+}
+
+int orc_num_threads(void) {
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}

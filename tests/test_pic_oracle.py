@@ -1,0 +1,131 @@
+"""Known-answer tests for the AUTHORED particle oracle (oracle/pic_oracle.c).  The reference has no particle code
+(SURVEY.md F1), so these physics checks are what pins the oracle: parity for push/deposit/sort is "unpinned"
+with respect to the reference and is GPU-vs-this-oracle."""
+import importlib
+import numpy as np
+from oracle import bindings as ob
+
+plasma = importlib.import_module("mini-pic--2d-pic-code-with-tiling-load-balance_b200.plasma")
+lib = ob.load_oracle()
+
+
+def _zero_planes(nx, ny):
+    return [np.zeros((ny, nx)) for _ in range(6)]
+
+
+def _one(x, y, ux, uy, uz, q=-1e-3):
+    return {"x": np.array([x]), "y": np.array([y]), "ux": np.array([ux]), "uy": np.array([uy]),
+            "uz": np.array([uz]), "q": np.array([q]), "tag": np.array([0], dtype=np.int32)}
+
+
+def test_gyration_in_uniform_bz():
+    nx = ny = 16; dx = dy = 0.1; dt = 0.03
+    P = ob.make_params(lib, nx, ny, 8, 8, dx, dy, dt)
+    pl = _zero_planes(nx, ny); pl[5][:] = 2.0
+    p = _one(0.8, 0.8, 0.3, 0.0, 0.1)
+    u0 = np.sqrt(0.3**2 + 0.1**2)
+    gam = np.sqrt(1 + u0**2)
+    ang = []
+    for _ in range(50):
+        ob.push_deposit(lib, P, pl, p)
+        assert abs(np.sqrt(p["ux"][0]**2 + p["uy"][0]**2 + p["uz"][0]**2) - u0) < 1e-15   # |u| conserved
+        assert abs(p["uz"][0] - 0.1) < 1e-16
+        ang.append(np.arctan2(p["uy"][0], p["ux"][0]))
+    dphi = np.diff(np.unwrap(ang))
+    want = 2 * np.arctan(P.h * 2.0 / gam)        # rotation per step, SURVEY.md B.9 (q/m=-1: sign carried by h)
+    assert np.allclose(dphi, -want, rtol=0, atol=1e-13)
+
+
+def test_exb_drift():
+    nx = ny = 16; dx = dy = 0.1; dt = 0.02
+    P = ob.make_params(lib, nx, ny, 8, 8, dx, dy, dt)
+    pl = _zero_planes(nx, ny); pl[5][:] = 1.0; pl[1][:] = 0.01          # Bz, Ey -> drift vx = Ey/Bz
+    p = _one(0.8, 0.8, 0.0, 0.0, 0.0)
+    xs = []
+    x_unw, prev = 0.8, 0.8
+    for _ in range(2000):
+        ob.push_deposit(lib, P, pl, p)
+        d = p["x"][0] - prev
+        d -= P.box_x * np.round(d / P.box_x)
+        x_unw += d; prev = p["x"][0]
+        xs.append(x_unw)
+    v = (xs[-1] - xs[0]) / (dt * (len(xs) - 1))
+    assert abs(v - 0.01) < 2e-4
+
+
+def test_wrap_and_tile_key_edges():
+    nx, ny, tnx, tny = 32, 16, 8, 4; dx = dy = 0.1
+    P = ob.make_params(lib, nx, ny, tnx, tny, dx, dy, 0.03)
+    pl = _zero_planes(nx, ny)
+    # leaves through the right/upper box edge and through the left/lower edge
+    for (x, y, ux, uy) in ((3.199, 1.599, 0.5, 0.5), (0.001, 0.001, -0.5, -0.5)):
+        p = _one(x, y, ux, uy, 0.0)
+        ob.push_deposit(lib, P, pl, p)
+        assert 0.0 <= p["x"][0] < P.box_x and 0.0 <= p["y"][0] < P.box_y
+        k = ob.tile_keys(lib, P, p["x"], p["y"])[0]
+        assert k == plasma.tile_of(p["x"], p["y"], nx, tnx, tny, dx, dy)[0]
+        assert 0 <= k < (nx // tnx) * (ny // tny)
+    x = np.nextafter(np.array([P.box_x]), 0.0); y = np.array([0.05])
+    assert ob.tile_keys(lib, P, x, y)[0] in (nx // tnx - 1, 0)
+
+
+def test_deposit_total_and_continuity():
+    """Sum of Jx*dx*dy = q*vx per particle, and the discrete continuity equation holds to round-off:
+    (rho1-rho0)/dt + div J = 0 at every node (zigzag is charge conserving)."""
+    nx, ny, tnx, tny = 24, 16, 8, 8; dx, dy = 0.1, 0.125
+    dt = 0.5 / np.sqrt(1 / dx**2 + 1 / dy**2)
+    P = ob.make_params(lib, nx, ny, tnx, tny, dx, dy, dt)
+    parts = plasma.load_uniform(nx, ny, tnx, tny, dx, dy, 9, u_th=0.6, seed=5)
+    pl = [0.05 * np.random.default_rng(2).standard_normal((ny, nx)) for _ in range(6)]
+    rho0 = ob.deposit_rho(lib, P, parts).astype(np.float64) / 2.0**52
+    x0 = parts["x"].copy()
+    J = ob.push_deposit(lib, P, pl, parts).astype(np.float64) / 2.0**52
+    rho1 = ob.deposit_rho(lib, P, parts).astype(np.float64) / 2.0**52
+    div = (J[0] - np.roll(J[0], 1, axis=1)) / dx + (J[1] - np.roll(J[1], 1, axis=0)) / dy
+    res = (rho1 - rho0) / dt + div
+    assert np.abs(res).max() < 1e-12 * np.abs(rho0).max() / dt
+    g = np.sqrt(1 + parts["ux"]**2 + parts["uy"]**2 + parts["uz"]**2)
+    assert abs(J[0].sum() * dx * dy - (parts["q"] * parts["ux"] / g).sum()) < 1e-13
+    assert abs(J[2].sum() * dx * dy - (parts["q"] * parts["uz"] / g).sum()) < 1e-13
+    assert (np.abs(parts["x"] - x0) > 0).any()
+
+
+def test_sort_is_stable_and_counts_match():
+    nx, ny, tnx, tny = 32, 32, 8, 8; dx = dy = 0.1; dt = 0.035
+    P = ob.make_params(lib, nx, ny, tnx, tny, dx, dy, dt)
+    parts = plasma.load_uniform(nx, ny, tnx, tny, dx, dy, 4, u_th=0.5, seed=9)
+    pl = _zero_planes(nx, ny)
+    before = {k: v.copy() for k, v in parts.items()}
+    counts, _ = ob.pic_steps(lib, P, pl, parts, 3, do_sort=True)
+    key = ob.tile_keys(lib, P, parts["x"], parts["y"])
+    assert (np.diff(key) >= 0).all() and np.array_equal(np.bincount(key, minlength=16), counts)
+    assert sorted(parts["tag"]) == sorted(before["tag"])
+    # stability: replay unsorted, then one stable argsort per step must give the same slot order
+    ref = {k: v.copy() for k, v in before.items()}
+    pl2 = _zero_planes(nx, ny)
+    for _ in range(3):
+        ob.pic_steps(lib, P, pl2, ref, 1, do_sort=False)
+        perm = np.argsort(ob.tile_keys(lib, P, ref["x"], ref["y"]), kind="stable")
+        ref = {k: np.ascontiguousarray(v[perm]) for k, v in ref.items()}
+    assert np.array_equal(ref["tag"], parts["tag"]) and np.array_equal(ref["x"], parts["x"])
+
+
+def test_cold_plasma_oscillation_at_omega_p():
+    """Uniform cold electrons with a sinusoidal velocity kick oscillate at omega_p = 1 (n0 = 1, q/m = -1)."""
+    nx, ny, tnx, tny = 32, 8, 8, 8; dx = dy = 0.1
+    dt = 0.5 / np.sqrt(2) * dx
+    P = ob.make_params(lib, nx, ny, tnx, tny, dx, dy, dt)
+    parts = plasma.load_uniform(nx, ny, tnx, tny, dx, dy, 16)
+    parts["ux"] = 1e-3 * np.sin(2 * np.pi * parts["x"] / P.box_x)
+    pl = _zero_planes(nx, ny)
+    mode = np.exp(-2j * np.pi * (np.arange(nx) + 0.5) / nx)
+    amp, t = [], []
+    nsteps = int(2.2 * np.pi / dt)
+    for s in range(nsteps):
+        ob.pic_steps(lib, P, pl, parts, 1, do_sort=True)
+        amp.append((pl[0].mean(axis=0) * mode).sum().imag); t.append((s + 1) * dt)
+    amp = np.array(amp); t = np.array(t)
+    zc = np.where(np.sign(amp[1:]) != np.sign(amp[:-1]))[0]
+    t_cross = [t[i] - amp[i] * dt / (amp[i + 1] - amp[i]) for i in zc[:2]]
+    assert len(t_cross) == 2
+    assert abs((t_cross[1] - t_cross[0]) - np.pi) < 0.03 * np.pi      # half period = pi/omega_p
