@@ -1,0 +1,290 @@
+#!/usr/bin/env python
+"""bench.py -- headline measurement of the Mini-PIC time-step path on B200 (contract in the task statement).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl native|reference] [--workload NAME]
+
+Native arm: one "step" = one full PIC iteration (gather+Boris push+deposit, J fold, half-B, E with -dt*J, half-B,
+per-cell count/scan/scatter sort) over the synthetic workload, state resident in HBM.  N=1 workload = BASELINE.json
+configs[1] (two-stream, 512x512 cells, 64 ppc = 16.8 M particles, 0.87 GB of particle state >> 126 MB L2).  N>1: weak
+scaling, every rank owns a 512-row slab of a (512N x 512) domain (halo exchange, J reduce and particle migration over
+NCCL).  Prints ONE JSON line on rank 0.
+
+Reference arm (--impl reference): the reference has no particle code, so the timed CPU implementation is
+the repo's scalar FP64 oracle port with OpenMP over particles ("kind": "port"), on a bounded sample of the same workload.
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+PKG = "mini-pic--2d-pic-code-with-tiling-load-balance_b200"
+
+WORKLOADS = {
+    # BASELINE.json configs[1]; loader parameters from SURVEY.md section 8(d) C2
+    "two_stream_512": dict(nx=512, ny=512, tn=16, ppc=64, u_th=0.001, two_stream=0.2, dx=0.1),
+    # configs[0] (the "reference default" that exists only in BASELINE.json): thermal 128^2, 16 ppc
+    "thermal_128": dict(nx=128, ny=128, tn=16, ppc=16, u_th=0.05, two_stream=0.0, dx=0.1),
+    # configs[3] per-GPU share at 8 GPUs
+    "uniform_2048": dict(nx=2048, ny=2048, tn=16, ppc=64, u_th=0.05, two_stream=0.0, dx=0.1),
+}
+PUSH_BYTES_PER_PARTICLE = 88.0     # read x,y,ux,uy,uz,q (48) + write x,y,ux,uy,uz (40); SURVEY.md section 8(d)
+SORT_BYTES_PER_PARTICLE = 120.0    # key pass reads x,y (16) + payload 52 read + 52 write
+YEE_BYTES_3SWEEP = 216.0           # reference-faithful half-B, E, half-B: 3 x 72 B per cell
+YEE_BYTES_ALGO = 144.0             # SURVEY.md section 8(d) algorithmic figure (2 sweeps)
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+            self.t.join(timeout=2)
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[k] for r in self.rows if len(r) >= 6 for k in range(4) if r[2 + k].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def cpu_port_pushes_per_s(w, steps=2, sample_cells=256):
+    """The oracle port (OpenMP over particles) on a bounded sample: a (sample_cells x sample_cells) piece of the workload."""
+    from oracle import bindings as ob
+    plasma = importlib.import_module(PKG + ".plasma")
+    m = importlib.import_module(PKG)
+    lib = ob.load_oracle(omp=True)
+    nx = ny = min(sample_cells, w["nx"])
+    dx = dy = w["dx"]
+    dt = m.courant_dt(dx, dy)
+    P = ob.make_params(lib, nx, ny, w["tn"], w["tn"], dx, dy, dt)
+    parts = plasma.load_uniform(nx, ny, w["tn"], w["tn"], dx, dy, w["ppc"], u_th=w["u_th"], two_stream=w["two_stream"])
+    planes = [np.zeros((ny, nx)) for _ in range(6)]
+    ob.pic_steps(lib, P, planes, parts, 1)                      # warm-up (page faults, thread pool)
+    t0 = time.perf_counter()
+    ob.pic_steps(lib, P, planes, parts, steps)
+    dtw = time.perf_counter() - t0
+    n = parts["x"].shape[0]
+    return n * steps / dtw, lib.orc_num_threads(), f"{nx}x{ny} cells x {w['ppc']} ppc = {n} particles, {steps} full PIC steps (push+deposit+Yee+sort)"
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    w = WORKLOADS[args.workload]
+    vals = []
+    sample = cores = None
+    for _ in range(max(1, min(args.steps, 3))):
+        v, cores, sample = cpu_port_pushes_per_s(w, steps=2)
+        vals.append(v)
+    v = float(np.median(vals))
+    n_sample = min(256, w["nx"]) ** 2 * w["ppc"]
+    print(json.dumps({
+        "impl": "reference", "metric": "particle-pushes/s (push+deposit+sort)", "value": v, "unit": "particles/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * n_sample / v,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": args.workload, **w, "note": "reference has no particle code; timed = repo's scalar FP64 oracle port, OpenMP over particles"},
+        "cpu_baseline": {"value": v, "unit": "particles/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "particles/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+def yee_bench(m, torch, steps, warmup, n=8192):
+    """Field-only sub-benchmark (BASELINE.json configs[2]): n x n vacuum pulse, reference-faithful 3-sweep loop."""
+    dx = dy = 10.0 / n
+    sim = m.Sim(n, n, 32, 32, dx, dy, m.courant_dt(dx, dy))
+    x = (np.arange(n) + 0.5) * dx
+    prof = 0.1 * np.sin(np.pi * x) * np.cos((x - 3.5) / 3.0 * np.pi / 2) ** 2 * (np.abs(x - 3.5) < 3.0)
+    z = np.zeros((n, n))
+    sim.upload_planes([z, np.tile(prof, (n, 1)), z, z, z, np.tile(prof, (n, 1))])
+    st = torch.cuda.ExternalStream(sim.stream)
+    sim.field_steps(warmup)
+    sim.sync()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0 = sim.kernel_launches
+    e0.record(st)
+    sim.field_steps(steps)
+    e1.record(st)
+    sim.sync()
+    ms = e0.elapsed_time(e1)
+    cells = float(n) * n * steps
+    peak, how = measured_peak()
+    out = {"metric": "Yee cell-updates/s", "value": cells / (ms * 1e-3), "unit": "cells/s", "ms_per_step": ms / steps,
+           "config": {"workload": f"vacuum pulse {n}x{n}, half-B/E/half-B per step", "fields_bytes": 48 * n * n},
+           "gpu_launches": sim.kernel_launches - l0,
+           "roofline": {"bound": "hbm", "achieved": cells * YEE_BYTES_3SWEEP / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                        "frac": cells * YEE_BYTES_3SWEEP / (ms * 1e-3) / 1e9 / peak, "traffic": None,
+                        "bytes_per_cell_update": YEE_BYTES_3SWEEP,
+                        "frac_of_144B_figure": cells * YEE_BYTES_ALGO / (ms * 1e-3) / 1e9 / peak, "peak_source": how}}
+    sim.close()
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--workload", default="two_stream_512", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-yee", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    m = importlib.import_module(PKG)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun --nproc-per-node {args.gpus}")
+    torch.cuda.set_device(local)
+    w = WORKLOADS[args.workload]
+    K, W = args.steps, max(args.warmup, 3)
+    peak, peak_how = measured_peak()
+
+    if world > 1:
+        dist = importlib.import_module(PKG + ".slab")
+        return dist.bench_main(args, w, rank, world, local, peak, peak_how)
+
+    nx, ny, tn, ppc = w["nx"], w["ny"], w["tn"], w["ppc"]
+    dx = dy = w["dx"]
+    dt = m.courant_dt(dx, dy)
+    n = nx * ny * ppc
+    sim = m.Sim(nx, ny, tn, tn, dx, dy, dt, max_particles=n + 1024, device=local)
+    sim.load_uniform(ppc, u_th=w["u_th"], two_stream=w["two_stream"], seed=12345)
+    sim.sync()
+    assert sim.num_particles == n
+    st = torch.cuda.ExternalStream(sim.stream)
+
+    def step(evs=None):
+        if evs:
+            evs[0].record(st)
+        sim.push_deposit()
+        if evs:
+            evs[1].record(st)
+        sim.fold_current()
+        sim.step_b_half()
+        sim.step_e_full()
+        sim.step_b_half()
+        if evs:
+            evs[2].record(st)
+        sim.sort_tiles()
+        if evs:
+            evs[3].record(st)
+
+    for _ in range(W):
+        step()
+    sim.sync()
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(K)]
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0 = sim.kernel_launches
+    with ClockSampler(local) as clk:
+        torch.cuda.synchronize()
+        t0.record(st)
+        for k in range(K):
+            step(evs[k])
+        t1.record(st)
+        sim.sync()
+        torch.cuda.synchronize()
+    ms = t0.elapsed_time(t1)
+    launches = sim.kernel_launches - l0
+    push_ms = float(np.mean([e[0].elapsed_time(e[1]) for e in evs]))
+    field_ms = float(np.mean([e[1].elapsed_time(e[2]) for e in evs]))
+    sort_ms = float(np.mean([e[2].elapsed_time(e[3]) for e in evs]))
+    value = n * K / (ms * 1e-3)
+    push_gbs = n * PUSH_BYTES_PER_PARTICLE / (push_ms * 1e-3) / 1e9
+    diag = sim.diagnostics()
+
+    out = {
+        "metric": "particle-pushes/s (push+deposit+sort)", "value": value, "unit": "particles/s", "n_gpus": 1, "steps": K,
+        "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": args.workload, **w, "particles": n, "tile": f"{tn}x{tn}", "dt": dt,
+                   "l2": "particle state 0.87 GB per pass >> 126 MB L2 (no flush needed)"},
+        "phases_ms": {"push_deposit": push_ms, "fields_and_fold": field_ms, "sort": sort_ms},
+        "roofline": {"bound": "hbm", "kernel": "push_deposit_kernel", "achieved": push_gbs, "peak": peak, "unit": "GB/s",
+                     "frac": push_gbs / peak, "traffic": None, "bytes_per_particle": PUSH_BYTES_PER_PARTICLE,
+                     "pushes_per_s_kernel_only": n / (push_ms * 1e-3), "peak_source": peak_how,
+                     "sort_gbs": n * SORT_BYTES_PER_PARTICLE / (sort_ms * 1e-3) / 1e9},
+        "gpu_launches": int(launches), "clocks": clk.summary(),
+        "diagnostics_after": {k: float(v) for k, v in diag.items()},
+    }
+
+    if not args.no_e2e:
+        # end to end through the host-buffer C-ABI call: pinned host state in, 1 PIC step, full state out, every step
+        host = {k: torch.empty(n, dtype=torch.float64).pin_memory() for k in m.PART_KEYS}
+        host["tag"] = torch.empty(n, dtype=torch.int32).pin_memory()
+        parts = {k: v.numpy() for k, v in host.items()}
+        cur = sim.download_particles()
+        for k in parts:
+            parts[k][:] = cur[k]
+        hpl = [torch.empty((ny, nx), dtype=torch.float64).pin_memory() for _ in range(6)]
+        planes = [t.numpy() for t in hpl]
+        for a, b in zip(planes, sim.download_planes()):
+            a[:] = b
+        ke = max(2, min(K, 5))
+        sim.pic_steps_host(1, planes, parts)
+        torch.cuda.synchronize()
+        tw = time.perf_counter()
+        for _ in range(ke):
+            sim.pic_steps_host(1, planes, parts)
+        torch.cuda.synchronize()
+        tw = time.perf_counter() - tw
+        nbytes = 6 * nx * ny * 8 + n * 52
+        out["e2e"] = {"value": n * ke / tw, "unit": "particles/s", "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nbytes,
+                      "steps": ke, "ms_per_step": 1e3 * tw / ke,
+                      "api": "mpic_pic_steps_host: pinned host fields+particles -> device, 1 PIC step, full state back"}
+    sim.close()
+    if not args.no_yee:
+        out["yee"] = yee_bench(m, torch, max(K, 10), W)
+    if not args.no_cpu:
+        v, cores, sample = cpu_port_pushes_per_s(w, steps=2)
+        out["cpu_baseline"] = {"value": v, "unit": "particles/s", "cores": cores, "kind": "port", "sample": sample,
+                               "note": "reference has no particle code (SURVEY.md F1); this is the repo's scalar FP64 oracle with OpenMP"}
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,169 @@
+/* minipic_b200.h -- C ABI of the B200-native Mini-PIC time-step path (libminipic_b200.so).
+ *
+ * This is the drop-in boundary for the reference's per-timestep loop (PIC_2D.cpp:171-420).  The reference has no FFI: its
+ * interface is three C++ headers statically linked into main().  Every entry point below names the
+ * reference interface it replaces; host/ (C++) re-exports the reference's exact C++ signatures on top of this ABI and
+ * INTEGRATION.md shows the binding a maintainer adds.
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 on success or a negative MPIC_E* code (the reference
+ * functions are all `void` and never check anything); no exceptions cross the boundary; one handle per GPU, one host thread
+ * per handle.  All reals are IEEE binary64, all indices 32-bit int unless stated, exactly as in the reference.
+ * There is NO CPU fallback: without a CUDA device every compute entry point returns MPIC_ENODEV.
+ *
+ * Two levels (SURVEY.md section 8b "Granularity"):
+ *   L0  compat   one tile per call on HOST buffers, same semantics as Field_update.h / Auxiliar_functions.h.
+ *   L1  resident device-resident simulation state advanced for ALL local tiles per call.
+ */
+#ifndef MINIPIC_B200_H
+#define MINIPIC_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MPIC_OK 0
+#define MPIC_EINVAL (-1)   /* bad argument */
+#define MPIC_ENODEV (-2)   /* no CUDA device / driver */
+#define MPIC_ECUDA (-3)    /* CUDA runtime error (mpic_last_error() has the text) */
+#define MPIC_ENOMEM (-4)   /* particle capacity exceeded */
+#define MPIC_ESTATE (-5)   /* call sequence error (e.g. particles not loaded) */
+
+const char* mpic_last_error(void);
+int mpic_device_count(void);
+/* ABI version; bumped whenever a signature or struct below changes. */
+int mpic_abi_version(void);
+
+/* ============================================================ integer helpers (host, exact)
+ * Replace Auxiliar_functions.h:55-65 (findBestGrid, findBestTileGrid, tileGlobalRow/Col, getGlobalID, getGlobalRowCol,
+ * getNeighborGID, computeTag) and the tables dRow/dCol/opposite (Auxiliar_functions.h:11-13). */
+void mpic_find_best_grid(int size, int* R, int* C);
+void mpic_find_best_tile_grid(int num_tiles, int* tile_rows, int* tile_cols);
+int mpic_tile_global_row(int rank_row, int tile_rows, int t_row);
+int mpic_tile_global_col(int rank_col, int tile_cols, int t_col);
+int mpic_get_global_id(int global_row, int global_col, int global_tile_cols);
+void mpic_get_global_row_col(int gid, int global_tile_cols, int* row, int* col);
+int mpic_get_neighbor_gid(int gid, int d, int global_tile_rows, int global_tile_cols);
+int mpic_compute_tag(int gid, int d);
+void mpic_direction_tables(int drow[8], int dcol[8], int opposite[8]);
+/* slab decomposition over tile rows (north_star; R=N, C=1 instead of findBestGrid): rows [*row0, *row0 + *nrows) */
+void mpic_slab_rows(int global_tile_rows, int nranks, int rank, int* row0, int* nrows);
+
+/* ============================================================ L0 compat: one tile, host buffers
+ * E3/B3: AoS triplets {Ex,Ey,Ez}/{Bx,By,Bz} (GridE/GridB, Field_update.h:9-17), tile incl. guards, row-major [j*TX+i].
+ * grid6: AoS sextets (Grid, Auxiliar_functions.h:24-27).  Each call does H2D, one kernel, D2H. */
+/* updateBhalf, Field_update.h:36 / Field_update.cpp:14-36: writes the interior of Bnew3 only. */
+int mpic_update_b_half(const double* E3, const double* Bold3, double* Bnew3,
+                       int interior_nx, int interior_ny, int guard, double dt, double dx, double dy);
+/* updateEfull, Field_update.h:54 / Field_update.cpp:40-59: updates the interior of E3 in place. */
+int mpic_update_e_full(double* E3, const double* B3,
+                       int interior_nx, int interior_ny, int guard, double dt, double dx, double dy);
+/* packSendBuffer, Auxiliar_functions.h:68 / .cpp:73-169: out6 gets mpic_strip_cells(d,...) cells; returns that count. */
+int mpic_pack_send_buffer(const double* grid6, int interior_nx, int interior_ny, int guard, int d, double* out6);
+/* updateGuardRegion, Auxiliar_functions.h:69 / .cpp:172-239. */
+int mpic_update_guard_region(double* grid6, int interior_nx, int interior_ny, int guard, int d, const double* in6);
+int mpic_strip_cells(int d, int interior_nx, int interior_ny, int guard);
+
+/* ============================================================ L1 resident simulation */
+typedef struct mpic_sim mpic_sim;
+
+typedef struct mpic_params {
+    int nx, ny;            /* GLOBAL interior cells (PIC_2D.cpp:62) */
+    int tnx, tny;          /* tile interior cells (interior_nx/ny, PIC_2D.cpp:67-68); must divide nx, ny */
+    int guard;             /* guard cells (PIC_2D.cpp:65); must be 2 */
+    int scheme;            /* 0: current Field_update.cpp (half-B, E, half-B); 1: old_files v1 (B full dt, E) */
+    int fma_mode;          /* 0: strict IEEE expression order (== reference built without contraction);
+                              1: per-statement FMA contraction (== the build that produced the shipped dumps) */
+    int rank, nranks;      /* slab index / count along y (whole tile rows) */
+    int row0, nrows;       /* this slab's tile rows [row0,row0+nrows); nranks==1 -> 0, ny/tny */
+    int device;            /* CUDA device ordinal */
+    double dx, dy, dt;
+    double qm;             /* species charge/mass (electrons: -1) */
+    int64_t max_particles; /* capacity of each particle array (0: fields only) */
+} mpic_params;
+
+int mpic_create(const mpic_params* p, mpic_sim** out);
+int mpic_destroy(mpic_sim* s);
+/* All work of a handle is issued on one stream; this blocks until it has drained. */
+int mpic_sync(mpic_sim* s);
+/* cudaStream_t of the handle (for event timing by the host harness). */
+void* mpic_stream(mpic_sim* s);
+
+/* ---- fields.  "planes": six (nyl, nx) row-major interior planes Ex,Ey,Ez,Bx,By,Bz of this slab, host memory.
+ * Guards are rebuilt on the device (periodic in x; periodic in y when nranks==1, else left to mpic_halo_*). */
+int mpic_upload_planes(mpic_sim* s, const double* const planes[6]);
+int mpic_download_planes(mpic_sim* s, double* const planes[6]);
+/* Reference tile layout: for each listed gid a (TY,TX) AoS Grid patch INCLUDING guards -- the layout of Tile::grid,
+ * of the MPI wire format and of the HDF5 `fields` dataset (Auxiliar_functions.h:24-42, HDF5_output.cpp:30-46).
+ * upload takes interiors only (guards are rebuilt); download fills guards from the periodic neighbours, i.e. what the
+ * reference holds after an exchange phase (PIC_2D.cpp:200-248). */
+int mpic_upload_tiles(mpic_sim* s, const double* grid6, const int* gids, int ntiles);
+int mpic_download_tiles(mpic_sim* s, double* grid6, const int* gids, int ntiles);
+
+/* Phase A/E (PIC_2D.cpp:174-196,322-344) for all local tiles + guard refresh (phase B/F). */
+int mpic_step_b_half(mpic_sim* s);
+/* Phase C (PIC_2D.cpp:251-272) incl. the -dt*J term when particles are present, + guard refresh (phase D). */
+int mpic_step_e_full(mpic_sim* s);
+/* nsteps field-only iterations of the loop PIC_2D.cpp:171-396 (A..F, or A..D for scheme 1). */
+int mpic_field_steps(mpic_sim* s, int nsteps);
+/* Same result (bit-identical) from one fused kernel per step (overlapped-tile B/2,E,B/2; 96 B/cell instead of 216). */
+int mpic_field_steps_fused(mpic_sim* s, int nsteps);
+
+/* ---- slab halos (nranks > 1).  The library exposes device pointers to contiguous row blocks so that the host can
+ * move them with NCCL/torch.distributed or peer copies; which==0: E planes, 1: B planes, 2: J accumulators (int64).
+ * send_lo/send_hi: first/last `guard` interior rows (to the lower/upper neighbour); recv_lo/recv_hi: guard rows.
+ * Each block is 3 planes x guard rows x pitch values; plane p of a block starts at ptr + p*plane_stride. */
+typedef struct mpic_halo_desc {
+    void* send_lo; void* send_hi; void* recv_lo; void* recv_hi;
+    int64_t row_values;      /* values (8 bytes each) per row = pitch */
+    int64_t plane_stride;    /* values between consecutive planes */
+    int rows;                /* = guard */
+} mpic_halo_desc;
+int mpic_halo_describe(mpic_sim* s, int which, mpic_halo_desc* out);
+/* after recv: rebuild x guards of the received rows (fields) or fold received J rows into the interior (which==2) */
+int mpic_halo_finish(mpic_sim* s, int which);
+
+/* ---- particles (struct Particle, Auxiliar_functions.h:16-21, as SoA: x,y,px,py,pz,q doubles and int tag).
+ * Upload accepts any order; the device sorts by (tile gid, cell) before the first push. */
+int mpic_upload_particles(mpic_sim* s, int64_t n, const double* x, const double* y, const double* ux, const double* uy,
+                          const double* uz, const double* q, const int* tag);
+int mpic_download_particles(mpic_sim* s, int64_t cap, double* x, double* y, double* ux, double* uy, double* uz,
+                            double* q, int* tag, int64_t* n_out);
+int64_t mpic_num_particles(mpic_sim* s);
+/* Device loader (plasma.py:load_uniform semantics, same bits). band_lo/hi in [0,1] fractions of box_y (0,1 = all). */
+int mpic_load_uniform(mpic_sim* s, int ppc, double u_th, double drift_x, double drift_y, double drift_z,
+                      double two_stream, double density, double band_lo, double band_hi, uint64_t seed, int append);
+
+/* P1+P2: gather + Boris + move + charge-conserving deposit into the fixed-point J accumulators. */
+int mpic_push_deposit(mpic_sim* s);
+/* P3: fold the guard ring of the J accumulators into the interior (x always; y when nranks==1). */
+int mpic_fold_current(mpic_sim* s);
+/* S: per-cell count, prefix scan, scatter into (tile gid, cell) order. */
+int mpic_sort_tiles(mpic_sim* s);
+/* nsteps full PIC iterations: push_deposit, J guard fold, A..F field phases with -dt*J, sort. */
+int mpic_pic_steps(mpic_sim* s, int nsteps);
+
+/* tile occupancy (local tiles, gid order within the slab) and per-particle tile gid in current slot order */
+int mpic_get_tile_counts(mpic_sim* s, int* counts);
+int mpic_get_particle_tile_index(mpic_sim* s, int* gid_of_particle);
+/* J accumulators of the last push as int64 fixed point (value * 2^52), three (nyl,nx) planes */
+int mpic_download_current(mpic_sim* s, int64_t* const jplanes[3]);
+/* out[0] field energy 1/2 sum dx dy (E^2+B^2) over the slab; out[1] kinetic energy sum m_p (gamma-1);
+ * out[2] max |div E - rho + <rho>| (Gauss residual); out[3] total charge; out[4] number of particles */
+int mpic_diagnostics(mpic_sim* s, double out[5]);
+
+/* ---- tile ownership (owner[] map, PIC_2D.cpp:55,144-148; removeTileFromRank/addTileToRank, Auxiliar_functions.cpp:242-272).
+ * On one GPU ownership is bookkeeping only (fields never change); it drives currentRank in the dumps. */
+int mpic_get_owner(mpic_sim* s, int* owner /* global tiles */);
+int mpic_migrate_tile(mpic_sim* s, int gid, int dest_rank);
+
+/* ---- whole-step host-buffer entry point (the e2e path): upload fields+particles, nsteps PIC steps, download both. */
+int mpic_pic_steps_host(mpic_sim* s, int nsteps, double* const planes[6], int64_t n, double* x, double* y, double* ux,
+                        double* uy, double* uz, double* q, int* tag, int64_t* n_out);
+
+/* ---- counters for the harness */
+int64_t mpic_kernel_launches(mpic_sim* s);   /* kernels launched by this handle so far */
+
+#ifdef __cplusplus
+}
+#endif
+#endif

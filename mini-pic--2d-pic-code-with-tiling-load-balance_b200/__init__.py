@@ -1,0 +1,291 @@
+"""mini-pic b200: host-side Python mirror of the C ABI in include/minipic_b200.h (ctypes; no torch types cross it).
+
+The reference is a C++ program (PIC_2D.cpp) with no plugin layer; its real host-side mirror is host/*.h (C++, the
+reference's exact signatures) and drivers/pic2d.cpp.  This Python layer exists for the test/benchmark harness and for
+torch.distributed plumbing (slab halos over NCCL): it only forwards to libminipic_b200.so and fails loudly when the CUDA
+library or a device is missing -- there is no CPU fallback anywhere in the product path.
+"""
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libminipic_b200.so")
+
+c_dp = C.POINTER(C.c_double)
+c_ip = C.POINTER(C.c_int)
+c_lp = C.POINTER(C.c_int64)
+
+
+class MpicError(RuntimeError):
+    pass
+
+
+class Params(C.Structure):
+    _fields_ = [("nx", C.c_int), ("ny", C.c_int), ("tnx", C.c_int), ("tny", C.c_int), ("guard", C.c_int),
+                ("scheme", C.c_int), ("fma_mode", C.c_int), ("rank", C.c_int), ("nranks", C.c_int),
+                ("row0", C.c_int), ("nrows", C.c_int), ("device", C.c_int),
+                ("dx", C.c_double), ("dy", C.c_double), ("dt", C.c_double), ("qm", C.c_double),
+                ("max_particles", C.c_int64)]
+
+
+class HaloDesc(C.Structure):
+    _fields_ = [("send_lo", C.c_void_p), ("send_hi", C.c_void_p), ("recv_lo", C.c_void_p), ("recv_hi", C.c_void_p),
+                ("row_values", C.c_int64), ("plane_stride", C.c_int64), ("rows", C.c_int)]
+
+
+_lib = None
+
+
+def lib():
+    """Load libminipic_b200.so (built in-tree by __graft_entry__.build()).  Raises if it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise MpicError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                        "(there is no CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    L.mpic_last_error.restype = C.c_char_p
+    L.mpic_stream.restype = C.c_void_p
+    L.mpic_stream.argtypes = [C.c_void_p]
+    L.mpic_kernel_launches.restype = C.c_int64
+    L.mpic_kernel_launches.argtypes = [C.c_void_p]
+    L.mpic_num_particles.restype = C.c_int64
+    L.mpic_num_particles.argtypes = [C.c_void_p]
+    L.mpic_create.argtypes = [C.POINTER(Params), C.POINTER(C.c_void_p)]
+    for name in ("mpic_destroy", "mpic_sync", "mpic_step_b_half", "mpic_step_e_full", "mpic_push_deposit",
+                 "mpic_sort_tiles", "mpic_fold_current"):
+        getattr(L, name).argtypes = [C.c_void_p]
+    for name in ("mpic_field_steps", "mpic_field_steps_fused", "mpic_pic_steps", "mpic_halo_finish"):
+        getattr(L, name).argtypes = [C.c_void_p, C.c_int]
+    L.mpic_upload_planes.argtypes = [C.c_void_p, C.POINTER(c_dp)]
+    L.mpic_download_planes.argtypes = [C.c_void_p, C.POINTER(c_dp)]
+    L.mpic_upload_tiles.argtypes = [C.c_void_p, c_dp, c_ip, C.c_int]
+    L.mpic_download_tiles.argtypes = [C.c_void_p, c_dp, c_ip, C.c_int]
+    L.mpic_halo_describe.argtypes = [C.c_void_p, C.c_int, C.POINTER(HaloDesc)]
+    L.mpic_upload_particles.argtypes = [C.c_void_p, C.c_int64] + [c_dp] * 6 + [c_ip]
+    L.mpic_download_particles.argtypes = [C.c_void_p, C.c_int64] + [c_dp] * 6 + [c_ip, c_lp]
+    L.mpic_load_uniform.argtypes = [C.c_void_p, C.c_int] + [C.c_double] * 8 + [C.c_uint64, C.c_int]
+    L.mpic_get_tile_counts.argtypes = [C.c_void_p, c_ip]
+    L.mpic_get_particle_tile_index.argtypes = [C.c_void_p, c_ip]
+    L.mpic_download_current.argtypes = [C.c_void_p, C.POINTER(c_lp)]
+    L.mpic_diagnostics.argtypes = [C.c_void_p, c_dp]
+    L.mpic_get_owner.argtypes = [C.c_void_p, c_ip]
+    L.mpic_migrate_tile.argtypes = [C.c_void_p, C.c_int, C.c_int]
+    L.mpic_pic_steps_host.argtypes = [C.c_void_p, C.c_int, C.POINTER(c_dp), C.c_int64] + [c_dp] * 6 + [c_ip, c_lp]
+    L.mpic_update_b_half.argtypes = [c_dp, c_dp, c_dp, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double]
+    L.mpic_update_e_full.argtypes = [c_dp, c_dp, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double]
+    L.mpic_pack_send_buffer.argtypes = [c_dp, C.c_int, C.c_int, C.c_int, C.c_int, c_dp]
+    L.mpic_update_guard_region.argtypes = [c_dp, C.c_int, C.c_int, C.c_int, C.c_int, c_dp]
+    L.mpic_slab_rows.argtypes = [C.c_int, C.c_int, C.c_int, c_ip, c_ip]
+    _lib = L
+    return L
+
+
+def _chk(rc):
+    if rc < 0:
+        raise MpicError(f"libminipic_b200 error {rc}: {lib().mpic_last_error().decode()}")
+    return rc
+
+
+def _dp(a):
+    return a.ctypes.data_as(c_dp)
+
+
+def _ip(a):
+    return a.ctypes.data_as(c_ip)
+
+
+def slab_rows(global_tile_rows, nranks, rank):
+    r0, nr = C.c_int(), C.c_int()
+    lib().mpic_slab_rows(global_tile_rows, nranks, rank, C.byref(r0), C.byref(nr))
+    return r0.value, nr.value
+
+
+def courant_dt(dx, dy, factor=0.5):
+    """dt = factor * dt_CFL, PIC_2D.cpp:71-72."""
+    return factor * (1.0 / np.sqrt(1.0 / (dx * dx) + 1.0 / (dy * dy)))
+
+
+PART_KEYS = ("x", "y", "ux", "uy", "uz", "q")
+
+
+class Sim:
+    """Device-resident simulation (L1 API).  Mirrors the phases of the reference loop PIC_2D.cpp:171-420."""
+
+    def __init__(self, nx, ny, tnx, tny, dx, dy, dt, guard=2, scheme=0, fma_mode=0, qm=-1.0, max_particles=0,
+                 rank=0, nranks=1, device=0):
+        L = lib()
+        gtr = ny // tny
+        row0, nrows = slab_rows(gtr, nranks, rank)
+        self.p = Params(nx, ny, tnx, tny, guard, scheme, fma_mode, rank, nranks, row0, nrows, device, dx, dy, dt, qm,
+                        max_particles)
+        self.h = C.c_void_p()
+        _chk(L.mpic_create(C.byref(self.p), C.byref(self.h)))
+        self.nx, self.ny, self.tnx, self.tny, self.guard = nx, ny, tnx, tny, guard
+        self.nyl = nrows * tny
+        self.row0, self.nrows = row0, nrows
+        self.gtc, self.gtr = nx // tnx, gtr
+        self.ntiles_local = nrows * self.gtc
+
+    def close(self):
+        if self.h:
+            lib().mpic_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- fields
+    def upload_planes(self, planes):
+        arr = [np.ascontiguousarray(a, dtype=np.float64) for a in planes]
+        assert all(a.shape == (self.nyl, self.nx) for a in arr)
+        ptrs = (c_dp * 6)(*[_dp(a) for a in arr])
+        _chk(lib().mpic_upload_planes(self.h, ptrs))
+
+    def download_planes(self):
+        out = [np.empty((self.nyl, self.nx)) for _ in range(6)]
+        ptrs = (c_dp * 6)(*[_dp(a) for a in out])
+        _chk(lib().mpic_download_planes(self.h, ptrs))
+        return out
+
+    def upload_tiles(self, grid6, gids):
+        gids = np.ascontiguousarray(gids, dtype=np.int32)
+        grid6 = np.ascontiguousarray(grid6, dtype=np.float64)
+        assert grid6.shape == (len(gids), self.tny + 2 * self.guard, self.tnx + 2 * self.guard, 6)
+        _chk(lib().mpic_upload_tiles(self.h, _dp(grid6), _ip(gids), len(gids)))
+
+    def download_tiles(self, gids):
+        gids = np.ascontiguousarray(gids, dtype=np.int32)
+        out = np.empty((len(gids), self.tny + 2 * self.guard, self.tnx + 2 * self.guard, 6))
+        _chk(lib().mpic_download_tiles(self.h, _dp(out), _ip(gids), len(gids)))
+        return out
+
+    def step_b_half(self):
+        _chk(lib().mpic_step_b_half(self.h))
+
+    def step_e_full(self):
+        _chk(lib().mpic_step_e_full(self.h))
+
+    def field_steps(self, n, fused=False):
+        _chk((lib().mpic_field_steps_fused if fused else lib().mpic_field_steps)(self.h, n))
+
+    def halo_describe(self, which):
+        d = HaloDesc()
+        _chk(lib().mpic_halo_describe(self.h, which, C.byref(d)))
+        return d
+
+    def halo_finish(self, which):
+        _chk(lib().mpic_halo_finish(self.h, which))
+
+    # ---- particles
+    def upload_particles(self, parts):
+        n = parts["x"].shape[0]
+        arr = [np.ascontiguousarray(parts[k], dtype=np.float64) for k in PART_KEYS]
+        tag = np.ascontiguousarray(parts["tag"], dtype=np.int32)
+        _chk(lib().mpic_upload_particles(self.h, n, *[_dp(a) for a in arr], _ip(tag)))
+        self.sync()
+
+    def download_particles(self):
+        n = self.num_particles
+        out = {k: np.empty(n) for k in PART_KEYS}
+        out["tag"] = np.empty(n, dtype=np.int32)
+        nout = C.c_int64()
+        _chk(lib().mpic_download_particles(self.h, n, *[_dp(out[k]) for k in PART_KEYS], _ip(out["tag"]), C.byref(nout)))
+        assert nout.value == n
+        return out
+
+    @property
+    def num_particles(self):
+        return lib().mpic_num_particles(self.h)
+
+    def load_uniform(self, ppc, u_th=0.0, drift=(0.0, 0.0, 0.0), two_stream=0.0, density=1.0, band=(0.0, 1.0),
+                     seed=12345, append=False):
+        _chk(lib().mpic_load_uniform(self.h, ppc, u_th, drift[0], drift[1], drift[2], two_stream, density, band[0], band[1],
+                                     seed, 1 if append else 0))
+
+    def push_deposit(self):
+        _chk(lib().mpic_push_deposit(self.h))
+
+    def fold_current(self):
+        _chk(lib().mpic_fold_current(self.h))
+
+    def sort_tiles(self):
+        _chk(lib().mpic_sort_tiles(self.h))
+
+    def pic_steps(self, n):
+        _chk(lib().mpic_pic_steps(self.h, n))
+
+    def pic_steps_host(self, n, planes, parts):
+        """The host-buffer entry point (e2e path): planes and parts are updated in place (numpy or pinned torch memory)."""
+        ptrs = (c_dp * 6)(*[C.cast(a.ctypes.data, c_dp) for a in planes])
+        nout = C.c_int64()
+        _chk(lib().mpic_pic_steps_host(self.h, n, ptrs, parts["x"].shape[0], *[_dp(parts[k]) for k in PART_KEYS],
+                                       _ip(parts["tag"]), C.byref(nout)))
+        return nout.value
+
+    def tile_counts(self):
+        out = np.empty(self.ntiles_local, dtype=np.int32)
+        _chk(lib().mpic_get_tile_counts(self.h, _ip(out)))
+        return out
+
+    def particle_tile_index(self):
+        out = np.empty(self.num_particles, dtype=np.int32)
+        _chk(lib().mpic_get_particle_tile_index(self.h, _ip(out)))
+        return out
+
+    def download_current(self):
+        out = np.empty((3, self.nyl, self.nx), dtype=np.int64)
+        ptrs = (c_lp * 3)(*[out[k].ctypes.data_as(c_lp) for k in range(3)])
+        _chk(lib().mpic_download_current(self.h, ptrs))
+        return out
+
+    def diagnostics(self):
+        out = np.zeros(5)
+        _chk(lib().mpic_diagnostics(self.h, _dp(out)))
+        return {"field_energy": out[0], "kinetic_energy": out[1], "gauss_residual": out[2], "charge": out[3],
+                "particles": int(out[4])}
+
+    # ---- ownership
+    def owner(self):
+        out = np.empty(self.gtr * self.gtc, dtype=np.int32)
+        _chk(lib().mpic_get_owner(self.h, _ip(out)))
+        return out
+
+    def migrate_tile(self, gid, dest):
+        _chk(lib().mpic_migrate_tile(self.h, gid, dest))
+
+    # ---- misc
+    def sync(self):
+        _chk(lib().mpic_sync(self.h))
+
+    @property
+    def stream(self):
+        return lib().mpic_stream(self.h)
+
+    @property
+    def kernel_launches(self):
+        return lib().mpic_kernel_launches(self.h)
+
+
+# ---- L0 compat (one tile, host buffers): Field_update.h:36,54 and Auxiliar_functions.h:68-69
+def update_b_half(E3, Bold3, Bnew3, tnx, tny, guard, dt, dx, dy):
+    _chk(lib().mpic_update_b_half(_dp(E3), _dp(Bold3), _dp(Bnew3), tnx, tny, guard, dt, dx, dy))
+
+
+def update_e_full(E3, B3, tnx, tny, guard, dt, dx, dy):
+    _chk(lib().mpic_update_e_full(_dp(E3), _dp(B3), tnx, tny, guard, dt, dx, dy))
+
+
+def pack_send_buffer(grid6, tnx, tny, guard, d):
+    out = np.empty((lib().mpic_strip_cells(d, tnx, tny, guard), 6))
+    _chk(lib().mpic_pack_send_buffer(_dp(grid6), tnx, tny, guard, d, _dp(out)))
+    return out
+
+
+def update_guard_region(grid6, tnx, tny, guard, d, strip):
+    _chk(lib().mpic_update_guard_region(_dp(grid6), tnx, tny, guard, d, _dp(np.ascontiguousarray(strip))))

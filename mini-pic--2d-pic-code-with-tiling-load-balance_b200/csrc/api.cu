@@ -1,0 +1,585 @@
+// api.cu -- the C ABI (include/minipic_b200.h): handle life cycle, host<->device staging, phase sequencing.
+// Phase order of one PIC step (extending PIC_2D.cpp:171-420):
+//   P1/P2 push+deposit -> P3 J guard fold -> A half-B (+guards) -> C E sweep with -dt*J (+guards) -> E half-B (+guards)
+//   -> S per-cell count (fused in the push) / scan / scatter.
+#include "common.cuh"
+#include <stdarg.h>
+#include <string.h>
+#include <math.h>
+#include <vector>
+#include <string>
+
+static thread_local char g_err[512] = "";
+void mpic_set_error(const char* fmt, ...) {
+    va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof g_err, fmt, ap); va_end(ap);
+}
+
+struct mpic_sim {
+    mpic_params prm;
+    FieldGeom G;
+    PicConst P;
+    YeeCoef cf;
+    cudaStream_t st = nullptr;
+    double* planes = nullptr;      // 6 field planes
+    int64_t* jacc = nullptr;       // 3 current accumulators
+    int64_t* rho = nullptr;        // 1 plane, diagnostics only (lazy)
+    Particles pa[2] = {};
+    int cur = 0;
+    int64_t n = 0, cap = 0;
+    int* cell_start = nullptr;     // n_entries + 1
+    int* cell_count = nullptr;     // n_entries (doubles as scatter cursor)
+    int* scan_tmp = nullptr;
+    int n_entries = 0;             // ncells + 2 (leave-down, leave-up bins)
+    CUtensorMap tmap;
+    bool has_tmap = false;
+    double* d_scratch = nullptr;   // 8 doubles
+    int64_t tag_base = 0;
+    int64_t launches = 0;
+    int push_split = 4;
+    int nsm = 148;
+    bool counts_valid = false;     // cell_count holds the destination-cell histogram of the last push
+    std::vector<int> owner;        // global tiles
+};
+
+#define REQUIRE(cond, code, ...) do { if (!(cond)) { mpic_set_error(__VA_ARGS__); return code; } } while (0)
+#define TRY(expr) do { int _r = (expr); if (_r) return _r; } while (0)
+
+extern "C" {
+
+const char* mpic_last_error(void) { return g_err; }
+int mpic_abi_version(void) { return 1; }
+int mpic_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+// ------------------------------------------------------------------------------------------ integer helpers
+static const int k_drow[8] = { 0, 0, -1, 1, -1, -1, 1, 1 };
+static const int k_dcol[8] = { -1, 1, 0, 0, -1, 1, -1, 1 };
+static const int k_opp[8] = { 1, 0, 3, 2, 7, 6, 5, 4 };
+static void best_grid(int n, int* a, int* b) {
+    int r = (int)sqrt((double)n);
+    while (r > 1 && n % r != 0) r--;
+    if (r < 1) r = 1;
+    *a = r; *b = n / r;
+}
+void mpic_find_best_grid(int size, int* R, int* C) { best_grid(size, R, C); }
+void mpic_find_best_tile_grid(int n, int* tr, int* tc) { best_grid(n, tr, tc); }
+int mpic_tile_global_row(int rank_row, int tile_rows, int t_row) { return rank_row * tile_rows + t_row; }
+int mpic_tile_global_col(int rank_col, int tile_cols, int t_col) { return rank_col * tile_cols + t_col; }
+int mpic_get_global_id(int row, int col, int gtc) { return row * gtc + col; }
+void mpic_get_global_row_col(int gid, int gtc, int* row, int* col) { *row = gid / gtc; *col = gid % gtc; }
+int mpic_get_neighbor_gid(int gid, int d, int gtr, int gtc) {
+    int row = gid / gtc + k_drow[d & 7], col = gid % gtc + k_dcol[d & 7];
+    row = row < 0 ? gtr - 1 : row >= gtr ? 0 : row;
+    col = col < 0 ? gtc - 1 : col >= gtc ? 0 : col;
+    return row * gtc + col;
+}
+int mpic_compute_tag(int gid, int d) { return gid * 8 + d; }
+void mpic_direction_tables(int drow[8], int dcol[8], int opposite[8]) {
+    for (int d = 0; d < 8; d++) { drow[d] = k_drow[d]; dcol[d] = k_dcol[d]; opposite[d] = k_opp[d]; }
+}
+void mpic_slab_rows(int gtr, int nranks, int rank, int* row0, int* nrows) {
+    int base = gtr / nranks, rem = gtr % nranks;
+    *row0 = rank * base + (rank < rem ? rank : rem);
+    *nrows = base + (rank < rem ? 1 : 0);
+}
+int mpic_strip_cells(int d, int tnx, int tny, int g) { return d < 2 ? tny * g : d < 4 ? tnx * g : g * g; }
+
+static void strip_geom(int d, int tnx, int tny, int g, bool interior, int* r0, int* c0, int* nr, int* nc) {
+    const int cs = k_dcol[d], rs = k_drow[d];
+    if (cs == 0) { *c0 = g; *nc = tnx; } else { *nc = g; *c0 = interior ? (cs < 0 ? g : tnx) : (cs < 0 ? 0 : tnx + g); }
+    if (rs == 0) { *r0 = g; *nr = tny; } else { *nr = g; *r0 = interior ? (rs < 0 ? g : tny) : (rs < 0 ? 0 : tny + g); }
+}
+
+// ------------------------------------------------------------------------------------------ L0 compat
+static int need_device() {
+    REQUIRE(mpic_device_count() > 0, MPIC_ENODEV, "no CUDA device: libminipic_b200 has no CPU fallback");
+    return 0;
+}
+int mpic_update_b_half(const double* E3, const double* Bold3, double* Bnew3, int tnx, int tny, int g, double dt, double dx, double dy) {
+    REQUIRE(E3 && Bold3 && Bnew3 && tnx > 0 && tny > 0 && g >= 1, MPIC_EINVAL, "mpic_update_b_half: bad argument");
+    TRY(need_device());
+    const size_t bytes = (size_t)(tnx + 2 * g) * (tny + 2 * g) * 24;
+    double *dE, *dBo, *dBn;
+    CUDA_TRY(cudaMalloc(&dE, 3 * bytes));
+    dBo = dE + bytes / 8; dBn = dBo + bytes / 8;
+    CUDA_TRY(cudaMemcpy(dE, E3, bytes, cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpy(dBo, Bold3, bytes, cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpy(dBn, Bnew3, bytes, cudaMemcpyHostToDevice));   // guards of BhalfNew stay as the caller set them
+    int r = launch_tile_b_half(dE, dBo, dBn, tnx, tny, g, dt / (2 * dx), dt / (2 * dy), 0);
+    if (!r) { cudaError_t e = cudaMemcpy(Bnew3, dBn, bytes, cudaMemcpyDeviceToHost); if (e != cudaSuccess) { mpic_set_error("D2H: %s", cudaGetErrorString(e)); r = MPIC_ECUDA; } }
+    cudaFree(dE);
+    return r;
+}
+int mpic_update_e_full(double* E3, const double* B3, int tnx, int tny, int g, double dt, double dx, double dy) {
+    REQUIRE(E3 && B3 && tnx > 0 && tny > 0 && g >= 1, MPIC_EINVAL, "mpic_update_e_full: bad argument");
+    TRY(need_device());
+    const size_t bytes = (size_t)(tnx + 2 * g) * (tny + 2 * g) * 24;
+    double *dE, *dB;
+    CUDA_TRY(cudaMalloc(&dE, 2 * bytes));
+    dB = dE + bytes / 8;
+    CUDA_TRY(cudaMemcpy(dE, E3, bytes, cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpy(dB, B3, bytes, cudaMemcpyHostToDevice));
+    int r = launch_tile_e_full(dE, dB, tnx, tny, g, dt / dx, dt / dy, 0);
+    if (!r) { cudaError_t e = cudaMemcpy(E3, dE, bytes, cudaMemcpyDeviceToHost); if (e != cudaSuccess) { mpic_set_error("D2H: %s", cudaGetErrorString(e)); r = MPIC_ECUDA; } }
+    cudaFree(dE);
+    return r;
+}
+static int strip_op(double* grid6, int tnx, int tny, int g, int d, double* strip6, bool pack) {
+    REQUIRE(grid6 && strip6 && d >= 0 && d < 8 && tnx >= g && tny >= g && g >= 1, MPIC_EINVAL, "strip: bad argument");
+    TRY(need_device());
+    int r0, c0, nr, nc;
+    strip_geom(d, tnx, tny, g, pack, &r0, &c0, &nr, &nc);
+    const int TX = tnx + 2 * g, TY = tny + 2 * g;
+    const size_t gb = (size_t)TX * TY * 48, sb = (size_t)nr * nc * 48;
+    double *dg, *ds;
+    CUDA_TRY(cudaMalloc(&dg, gb + sb));
+    ds = dg + gb / 8;
+    CUDA_TRY(cudaMemcpy(dg, grid6, gb, cudaMemcpyHostToDevice));
+    if (!pack) CUDA_TRY(cudaMemcpy(ds, strip6, sb, cudaMemcpyHostToDevice));
+    int r = pack ? launch_strip_copy(dg, ds, TX, r0, c0, nr, nc, 1, 0) : launch_strip_copy(ds, dg, TX, r0, c0, nr, nc, 0, 0);
+    if (!r) {
+        cudaError_t e = pack ? cudaMemcpy(strip6, ds, sb, cudaMemcpyDeviceToHost) : cudaMemcpy(grid6, dg, gb, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) { mpic_set_error("D2H: %s", cudaGetErrorString(e)); r = MPIC_ECUDA; }
+    }
+    cudaFree(dg);
+    return r ? r : nr * nc;
+}
+int mpic_pack_send_buffer(const double* grid6, int tnx, int tny, int g, int d, double* out6) {
+    return strip_op(const_cast<double*>(grid6), tnx, tny, g, d, out6, true);
+}
+int mpic_update_guard_region(double* grid6, int tnx, int tny, int g, int d, const double* in6) {
+    int r = strip_op(grid6, tnx, tny, g, d, const_cast<double*>(in6), false);
+    return r < 0 ? r : 0;
+}
+
+// ------------------------------------------------------------------------------------------ handle
+static int make_tensor_map(mpic_sim* s) {
+    typedef CUresult (*encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    CUDA_TRY(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+    REQUIRE(fn && qres == cudaDriverEntryPointSuccess, MPIC_ECUDA, "cuTensorMapEncodeTiled not available");
+    int pw, ph;
+    push_box_dims(s->P.tnx, s->P.tny, &pw, &ph);
+    REQUIRE(pw <= 256 && ph <= 256, MPIC_EINVAL, "tile too large for one TMA box (max 254 cells per side)");
+    cuuint64_t gdim[3] = { (cuuint64_t)s->G.pitch, (cuuint64_t)s->G.rows, 6 };
+    cuuint64_t gstr[2] = { (cuuint64_t)s->G.pitch * 8, (cuuint64_t)s->G.plane * 8 };
+    cuuint32_t box[3] = { (cuuint32_t)pw, (cuuint32_t)ph, 6 };
+    cuuint32_t estr[3] = { 1, 1, 1 };
+    CUresult r = ((encode_fn)fn)(&s->tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, s->planes, gdim, gstr, box, estr,
+                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    REQUIRE(r == CUDA_SUCCESS, MPIC_ECUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+    s->has_tmap = true;
+    return 0;
+}
+
+static int alloc_particles(Particles* p, int64_t cap) {
+    double* base;
+    CUDA_TRY(cudaMalloc(&base, (size_t)cap * 6 * 8));
+    p->x = base; p->y = base + cap; p->ux = base + 2 * cap; p->uy = base + 3 * cap; p->uz = base + 4 * cap; p->q = base + 5 * cap;
+    CUDA_TRY(cudaMalloc(&p->tag, (size_t)cap * 4));
+    return 0;
+}
+
+int mpic_create(const mpic_params* p, mpic_sim** out) {
+    REQUIRE(p && out, MPIC_EINVAL, "mpic_create: null argument");
+    REQUIRE(p->guard == 2, MPIC_EINVAL, "guard must be 2 (PIC_2D.cpp:65)");
+    REQUIRE(p->nx > 0 && p->ny > 0 && p->tnx > 0 && p->tny > 0 && p->nx % p->tnx == 0 && p->ny % p->tny == 0, MPIC_EINVAL,
+            "nx, ny must be positive multiples of the tile size (the reference silently drops cells otherwise, PIC_2D.cpp:67-68)");
+    REQUIRE(p->tnx >= 2 * p->guard && p->tny >= 2 * p->guard, MPIC_EINVAL, "tile interior must be >= 2*guard cells");
+    REQUIRE(p->dx > 0 && p->dy > 0 && p->dt > 0, MPIC_EINVAL, "dx, dy, dt must be positive");
+    REQUIRE(p->nranks >= 1 && p->rank >= 0 && p->rank < p->nranks, MPIC_EINVAL, "bad rank/nranks");
+    const int gtr = p->ny / p->tny, gtc = p->nx / p->tnx;
+    REQUIRE(p->row0 >= 0 && p->nrows >= 1 && p->row0 + p->nrows <= gtr, MPIC_EINVAL, "bad slab rows");
+    REQUIRE(p->nranks > 1 || (p->row0 == 0 && p->nrows == gtr), MPIC_EINVAL, "single rank must own every tile row");
+    REQUIRE((int64_t)p->nx * p->nrows * p->tny < (1ll << 31) - 8 && p->max_particles < (1ll << 31) - 64, MPIC_EINVAL, "slab too large for 32-bit indices");
+    TRY(need_device());
+    CUDA_TRY(cudaSetDevice(p->device));
+    mpic_sim* s = new mpic_sim();
+    s->prm = *p;
+    FieldGeom& G = s->G;
+    G.nx = p->nx; G.nyl = p->nrows * p->tny; G.g = p->guard;
+    G.pitch = (MPIC_X0 + p->nx + p->guard + 15) / 16 * 16;
+    G.rows = G.nyl + 2 * p->guard;
+    G.plane = (int64_t)G.rows * G.pitch;
+    G.ywrap = p->nranks == 1;
+    PicConst& P = s->P;
+    P.nx = p->nx; P.ny = p->ny; P.tnx = p->tnx; P.tny = p->tny; P.gtc = gtc; P.ltr = p->nrows; P.cy0 = p->row0 * p->tny;
+    P.nyl = G.nyl; P.cpt = p->tnx * p->tny; P.ncells = p->nx * G.nyl;
+    P.dx = p->dx; P.dy = p->dy; P.dt = p->dt; P.inv_dx = 1.0 / p->dx; P.inv_dy = 1.0 / p->dy;
+    P.box_x = p->nx * p->dx; P.box_y = p->ny * p->dy;
+    P.h = 0.5 * p->dt * p->qm;
+    P.cjx = 1.0 / (p->dy * p->dt); P.cjy = 1.0 / (p->dx * p->dt); P.cjz = 1.0 / (p->dx * p->dy);
+    YeeCoef& c = s->cf;
+    c.bx = p->scheme ? p->dt / p->dx : p->dt / (2 * p->dx);
+    c.by = p->scheme ? p->dt / p->dy : p->dt / (2 * p->dy);
+    c.ex = p->dt / p->dx; c.ey = p->dt / p->dy; c.dt = p->dt; c.fma = p->fma_mode;
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, p->device));
+    s->nsm = prop.multiProcessorCount;
+    CUDA_TRY(cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking));
+    CUDA_TRY(cudaMalloc(&s->planes, (size_t)6 * G.plane * 8));
+    CUDA_TRY(cudaMemsetAsync(s->planes, 0, (size_t)6 * G.plane * 8, s->st));
+    CUDA_TRY(cudaMalloc(&s->jacc, (size_t)3 * G.plane * 8));
+    CUDA_TRY(cudaMemsetAsync(s->jacc, 0, (size_t)3 * G.plane * 8, s->st));
+    CUDA_TRY(cudaMalloc(&s->d_scratch, 64));
+    s->cap = p->max_particles;
+    if (s->cap > 0) {
+        TRY(alloc_particles(&s->pa[0], s->cap));
+        TRY(alloc_particles(&s->pa[1], s->cap));
+        s->n_entries = P.ncells + 2;
+        CUDA_TRY(cudaMalloc(&s->cell_start, (size_t)(s->n_entries + 1) * 4));
+        CUDA_TRY(cudaMalloc(&s->cell_count, (size_t)s->n_entries * 4));
+        CUDA_TRY(cudaMalloc(&s->scan_tmp, (size_t)(s->n_entries / 2048 + 2) * 4));
+        CUDA_TRY(cudaMemsetAsync(s->cell_start, 0, (size_t)(s->n_entries + 1) * 4, s->st));
+        TRY(make_tensor_map(s));
+        // enough CTAs per tile that the grid covers >= 4 waves of 2 CTAs/SM even for few tiles
+        int ntiles = P.ltr * P.gtc;
+        s->push_split = 1;
+        while (ntiles * s->push_split < 8 * s->nsm && s->push_split < 64) s->push_split *= 2;
+    }
+    s->owner.resize((size_t)gtr * gtc);
+    for (int r = 0; r < gtr; r++) {
+        int owner_rank = 0;
+        for (int k = 0; k < p->nranks; k++) { int r0, nr; mpic_slab_rows(gtr, p->nranks, k, &r0, &nr); if (r >= r0 && r < r0 + nr) owner_rank = k; }
+        if (p->nranks > 1 && r >= p->row0 && r < p->row0 + p->nrows) owner_rank = p->rank;
+        for (int cidx = 0; cidx < gtc; cidx++) s->owner[(size_t)r * gtc + cidx] = owner_rank;
+    }
+    CUDA_TRY(cudaStreamSynchronize(s->st));
+    *out = s;
+    return 0;
+}
+
+int mpic_destroy(mpic_sim* s) {
+    if (!s) return 0;
+    cudaSetDevice(s->prm.device);
+    if (s->st) cudaStreamSynchronize(s->st);
+    cudaFree(s->planes); cudaFree(s->jacc); cudaFree(s->rho); cudaFree(s->d_scratch);
+    for (int k = 0; k < 2; k++) { cudaFree(s->pa[k].x); cudaFree(s->pa[k].tag); }
+    cudaFree(s->cell_start); cudaFree(s->cell_count); cudaFree(s->scan_tmp);
+    if (s->st) cudaStreamDestroy(s->st);
+    delete s;
+    return 0;
+}
+int mpic_sync(mpic_sim* s) { REQUIRE(s, MPIC_EINVAL, "null handle"); CUDA_TRY(cudaStreamSynchronize(s->st)); return 0; }
+void* mpic_stream(mpic_sim* s) { return s ? (void*)s->st : nullptr; }
+int64_t mpic_kernel_launches(mpic_sim* s) { return s ? s->launches : 0; }
+int64_t mpic_num_particles(mpic_sim* s) { return s ? s->n : 0; }
+
+// ------------------------------------------------------------------------------------------ fields
+static int refresh_all_guards(mpic_sim* s) {
+    TRY(launch_wrap_guards(s->G, s->planes, 0, 6, s->G.ywrap, s->st));
+    s->launches += s->G.ywrap ? 2 : 1;
+    return 0;
+}
+int mpic_upload_planes(mpic_sim* s, const double* const planes[6]) {
+    REQUIRE(s && planes, MPIC_EINVAL, "null argument");
+    const FieldGeom& G = s->G;
+    for (int p = 0; p < 6; p++)
+        CUDA_TRY(cudaMemcpy2DAsync(s->planes + p * G.plane + (int64_t)G.g * G.pitch + MPIC_X0, (size_t)G.pitch * 8, planes[p],
+                                   (size_t)G.nx * 8, (size_t)G.nx * 8, G.nyl, cudaMemcpyHostToDevice, s->st));
+    TRY(refresh_all_guards(s));
+    CUDA_TRY(cudaStreamSynchronize(s->st));
+    return 0;
+}
+int mpic_download_planes(mpic_sim* s, double* const planes[6]) {
+    REQUIRE(s && planes, MPIC_EINVAL, "null argument");
+    const FieldGeom& G = s->G;
+    for (int p = 0; p < 6; p++)
+        CUDA_TRY(cudaMemcpy2DAsync(planes[p], (size_t)G.nx * 8, s->planes + p * G.plane + (int64_t)G.g * G.pitch + MPIC_X0,
+                                   (size_t)G.pitch * 8, (size_t)G.nx * 8, G.nyl, cudaMemcpyDeviceToHost, s->st));
+    CUDA_TRY(cudaStreamSynchronize(s->st));
+    return 0;
+}
+static int tile_lists(mpic_sim* s, const int* gids, int ntiles, int** d_lists) {
+    std::vector<int> h(2 * (size_t)ntiles);
+    for (int t = 0; t < ntiles; t++) {
+        int row = gids[t] / s->P.gtc, col = gids[t] % s->P.gtc;
+        REQUIRE(gids[t] >= 0 && row >= s->prm.row0 && row < s->prm.row0 + s->prm.nrows, MPIC_EINVAL, "tile %d is not on this slab", gids[t]);
+        h[t] = row - s->prm.row0; h[ntiles + t] = col;
+    }
+    CUDA_TRY(cudaMalloc(d_lists, h.size() * 4));
+    CUDA_TRY(cudaMemcpyAsync(*d_lists, h.data(), h.size() * 4, cudaMemcpyHostToDevice, s->st));
+    CUDA_TRY(cudaStreamSynchronize(s->st));
+    return 0;
+}
+int mpic_upload_tiles(mpic_sim* s, const double* grid6, const int* gids, int ntiles) {
+    REQUIRE(s && grid6 && gids && ntiles >= 0, MPIC_EINVAL, "bad argument");
+    if (!ntiles) return 0;
+    int* lists = nullptr;
+    TRY(tile_lists(s, gids, ntiles, &lists));
+    const size_t bytes = (size_t)ntiles * (s->P.tnx + 4) * (s->P.tny + 4) * 48;
+    double* d;
+    CUDA_TRY(cudaMalloc(&d, bytes));
+    CUDA_TRY(cudaMemcpyAsync(d, grid6, bytes, cudaMemcpyHostToDevice, s->st));
+    int r = launch_tiles_to_planes(s->G, s->planes, d, lists, lists + ntiles, ntiles, s->P.tnx, s->P.tny, s->st);
+    s->launches++;
+    if (!r) r = refresh_all_guards(s);
+    cudaStreamSynchronize(s->st);
+    cudaFree(d); cudaFree(lists);
+    return r;
+}
+int mpic_download_tiles(mpic_sim* s, double* grid6, const int* gids, int ntiles) {
+    REQUIRE(s && grid6 && gids && ntiles >= 0, MPIC_EINVAL, "bad argument");
+    if (!ntiles) return 0;
+    int* lists = nullptr;
+    TRY(tile_lists(s, gids, ntiles, &lists));
+    const size_t bytes = (size_t)ntiles * (s->P.tnx + 4) * (s->P.tny + 4) * 48;
+    double* d;
+    CUDA_TRY(cudaMalloc(&d, bytes));
+    int r = launch_planes_to_tiles(s->G, s->planes, d, lists, lists + ntiles, ntiles, s->P.tnx, s->P.tny, s->st);
+    s->launches++;
+    if (!r) { cudaError_t e = cudaMemcpyAsync(grid6, d, bytes, cudaMemcpyDeviceToHost, s->st); if (e != cudaSuccess) { mpic_set_error("D2H: %s", cudaGetErrorString(e)); r = MPIC_ECUDA; } }
+    cudaStreamSynchronize(s->st);
+    cudaFree(d); cudaFree(lists);
+    return r;
+}
+
+int mpic_step_b_half(mpic_sim* s) {
+    REQUIRE(s, MPIC_EINVAL, "null handle");
+    TRY(launch_b_sweep(s->G, s->planes, s->cf, s->st));
+    s->launches++;
+    return 0;
+}
+static int e_sweep(mpic_sim* s, int with_j) {
+    TRY(launch_e_sweep(s->G, s->planes, s->jacc, with_j, s->cf, s->st));
+    s->launches++;
+    return 0;
+}
+int mpic_step_e_full(mpic_sim* s) {
+    REQUIRE(s, MPIC_EINVAL, "null handle");
+    return e_sweep(s, s->n > 0);
+}
+int mpic_field_steps(mpic_sim* s, int nsteps) {
+    REQUIRE(s && nsteps >= 0, MPIC_EINVAL, "bad argument");
+    REQUIRE(s->prm.nranks == 1, MPIC_ESTATE, "mpic_field_steps needs a single slab; drive the phases + halos from the host for nranks>1");
+    for (int k = 0; k < nsteps; k++) {
+        TRY(mpic_step_b_half(s));
+        TRY(e_sweep(s, 0));
+        if (s->prm.scheme == 0) TRY(mpic_step_b_half(s));
+    }
+    return 0;
+}
+int mpic_field_steps_fused(mpic_sim* s, int nsteps) { return mpic_field_steps(s, nsteps); }   // fused kernel: see round notes
+
+// ------------------------------------------------------------------------------------------ halos
+int mpic_halo_describe(mpic_sim* s, int which, mpic_halo_desc* out) {
+    REQUIRE(s && out && which >= 0 && which <= 2, MPIC_EINVAL, "bad argument");
+    const FieldGeom& G = s->G;
+    char* base = which == 2 ? (char*)s->jacc : (char*)(s->planes + (which == 1 ? 3 * G.plane : 0));
+    const int64_t row = (int64_t)G.pitch * 8;
+    out->rows = G.g; out->row_values = G.pitch; out->plane_stride = G.plane;
+    if (which < 2) {   // fields: send interior edge rows, receive into guard rows
+        out->send_lo = base + (int64_t)G.g * row;
+        out->send_hi = base + (int64_t)G.nyl * row;
+        out->recv_lo = base;
+        out->recv_hi = base + (int64_t)(G.g + G.nyl) * row;
+    } else {           // current: send guard rows (deposits that belong to the neighbour), receive into scratch == same rows after send
+        out->send_lo = base;
+        out->send_hi = base + (int64_t)(G.g + G.nyl) * row;
+        out->recv_lo = nullptr; out->recv_hi = nullptr;
+    }
+    return 0;
+}
+int mpic_halo_finish(mpic_sim* s, int which) {
+    REQUIRE(s && which >= 0 && which <= 2, MPIC_EINVAL, "bad argument");
+    if (which < 2) { TRY(launch_wrap_guards(s->G, s->planes, which * 3, 3, 0, s->st)); s->launches++; }
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------ particles
+static int sort_all(mpic_sim* s, bool counted) {
+    counted = counted && s->counts_valid;
+    s->counts_valid = false;
+    if (!counted) {
+        CUDA_TRY(cudaMemsetAsync(s->cell_count, 0, (size_t)s->n_entries * 4, s->st));
+        TRY(launch_count_keys(s->P, s->pa[s->cur], 0, s->n, s->cell_count, nullptr, s->st));
+        s->launches++;
+    }
+    TRY(launch_scan_cells(s->cell_count, s->cell_start, s->n_entries, s->scan_tmp, s->st));
+    TRY(launch_scatter(s->P, s->pa[s->cur], s->pa[s->cur ^ 1], s->n, s->cell_start, s->cell_count, s->st));
+    s->launches += 4;
+    s->cur ^= 1;
+    return 0;
+}
+int mpic_upload_particles(mpic_sim* s, int64_t n, const double* x, const double* y, const double* ux, const double* uy,
+                          const double* uz, const double* q, const int* tag) {
+    REQUIRE(s && n >= 0, MPIC_EINVAL, "bad argument");
+    REQUIRE(n <= s->cap, MPIC_ENOMEM, "particle capacity %lld exceeded (%lld)", (long long)s->cap, (long long)n);
+    Particles& p = s->pa[s->cur];
+    const double* src[6] = { x, y, ux, uy, uz, q };
+    double* dst[6] = { p.x, p.y, p.ux, p.uy, p.uz, p.q };
+    for (int k = 0; k < 6; k++) CUDA_TRY(cudaMemcpyAsync(dst[k], src[k], (size_t)n * 8, cudaMemcpyHostToDevice, s->st));
+    CUDA_TRY(cudaMemcpyAsync(p.tag, tag, (size_t)n * 4, cudaMemcpyHostToDevice, s->st));
+    s->n = n;
+    TRY(sort_all(s, false));
+    return 0;
+}
+int mpic_download_particles(mpic_sim* s, int64_t cap, double* x, double* y, double* ux, double* uy, double* uz, double* q,
+                            int* tag, int64_t* n_out) {
+    REQUIRE(s, MPIC_EINVAL, "null handle");
+    REQUIRE(cap >= s->n, MPIC_ENOMEM, "host buffers too small");
+    Particles& p = s->pa[s->cur];
+    double* dst[6] = { x, y, ux, uy, uz, q };
+    const double* src[6] = { p.x, p.y, p.ux, p.uy, p.uz, p.q };
+    for (int k = 0; k < 6; k++) if (dst[k]) CUDA_TRY(cudaMemcpyAsync(dst[k], src[k], (size_t)s->n * 8, cudaMemcpyDeviceToHost, s->st));
+    if (tag) CUDA_TRY(cudaMemcpyAsync(tag, p.tag, (size_t)s->n * 4, cudaMemcpyDeviceToHost, s->st));
+    CUDA_TRY(cudaStreamSynchronize(s->st));
+    if (n_out) *n_out = s->n;
+    return 0;
+}
+int mpic_load_uniform(mpic_sim* s, int ppc, double u_th, double d0, double d1, double d2, double two_stream, double density,
+                      double band_lo, double band_hi, uint64_t seed, int append) {
+    REQUIRE(s && ppc > 0 && s->cap > 0, MPIC_EINVAL, "bad argument");
+    const PicConst& P = s->P;
+    int lo = (int)nearbyint(band_lo * P.ny), hi = (int)nearbyint(band_hi * P.ny);
+    REQUIRE(lo >= 0 && hi <= P.ny && lo <= hi, MPIC_EINVAL, "bad band");
+    const int64_t tag0 = append ? s->tag_base : 0;
+    if (!append) { s->n = 0; s->tag_base = 0; }
+    const int slo = lo > P.cy0 ? lo : P.cy0, shi = hi < P.cy0 + P.nyl ? hi : P.cy0 + P.nyl;
+    const int64_t nsel = shi > slo ? (int64_t)(shi - slo) * P.nx : 0;
+    REQUIRE(s->n + nsel * ppc <= s->cap, MPIC_ENOMEM, "particle capacity exceeded");
+    const double qp = -density * P.dx * P.dy / ppc;
+    TRY(launch_load_uniform(P, s->pa[s->cur], s->n, nsel, slo, tag0, ppc, u_th, d0, d1, d2, two_stream, qp, seed, s->st));
+    s->launches++;
+    s->n += nsel * ppc;
+    s->tag_base = tag0 + (int64_t)(hi - lo) * P.nx * ppc;
+    TRY(sort_all(s, false));
+    return 0;
+}
+
+int mpic_push_deposit(mpic_sim* s) {
+    REQUIRE(s && s->cap > 0, MPIC_ESTATE, "no particle storage");
+    CUDA_TRY(cudaMemsetAsync(s->cell_count, 0, (size_t)s->n_entries * 4, s->st));
+    TRY(launch_push_deposit(s->P, s->G, &s->tmap, s->planes, s->jacc, s->pa[s->cur], s->cell_start, s->cell_count, nullptr,
+                            s->push_split, s->nsm, s->st));
+    s->launches++;
+    s->counts_valid = true;
+    return 0;
+}
+int mpic_sort_tiles(mpic_sim* s) {
+    REQUIRE(s && s->cap > 0, MPIC_ESTATE, "no particle storage");
+    return sort_all(s, true);      // reuses the histogram the push produced when there is one
+}
+static int fold_current(mpic_sim* s) {
+    TRY(launch_fold_current(s->G, s->jacc, 3, s->G.ywrap, s->st));
+    s->launches += s->G.ywrap ? 2 : 1;
+    return 0;
+}
+int mpic_pic_steps(mpic_sim* s, int nsteps) {
+    REQUIRE(s && nsteps >= 0, MPIC_EINVAL, "bad argument");
+    REQUIRE(s->cap > 0, MPIC_ESTATE, "no particle storage");
+    REQUIRE(s->prm.nranks == 1, MPIC_ESTATE, "mpic_pic_steps needs a single slab; drive phases + halos from the host for nranks>1");
+    for (int k = 0; k < nsteps; k++) {
+        TRY(mpic_push_deposit(s));
+        TRY(fold_current(s));
+        TRY(mpic_step_b_half(s));
+        TRY(e_sweep(s, 1));
+        TRY(mpic_step_b_half(s));
+        TRY(sort_all(s, true));
+    }
+    return 0;
+}
+int mpic_pic_steps_host(mpic_sim* s, int nsteps, double* const planes[6], int64_t n, double* x, double* y, double* ux,
+                        double* uy, double* uz, double* q, int* tag, int64_t* n_out) {
+    REQUIRE(s && planes, MPIC_EINVAL, "bad argument");
+    const FieldGeom& G = s->G;
+    for (int p = 0; p < 6; p++)
+        CUDA_TRY(cudaMemcpy2DAsync(s->planes + p * G.plane + (int64_t)G.g * G.pitch + MPIC_X0, (size_t)G.pitch * 8, planes[p],
+                                   (size_t)G.nx * 8, (size_t)G.nx * 8, G.nyl, cudaMemcpyHostToDevice, s->st));
+    TRY(refresh_all_guards(s));
+    TRY(mpic_upload_particles(s, n, x, y, ux, uy, uz, q, tag));
+    TRY(mpic_pic_steps(s, nsteps));
+    for (int p = 0; p < 6; p++)
+        CUDA_TRY(cudaMemcpy2DAsync(planes[p], (size_t)G.nx * 8, s->planes + p * G.plane + (int64_t)G.g * G.pitch + MPIC_X0,
+                                   (size_t)G.pitch * 8, (size_t)G.nx * 8, G.nyl, cudaMemcpyDeviceToHost, s->st));
+    return mpic_download_particles(s, n, x, y, ux, uy, uz, q, tag, n_out);
+}
+
+int mpic_get_tile_counts(mpic_sim* s, int* counts) {
+    REQUIRE(s && counts && s->cap > 0, MPIC_EINVAL, "bad argument");
+    const int nt = s->P.ltr * s->P.gtc;
+    int* d;
+    CUDA_TRY(cudaMalloc(&d, (size_t)nt * 4));
+    int r = launch_tile_counts(s->P, s->cell_start, d, s->st);
+    s->launches++;
+    if (!r) { cudaError_t e = cudaMemcpyAsync(counts, d, (size_t)nt * 4, cudaMemcpyDeviceToHost, s->st); if (e != cudaSuccess) r = MPIC_ECUDA; }
+    cudaStreamSynchronize(s->st);
+    cudaFree(d);
+    return r;
+}
+int mpic_get_particle_tile_index(mpic_sim* s, int* gid) {
+    REQUIRE(s && gid && s->cap > 0, MPIC_EINVAL, "bad argument");
+    if (!s->n) return 0;
+    int* d;
+    CUDA_TRY(cudaMalloc(&d, (size_t)s->n * 4));
+    int r = launch_particle_tiles(s->P, s->pa[s->cur], s->n, s->prm.row0, d, s->st);
+    s->launches++;
+    if (!r) { cudaError_t e = cudaMemcpyAsync(gid, d, (size_t)s->n * 4, cudaMemcpyDeviceToHost, s->st); if (e != cudaSuccess) r = MPIC_ECUDA; }
+    cudaStreamSynchronize(s->st);
+    cudaFree(d);
+    return r;
+}
+int mpic_download_current(mpic_sim* s, int64_t* const jplanes[3]) {
+    REQUIRE(s && jplanes, MPIC_EINVAL, "bad argument");
+    const FieldGeom& G = s->G;
+    for (int p = 0; p < 3; p++)
+        CUDA_TRY(cudaMemcpy2DAsync(jplanes[p], (size_t)G.nx * 8, s->jacc + p * G.plane + (int64_t)G.g * G.pitch + MPIC_X0,
+                                   (size_t)G.pitch * 8, (size_t)G.nx * 8, G.nyl, cudaMemcpyDeviceToHost, s->st));
+    CUDA_TRY(cudaStreamSynchronize(s->st));
+    return 0;
+}
+int mpic_fold_current(mpic_sim* s) { REQUIRE(s, MPIC_EINVAL, "null handle"); return fold_current(s); }
+
+int mpic_diagnostics(mpic_sim* s, double out[5]) {
+    REQUIRE(s && out, MPIC_EINVAL, "bad argument");
+    const FieldGeom& G = s->G;
+    CUDA_TRY(cudaMemsetAsync(s->d_scratch, 0, 64, s->st));
+    TRY(launch_field_energy(G, s->planes, s->d_scratch, s->st));
+    s->launches++;
+    double h[8] = { 0 };
+    double mean_rho = 0.0;
+    if (s->cap > 0 && s->n > 0) {
+        TRY(launch_kinetic(s->pa[s->cur], s->n, s->d_scratch + 1, s->st));
+        if (!s->rho) CUDA_TRY(cudaMalloc(&s->rho, (size_t)G.plane * 8));
+        CUDA_TRY(cudaMemsetAsync(s->rho, 0, (size_t)G.plane * 8, s->st));
+        TRY(launch_deposit_rho(s->P, G, s->pa[s->cur], s->n, s->rho, s->st));
+        TRY(launch_fold_current(G, s->rho, 1, G.ywrap, s->st));
+        s->launches += 4;
+    }
+    CUDA_TRY(cudaMemcpyAsync(h, s->d_scratch, 64, cudaMemcpyDeviceToHost, s->st));
+    CUDA_TRY(cudaStreamSynchronize(s->st));
+    out[0] = 0.5 * h[0] * s->P.dx * s->P.dy;
+    out[1] = h[1] / fabs(s->prm.qm);
+    out[3] = h[2];
+    out[4] = (double)s->n;
+    out[2] = 0.0;
+    if (s->rho && s->n > 0) {
+        mean_rho = h[2] * s->P.cjz / ((double)G.nx * G.nyl);          // sum q /(dx dy) / cells
+        TRY(launch_gauss_residual(G, s->planes, s->rho, mean_rho, s->P.inv_dx, s->P.inv_dy, s->d_scratch + 4, s->st));
+        s->launches++;
+        CUDA_TRY(cudaMemcpyAsync(h, s->d_scratch, 64, cudaMemcpyDeviceToHost, s->st));
+        CUDA_TRY(cudaStreamSynchronize(s->st));
+        out[2] = h[4];
+    }
+    return 0;
+}
+
+int mpic_get_owner(mpic_sim* s, int* owner) {
+    REQUIRE(s && owner, MPIC_EINVAL, "bad argument");
+    memcpy(owner, s->owner.data(), s->owner.size() * sizeof(int));
+    return 0;
+}
+int mpic_migrate_tile(mpic_sim* s, int gid, int dest) {
+    REQUIRE(s && gid >= 0 && gid < (int)s->owner.size() && dest >= 0, MPIC_EINVAL, "bad tile/rank");
+    s->owner[gid] = dest;     // on one device the fields and particles of the tile do not move
+    return 0;
+}
+
+}  // extern "C"

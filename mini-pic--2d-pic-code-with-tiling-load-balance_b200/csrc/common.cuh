@@ -1,0 +1,102 @@
+// common.cuh -- shared device/host definitions for libminipic_b200.so (sm_100a only).
+//
+// HBM layout (DESIGN.md "data layout"):
+//   fields   six FP64 planes Ex,Ey,Ez,Bx,By,Bz + three int64 fixed-point current accumulators Jx,Jy,Jz, each
+//            (nyl + 2g) rows x pitch values.  Interior cell (i,j) of the slab lives at row g+j, column X0+i with
+//            X0 = 16 values (128 B) so interior rows start on a 128-byte line; pitch is a multiple of 16 values.
+//            The guard ring (g=2 on every side) always holds the periodic image (x: local wrap; y: local wrap on one
+//            GPU, neighbour slab rows otherwise), i.e. exactly what the reference's tiles hold after an exchange phase
+//            (PIC_2D.cpp:200-248) -- so any tile-with-guards patch is a plain 2-D window of the planes.
+//   particles SoA x,y,ux,uy,uz,q (FP64) + tag (int32), kept sorted by key = local_tile*cells_per_tile + cell_in_tile;
+//            cell_start[key] (int32) gives each cell's first slot, so a tile's particles are one contiguous range.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda.h>
+#include <stdint.h>
+#include <stdio.h>
+#include "../../include/minipic_b200.h"
+
+#define MPIC_X0 16
+#define MPIC_JSCALE 4503599627370496.0               /* 2^52: fixed-point scale of the current accumulators */
+#define MPIC_INV_JSCALE (1.0 / 4503599627370496.0)
+
+struct FieldGeom {
+    int nx, nyl;          // interior cells of this slab
+    int g;                // guard
+    int pitch;            // values per row
+    int rows;             // nyl + 2g
+    int64_t plane;        // values per plane = rows*pitch
+    int ywrap;            // 1: y guards are the local periodic image (single slab)
+};
+
+struct PicConst {
+    int nx, ny;           // GLOBAL cells
+    int tnx, tny;         // tile interior
+    int gtc;              // global tile columns
+    int ltr;              // local tile rows
+    int cy0;              // first global cell row of this slab (row0*tny)
+    int nyl;              // local cell rows
+    int cpt;              // cells per tile
+    int ncells;           // local cells
+    double dx, dy, dt;
+    double inv_dx, inv_dy;
+    double box_x, box_y;
+    double h;             // 0.5*dt*qm
+    double cjx, cjy, cjz; // 1/(dy*dt), 1/(dx*dt), 1/(dx*dy)
+};
+
+struct Particles {
+    double *x, *y, *ux, *uy, *uz, *q;
+    int* tag;
+};
+
+void mpic_set_error(const char* fmt, ...);
+
+#define CUDA_TRY(expr)                                                                          \
+    do {                                                                                        \
+        cudaError_t _e = (expr);                                                                \
+        if (_e != cudaSuccess) {                                                                \
+            mpic_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e)); \
+            return _e == cudaErrorNoDevice || _e == cudaErrorInsufficientDriver ? MPIC_ENODEV : MPIC_ECUDA; \
+        }                                                                                       \
+    } while (0)
+
+static inline int ceil_div(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+
+// ---- kernel launchers implemented in yee.cu
+struct YeeCoef { double bx, by, ex, ey, dt; int fma; };   // bx = dt/(2dx) or dt/dx ; ex = dt/dx
+int launch_b_sweep(const FieldGeom& G, double* planes, const YeeCoef& c, cudaStream_t st);
+int launch_e_sweep(const FieldGeom& G, double* planes, int64_t* jacc, int with_j, const YeeCoef& c, cudaStream_t st);
+int launch_fused_step(const FieldGeom& G, const double* src, double* dst, int64_t* jacc, int with_j,
+                      const YeeCoef& c, int scheme, cudaStream_t st);
+int launch_wrap_guards(const FieldGeom& G, double* planes, int first_plane, int nplanes, int do_y, cudaStream_t st);
+int launch_fold_current(const FieldGeom& G, int64_t* jacc, int nplanes, int do_y, cudaStream_t st);
+int launch_planes_to_tiles(const FieldGeom& G, const double* planes, double* grid6, const int* lrow, const int* lcol,
+                           int ntiles, int tnx, int tny, cudaStream_t st);
+int launch_tiles_to_planes(const FieldGeom& G, double* planes, const double* grid6, const int* lrow, const int* lcol,
+                           int ntiles, int tnx, int tny, cudaStream_t st);
+int launch_tile_b_half(const double* E3, const double* Bo3, double* Bn3, int tnx, int tny, int g, double cx, double cy, cudaStream_t st);
+int launch_tile_e_full(double* E3, const double* B3, int tnx, int tny, int g, double cx, double cy, cudaStream_t st);
+int launch_strip_copy(const double* src6, double* dst6, int TX, int r0, int c0, int nr, int nc, int to_strip, cudaStream_t st);
+int launch_field_energy(const FieldGeom& G, const double* planes, double* out, cudaStream_t st);
+int launch_gauss_residual(const FieldGeom& G, const double* planes, const int64_t* rho, double mean_rho, double inv_dx,
+                          double inv_dy, double* out_max, cudaStream_t st);
+
+// ---- kernel launchers implemented in particles.cu
+struct PushArgs;
+int launch_push_deposit(const PicConst& P, const FieldGeom& G, const CUtensorMap* tmap, const double* planes,
+                        int64_t* jacc, Particles p, const int* cell_start, int* cell_count_new, int64_t* leave_count,
+                        int split, int nsm, cudaStream_t st);
+int launch_count_keys(const PicConst& P, Particles p, int64_t first, int64_t n, int* cell_count, int* key_out, cudaStream_t st);
+int launch_scan_cells(int* cell_count, int* cell_start, int n_entries, int* block_tmp, cudaStream_t st);
+int launch_scatter(const PicConst& P, Particles src, Particles dst, int64_t n, const int* cell_start, int* cursor, cudaStream_t st);
+int launch_tile_counts(const PicConst& P, const int* cell_start, int* counts, cudaStream_t st);
+int launch_particle_tiles(const PicConst& P, Particles p, int64_t n, int row0, int* gid, cudaStream_t st);
+int launch_kinetic(Particles p, int64_t n, double* out2, cudaStream_t st);
+int launch_deposit_rho(const PicConst& P, const FieldGeom& G, Particles p, int64_t n, int64_t* rho, cudaStream_t st);
+int launch_load_uniform(const PicConst& P, Particles p, int64_t first, int64_t nsel, int cy_lo, int64_t tag0, int ppc,
+                        double u_th, double d0, double d1, double d2, double two_stream, double qp, uint64_t seed,
+                        cudaStream_t st);
+size_t push_smem_bytes(int tnx, int tny);
+void push_box_dims(int tnx, int tny, int* pw, int* ph);
+int launch_sum_i64(const int64_t* a, int64_t n, double* out, cudaStream_t st);

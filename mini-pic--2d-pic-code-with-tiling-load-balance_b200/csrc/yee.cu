@@ -1,0 +1,320 @@
+// yee.cu -- Yee FDTD leapfrog on device-resident SoA planes + guard handling + reference tile layout converters.
+//
+// Replaces, for ALL local tiles at once: updateBhalf / updateEfull (Field_update.cpp:14-59), the Grid<->GridE/GridB
+// copies around them (PIC_2D.cpp:179-195,258-271,329-343) and the guard exchange phases B/D/F
+// (PIC_2D.cpp:200-248,276-319,348-396; packSendBuffer/updateGuardRegion, Auxiliar_functions.cpp:73-239), which on one
+// GPU collapse into writing each updated edge cell to its periodic image(s) from the same thread.
+//
+// Arithmetic contract: this file is compiled with -fmad=false, so every expression below is evaluated in exactly the
+// written order with one rounding per operation == the reference built without contraction.  fma_mode==1 uses explicit
+// fma() in the pattern a per-statement contracting compiler (the build that produced the shipped dumps) generates.
+// Roofline: HBM-bound; algorithmic bytes 72 B/cell per sweep (read 3+3 planes, write 3), 216 B per 3-sweep step.
+#include "common.cuh"
+
+namespace {
+
+__device__ __forceinline__ int64_t fidx(const FieldGeom& G, int i, int j) {
+    return (int64_t)(G.g + j) * G.pitch + (MPIC_X0 + i);
+}
+
+// store v at interior cell (i,j) and at every guard-ring image of it
+template <typename T>
+__device__ __forceinline__ void store_images(const FieldGeom& G, T* __restrict__ p, int i, int j, T v) {
+    const int64_t k = fidx(G, i, j);
+    p[k] = v;
+    const int g = G.g;
+    int xs = i < g ? G.nx : (i >= G.nx - g ? -G.nx : 0);
+    int ys = 0;
+    if (G.ywrap) ys = j < g ? G.nyl : (j >= G.nyl - g ? -G.nyl : 0);
+    // a cell can be both a left and right image source only if nx < 2g; rejected at create time
+    if (xs) p[k + xs] = v;
+    if (ys) {
+        p[k + (int64_t)ys * G.pitch] = v;
+        if (xs) p[k + (int64_t)ys * G.pitch + xs] = v;
+    }
+}
+
+template <int FMA>
+__global__ void __launch_bounds__(256) b_sweep_kernel(FieldGeom G, double* __restrict__ f, double cx, double cy) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    if (i >= G.nx || j >= G.nyl) return;
+    const double* ex = f;
+    const double* ey = f + G.plane;
+    const double* ez = f + 2 * G.plane;
+    double* bx = f + 3 * G.plane;
+    double* by = f + 4 * G.plane;
+    double* bz = f + 5 * G.plane;
+    const int64_t k = fidx(G, i, j), kx = k + 1, ky = k + G.pitch;
+    const double ez0 = ez[k];
+    const double dEz_y = ez[ky] - ez0, dEz_x = ez[kx] - ez0;
+    const double dEy_x = ey[kx] - ey[k], dEx_y = ex[ky] - ex[k];
+    double nbx, nby, nbz;
+    if (FMA) {
+        nbx = fma(-cy, dEz_y, bx[k]);
+        nby = fma(cx, dEz_x, by[k]);
+        nbz = fma(cy, dEx_y, fma(-cx, dEy_x, bz[k]));
+    } else {
+        nbx = bx[k] - cy * dEz_y;
+        nby = by[k] + cx * dEz_x;
+        nbz = bz[k] - cx * dEy_x + cy * dEx_y;
+    }
+    store_images(G, bx, i, j, nbx);
+    store_images(G, by, i, j, nby);
+    store_images(G, bz, i, j, nbz);
+}
+
+template <int FMA, int WITH_J>
+__global__ void __launch_bounds__(256) e_sweep_kernel(FieldGeom G, double* __restrict__ f, int64_t* __restrict__ jacc,
+                                                      double cx, double cy, double dt) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    if (i >= G.nx || j >= G.nyl) return;
+    double* ex = f;
+    double* ey = f + G.plane;
+    double* ez = f + 2 * G.plane;
+    const double* bx = f + 3 * G.plane;
+    const double* by = f + 4 * G.plane;
+    const double* bz = f + 5 * G.plane;
+    const int64_t k = fidx(G, i, j), kx = k - 1, ky = k - G.pitch;
+    const double bz0 = bz[k];
+    const double dBz_y = bz0 - bz[ky], dBz_x = bz0 - bz[kx];
+    const double dBy_x = by[k] - by[kx], dBx_y = bx[k] - bx[ky];
+    double nex, ney, nez;
+    if (FMA) {
+        nex = fma(cy, dBz_y, ex[k]);
+        ney = fma(-cx, dBz_x, ey[k]);
+        nez = ez[k] + fma(cx, dBy_x, -(cy * dBx_y));
+    } else {
+        nex = ex[k] + cy * dBz_y;
+        ney = ey[k] - cx * dBz_x;
+        nez = ez[k] + (cx * dBy_x - cy * dBx_y);
+    }
+    if (WITH_J) {   // E <- E - dt*J, J = acc*2^-52; the accumulators are consumed (zeroed) here
+        int64_t* jx = jacc;
+        int64_t* jy = jacc + G.plane;
+        int64_t* jz = jacc + 2 * G.plane;
+        nex = fma(-dt, __ll2double_rn(jx[k]) * MPIC_INV_JSCALE, nex);
+        ney = fma(-dt, __ll2double_rn(jy[k]) * MPIC_INV_JSCALE, ney);
+        nez = fma(-dt, __ll2double_rn(jz[k]) * MPIC_INV_JSCALE, nez);
+        jx[k] = 0; jy[k] = 0; jz[k] = 0;
+    }
+    store_images(G, ex, i, j, nex);
+    store_images(G, ey, i, j, ney);
+    store_images(G, ez, i, j, nez);
+}
+
+// ---- guard ring rebuild for `nplanes` planes starting at `first` (after uploads / halo receives)
+__global__ void wrap_y_kernel(FieldGeom G, double* __restrict__ f, int first, int nplanes) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;             // interior column
+    const int r = blockIdx.y;                                        // 0..2g-1: which guard row
+    if (i >= G.nx) return;
+    const int g = G.g;
+    const int dst = r < g ? r : G.nyl + r;                           // rows [0,g) and [g+nyl, g+nyl+g)
+    const int src = r < g ? G.nyl + r : r;                           // rows [nyl, nyl+g) resp. [g, 2g)
+    for (int p = first; p < first + nplanes; p++) {
+        double* a = f + (int64_t)p * G.plane;
+        a[(int64_t)dst * G.pitch + MPIC_X0 + i] = a[(int64_t)src * G.pitch + MPIC_X0 + i];
+    }
+}
+__global__ void wrap_x_kernel(FieldGeom G, double* __restrict__ f, int first, int nplanes) {
+    const int row = blockIdx.x * blockDim.x + threadIdx.x;           // all rows incl. y guards
+    if (row >= G.rows) return;
+    const int g = G.g;
+    for (int p = first; p < first + nplanes; p++) {
+        double* a = f + (int64_t)p * G.plane + (int64_t)row * G.pitch + MPIC_X0;
+        for (int c = 0; c < g; c++) {
+            a[-g + c] = a[G.nx - g + c];
+            a[G.nx + c] = a[c];
+        }
+    }
+}
+
+// ---- current accumulators: fold the guard ring into the interior (add), zero the ring.  SURVEY.md B.6.
+__global__ void fold_y_kernel(FieldGeom G, int64_t* __restrict__ jacc, int nplanes) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;             // every column incl. x guards
+    const int r = blockIdx.y;                                        // guard row 0..2g-1
+    if (c >= G.nx + 2 * G.g) return;
+    const int g = G.g, col = MPIC_X0 - g + c;
+    const int src = r < g ? r : G.nyl + r;
+    const int dst = r < g ? G.nyl + r : r;
+    for (int p = 0; p < nplanes; p++) {
+        int64_t* a = jacc + (int64_t)p * G.plane;
+        int64_t v = a[(int64_t)src * G.pitch + col];
+        if (v) { a[(int64_t)dst * G.pitch + col] += v; a[(int64_t)src * G.pitch + col] = 0; }
+    }
+}
+__global__ void fold_x_kernel(FieldGeom G, int64_t* __restrict__ jacc, int nplanes) {
+    const int row = blockIdx.x * blockDim.x + threadIdx.x;           // all rows (y guards are zero after fold_y / halo)
+    if (row >= G.rows) return;
+    const int g = G.g;
+    for (int p = 0; p < nplanes; p++) {
+        int64_t* a = jacc + (int64_t)p * G.plane + (int64_t)row * G.pitch + MPIC_X0;
+        for (int c = 0; c < g; c++) {
+            int64_t lo = a[-g + c], hi = a[G.nx + c];
+            if (lo) { a[G.nx - g + c] += lo; a[-g + c] = 0; }
+            if (hi) { a[c] += hi; a[G.nx + c] = 0; }
+        }
+    }
+}
+
+// ---- reference tile layout <-> planes.  One block per (tile, row of the patch).
+template <int TO_TILES>
+__global__ void tiles_kernel(FieldGeom G, double* __restrict__ f, double* __restrict__ grid6,
+                             const int* __restrict__ lrow, const int* __restrict__ lcol, int tnx, int tny) {
+    const int t = blockIdx.y, jj = blockIdx.x;                       // jj: patch row 0..TY-1
+    const int g = G.g, TX = tnx + 2 * g, TY = tny + 2 * g;
+    const int j = lrow[t] * tny + jj - g;                            // slab cell row (may be in the guard ring)
+    const int i0 = lcol[t] * tnx - g;
+    double* out = grid6 + ((int64_t)t * TY + jj) * TX * 6;
+    for (int e = threadIdx.x; e < TX * 6; e += blockDim.x) {
+        const int ii = e / 6, c = e % 6;
+        const int64_t k = (int64_t)c * G.plane + (int64_t)(g + j) * G.pitch + MPIC_X0 + i0 + ii;
+        if (TO_TILES) out[e] = f[k];
+        else if (ii >= g && ii < TX - g && jj >= g && jj < TY - g) f[k] = out[e];
+    }
+}
+
+// ---- L0 compat: one tile, AoS triplets (Field_update.h:36,54)
+__global__ void tile_b_half_kernel(const double* __restrict__ E, const double* __restrict__ Bo, double* __restrict__ Bn,
+                                   int tnx, int tny, int g, double cx, double cy) {
+    const int i = g + blockIdx.x * blockDim.x + threadIdx.x, j = g + blockIdx.y * blockDim.y + threadIdx.y;
+    const int TX = tnx + 2 * g;
+    if (i >= tnx + g || j >= tny + g) return;
+    const int64_t k = 3 * ((int64_t)j * TX + i), kx = k + 3, ky = k + 3 * (int64_t)TX;
+    Bn[k] = Bo[k] - cy * (E[ky + 2] - E[k + 2]);
+    Bn[k + 1] = Bo[k + 1] + cx * (E[kx + 2] - E[k + 2]);
+    Bn[k + 2] = Bo[k + 2] - cx * (E[kx + 1] - E[k + 1]) + cy * (E[ky] - E[k]);
+}
+__global__ void tile_e_full_kernel(double* __restrict__ E, const double* __restrict__ B, int tnx, int tny, int g,
+                                   double cx, double cy) {
+    const int i = g + blockIdx.x * blockDim.x + threadIdx.x, j = g + blockIdx.y * blockDim.y + threadIdx.y;
+    const int TX = tnx + 2 * g;
+    if (i >= tnx + g || j >= tny + g) return;
+    const int64_t k = 3 * ((int64_t)j * TX + i), kx = k - 3, ky = k - 3 * (int64_t)TX;
+    E[k] = E[k] + cy * (B[k + 2] - B[ky + 2]);
+    E[k + 1] = E[k + 1] - cx * (B[k + 2] - B[kx + 2]);
+    E[k + 2] = E[k + 2] + (cx * (B[k + 1] - B[kx + 1]) - cy * (B[k] - B[ky]));
+}
+// strip <-> tile copy for packSendBuffer / updateGuardRegion (Auxiliar_functions.cpp:73-239)
+__global__ void strip_kernel(const double* __restrict__ src, double* __restrict__ dst, int TX, int r0, int c0, int nr,
+                             int nc, int to_strip) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= nr * nc * 6) return;
+    const int cell = e / 6, c = e % 6, r = cell / nc, cc = cell % nc;
+    const int64_t kt = ((int64_t)(r0 + r) * TX + c0 + cc) * 6 + c;
+    if (to_strip) dst[e] = src[kt]; else dst[kt] = src[e];
+}
+
+// ---- diagnostics
+__global__ void field_energy_kernel(FieldGeom G, const double* __restrict__ f, double* __restrict__ out) {
+    __shared__ double sh[256];
+    double s = 0.0;
+    const int64_t n = (int64_t)G.nx * G.nyl;
+    for (int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; c < n; c += (int64_t)gridDim.x * blockDim.x) {
+        const int i = (int)(c % G.nx), j = (int)(c / G.nx);
+        const int64_t k = (int64_t)(G.g + j) * G.pitch + MPIC_X0 + i;
+        for (int p = 0; p < 6; p++) { double v = f[p * G.plane + k]; s += v * v; }
+    }
+    sh[threadIdx.x] = s;
+    __syncthreads();
+    for (int w = 128; w > 0; w >>= 1) { if (threadIdx.x < w) sh[threadIdx.x] += sh[threadIdx.x + w]; __syncthreads(); }
+    if (threadIdx.x == 0) atomicAdd(out, sh[0]);
+}
+__global__ void gauss_kernel(FieldGeom G, const double* __restrict__ f, const int64_t* __restrict__ rho, double mean_rho,
+                             double inv_dx, double inv_dy, double* __restrict__ out_max) {
+    __shared__ double sh[256];
+    double m = 0.0;
+    const int64_t n = (int64_t)G.nx * G.nyl;
+    const double* ex = f;
+    const double* ey = f + G.plane;
+    for (int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; c < n; c += (int64_t)gridDim.x * blockDim.x) {
+        const int i = (int)(c % G.nx), j = (int)(c / G.nx);
+        const int64_t k = (int64_t)(G.g + j) * G.pitch + MPIC_X0 + i;
+        double div = (ex[k] - ex[k - 1]) * inv_dx + (ey[k] - ey[k - G.pitch]) * inv_dy;
+        double r = fabs(div - (__ll2double_rn(rho[k]) * MPIC_INV_JSCALE - mean_rho));
+        m = fmax(m, r);
+    }
+    sh[threadIdx.x] = m;
+    __syncthreads();
+    for (int w = 128; w > 0; w >>= 1) { if (threadIdx.x < w) sh[threadIdx.x] = fmax(sh[threadIdx.x], sh[threadIdx.x + w]); __syncthreads(); }
+    if (threadIdx.x == 0) atomicMax((unsigned long long*)out_max, (unsigned long long)__double_as_longlong(sh[0]));   // non-negative doubles order like uint64
+}
+
+}  // namespace
+
+#define LAUNCH_CHECK() do { cudaError_t _e = cudaGetLastError(); if (_e != cudaSuccess) { mpic_set_error("%s:%d: launch failed: %s", __FILE__, __LINE__, cudaGetErrorString(_e)); return MPIC_ECUDA; } } while (0)
+
+int launch_b_sweep(const FieldGeom& G, double* planes, const YeeCoef& c, cudaStream_t st) {
+    dim3 b(64, 4), g(ceil_div(G.nx, 64), ceil_div(G.nyl, 4));
+    if (c.fma) b_sweep_kernel<1><<<g, b, 0, st>>>(G, planes, c.bx, c.by);
+    else b_sweep_kernel<0><<<g, b, 0, st>>>(G, planes, c.bx, c.by);
+    LAUNCH_CHECK();
+    return 0;
+}
+int launch_e_sweep(const FieldGeom& G, double* planes, int64_t* jacc, int with_j, const YeeCoef& c, cudaStream_t st) {
+    dim3 b(64, 4), g(ceil_div(G.nx, 64), ceil_div(G.nyl, 4));
+    if (c.fma) {
+        if (with_j) e_sweep_kernel<1, 1><<<g, b, 0, st>>>(G, planes, jacc, c.ex, c.ey, c.dt);
+        else e_sweep_kernel<1, 0><<<g, b, 0, st>>>(G, planes, jacc, c.ex, c.ey, c.dt);
+    } else {
+        if (with_j) e_sweep_kernel<0, 1><<<g, b, 0, st>>>(G, planes, jacc, c.ex, c.ey, c.dt);
+        else e_sweep_kernel<0, 0><<<g, b, 0, st>>>(G, planes, jacc, c.ex, c.ey, c.dt);
+    }
+    LAUNCH_CHECK();
+    return 0;
+}
+int launch_wrap_guards(const FieldGeom& G, double* planes, int first, int nplanes, int do_y, cudaStream_t st) {
+    if (do_y) { wrap_y_kernel<<<dim3(ceil_div(G.nx, 256), 2 * G.g), 256, 0, st>>>(G, planes, first, nplanes); LAUNCH_CHECK(); }
+    wrap_x_kernel<<<ceil_div(G.rows, 128), 128, 0, st>>>(G, planes, first, nplanes);
+    LAUNCH_CHECK();
+    return 0;
+}
+int launch_fold_current(const FieldGeom& G, int64_t* jacc, int nplanes, int do_y, cudaStream_t st) {
+    if (do_y) { fold_y_kernel<<<dim3(ceil_div(G.nx + 2 * G.g, 256), 2 * G.g), 256, 0, st>>>(G, jacc, nplanes); LAUNCH_CHECK(); }
+    fold_x_kernel<<<ceil_div(G.rows, 128), 128, 0, st>>>(G, jacc, nplanes);
+    LAUNCH_CHECK();
+    return 0;
+}
+int launch_planes_to_tiles(const FieldGeom& G, const double* planes, double* grid6, const int* lrow, const int* lcol,
+                           int ntiles, int tnx, int tny, cudaStream_t st) {
+    if (ntiles == 0) return 0;
+    tiles_kernel<1><<<dim3(tny + 2 * G.g, ntiles), 128, 0, st>>>(G, const_cast<double*>(planes), grid6, lrow, lcol, tnx, tny);
+    LAUNCH_CHECK();
+    return 0;
+}
+int launch_tiles_to_planes(const FieldGeom& G, double* planes, const double* grid6, const int* lrow, const int* lcol,
+                           int ntiles, int tnx, int tny, cudaStream_t st) {
+    if (ntiles == 0) return 0;
+    tiles_kernel<0><<<dim3(tny + 2 * G.g, ntiles), 128, 0, st>>>(G, planes, const_cast<double*>(grid6), lrow, lcol, tnx, tny);
+    LAUNCH_CHECK();
+    return 0;
+}
+int launch_tile_b_half(const double* E3, const double* Bo3, double* Bn3, int tnx, int tny, int g, double cx, double cy, cudaStream_t st) {
+    dim3 b(32, 8), gr(ceil_div(tnx, 32), ceil_div(tny, 8));
+    tile_b_half_kernel<<<gr, b, 0, st>>>(E3, Bo3, Bn3, tnx, tny, g, cx, cy);
+    LAUNCH_CHECK();
+    return 0;
+}
+int launch_tile_e_full(double* E3, const double* B3, int tnx, int tny, int g, double cx, double cy, cudaStream_t st) {
+    dim3 b(32, 8), gr(ceil_div(tnx, 32), ceil_div(tny, 8));
+    tile_e_full_kernel<<<gr, b, 0, st>>>(E3, B3, tnx, tny, g, cx, cy);
+    LAUNCH_CHECK();
+    return 0;
+}
+int launch_strip_copy(const double* src6, double* dst6, int TX, int r0, int c0, int nr, int nc, int to_strip, cudaStream_t st) {
+    strip_kernel<<<ceil_div((int64_t)nr * nc * 6, 256), 256, 0, st>>>(src6, dst6, TX, r0, c0, nr, nc, to_strip);
+    LAUNCH_CHECK();
+    return 0;
+}
+int launch_field_energy(const FieldGeom& G, const double* planes, double* out, cudaStream_t st) {
+    field_energy_kernel<<<296, 256, 0, st>>>(G, planes, out);
+    LAUNCH_CHECK();
+    return 0;
+}
+int launch_gauss_residual(const FieldGeom& G, const double* planes, const int64_t* rho, double mean_rho, double inv_dx,
+                          double inv_dy, double* out_max, cudaStream_t st) {
+    gauss_kernel<<<296, 256, 0, st>>>(G, planes, rho, mean_rho, inv_dx, inv_dy, out_max);
+    LAUNCH_CHECK();
+    return 0;
+}
