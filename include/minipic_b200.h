@@ -31,7 +31,7 @@ extern "C" {
 const char* mpic_last_error(void);
 int mpic_device_count(void);
 /* ABI version; bumped whenever a signature or struct below changes. */
-int mpic_abi_version(void);
+int mpic_abi_version(void);   /* currently 2 */
 
 /* ============================================================ integer helpers (host, exact)
  * Replace Auxiliar_functions.h:55-65 (findBestGrid, findBestTileGrid, tileGlobalRow/Col, getGlobalID, getGlobalRowCol,
@@ -108,19 +108,37 @@ int mpic_field_steps(mpic_sim* s, int nsteps);
 /* Same result (bit-identical) from one fused kernel per step (overlapped-tile B/2,E,B/2; 96 B/cell instead of 216). */
 int mpic_field_steps_fused(mpic_sim* s, int nsteps);
 
-/* ---- slab halos (nranks > 1).  The library exposes device pointers to contiguous row blocks so that the host can
- * move them with NCCL/torch.distributed or peer copies; which==0: E planes, 1: B planes, 2: J accumulators (int64).
- * send_lo/send_hi: first/last `guard` interior rows (to the lower/upper neighbour); recv_lo/recv_hi: guard rows.
- * Each block is 3 planes x guard rows x pitch values; plane p of a block starts at ptr + p*plane_stride. */
+/* ---- slab halos (nranks > 1): replace the inter-rank part of the exchange phases B/D/F (PIC_2D.cpp:200-248,276-319,
+ * 348-396; MPI_Isend/Irecv of packSendBuffer strips) for a 1-D slab decomposition over tile rows.
+ * which==0: E planes, 1: B planes, 2: current accumulators (int64; ADDED into the neighbour).
+ * The library packs the edge rows into contiguous device staging buffers; the host moves send[d] to the neighbour's
+ * recv[1-d] with any transport (NCCL send/recv through torch.distributed in slab.py, peer copies, MPI), then unpacks.
+ * Side 0 = lower neighbour (rank-1, periodic), side 1 = upper neighbour (rank+1).  One staging set is shared by all three
+ * `which`: finish one exchange (pack, transfer, unpack) before packing the next.  The which==2 message also carries,
+ * in its 128-byte header, the number of particles that left towards that side in the last push. */
 typedef struct mpic_halo_desc {
-    void* send_lo; void* send_hi; void* recv_lo; void* recv_hi;
-    int64_t row_values;      /* values (8 bytes each) per row = pitch */
-    int64_t plane_stride;    /* values between consecutive planes */
-    int rows;                /* = guard */
+    void* send[2]; void* recv[2];   /* device pointers, each `bytes` long */
+    int64_t bytes;                  /* bytes per message */
 } mpic_halo_desc;
-int mpic_halo_describe(mpic_sim* s, int which, mpic_halo_desc* out);
-/* after recv: rebuild x guards of the received rows (fields) or fold received J rows into the interior (which==2) */
-int mpic_halo_finish(mpic_sim* s, int which);
+int mpic_halo_describe(mpic_sim* s, mpic_halo_desc* out);
+int mpic_halo_pack(mpic_sim* s, int which);
+/* fields: received rows -> guard rows.  current: received rows added into the interior edge rows, own guard rows
+ * zeroed, then the x guards are folded (i.e. completes mpic_fold_current for a slab). */
+int mpic_halo_unpack(mpic_sim* s, int which);
+
+/* ---- particle migration between slabs (no reference counterpart; the reference's tile migration drops particles,
+ * Auxiliar_functions.cpp:244-246).  mpic_push_deposit appends every particle that left the slab to send[0] (down) or
+ * send[1] (up) as a 56-byte record {x,y,ux,uy,uz,q,tag}.  Protocol per step: push_deposit; halo exchange which==2;
+ * field phases; mpic_migration_counts (one stream sync: own leaver counts + the neighbours', which arrived in the
+ * which==2 header); transfer leave[d] records send[d] -> neighbour's recv[1-d]; mpic_migration_absorb; mpic_sort_tiles. */
+typedef struct mpic_migr_desc {
+    void* send[2]; void* recv[2];   /* device pointers to record arrays */
+    int64_t cap;                    /* records per buffer */
+    int64_t record_bytes;           /* 56 */
+} mpic_migr_desc;
+int mpic_migration_describe(mpic_sim* s, mpic_migr_desc* out);
+int mpic_migration_counts(mpic_sim* s, int leave[2], int arrive[2]);
+int mpic_migration_absorb(mpic_sim* s, int n_from_lo, int n_from_hi);
 
 /* ---- particles (struct Particle, Auxiliar_functions.h:16-21, as SoA: x,y,px,py,pz,q doubles and int tag).
  * Upload accepts any order; the device sorts by (tile gid, cell) before the first push. */

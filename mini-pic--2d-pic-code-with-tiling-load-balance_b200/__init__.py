@@ -30,8 +30,11 @@ class Params(C.Structure):
 
 
 class HaloDesc(C.Structure):
-    _fields_ = [("send_lo", C.c_void_p), ("send_hi", C.c_void_p), ("recv_lo", C.c_void_p), ("recv_hi", C.c_void_p),
-                ("row_values", C.c_int64), ("plane_stride", C.c_int64), ("rows", C.c_int)]
+    _fields_ = [("send", C.c_void_p * 2), ("recv", C.c_void_p * 2), ("bytes", C.c_int64)]
+
+
+class MigrDesc(C.Structure):
+    _fields_ = [("send", C.c_void_p * 2), ("recv", C.c_void_p * 2), ("cap", C.c_int64), ("record_bytes", C.c_int64)]
 
 
 _lib = None
@@ -57,13 +60,16 @@ def lib():
     for name in ("mpic_destroy", "mpic_sync", "mpic_step_b_half", "mpic_step_e_full", "mpic_push_deposit",
                  "mpic_sort_tiles", "mpic_fold_current"):
         getattr(L, name).argtypes = [C.c_void_p]
-    for name in ("mpic_field_steps", "mpic_field_steps_fused", "mpic_pic_steps", "mpic_halo_finish"):
+    for name in ("mpic_field_steps", "mpic_field_steps_fused", "mpic_pic_steps", "mpic_halo_pack", "mpic_halo_unpack"):
         getattr(L, name).argtypes = [C.c_void_p, C.c_int]
+    L.mpic_migration_describe.argtypes = [C.c_void_p, C.POINTER(MigrDesc)]
+    L.mpic_migration_counts.argtypes = [C.c_void_p, c_ip, c_ip]
+    L.mpic_migration_absorb.argtypes = [C.c_void_p, C.c_int, C.c_int]
     L.mpic_upload_planes.argtypes = [C.c_void_p, C.POINTER(c_dp)]
     L.mpic_download_planes.argtypes = [C.c_void_p, C.POINTER(c_dp)]
     L.mpic_upload_tiles.argtypes = [C.c_void_p, c_dp, c_ip, C.c_int]
     L.mpic_download_tiles.argtypes = [C.c_void_p, c_dp, c_ip, C.c_int]
-    L.mpic_halo_describe.argtypes = [C.c_void_p, C.c_int, C.POINTER(HaloDesc)]
+    L.mpic_halo_describe.argtypes = [C.c_void_p, C.POINTER(HaloDesc)]
     L.mpic_upload_particles.argtypes = [C.c_void_p, C.c_int64] + [c_dp] * 6 + [c_ip]
     L.mpic_download_particles.argtypes = [C.c_void_p, C.c_int64] + [c_dp] * 6 + [c_ip, c_lp]
     L.mpic_load_uniform.argtypes = [C.c_void_p, C.c_int] + [C.c_double] * 8 + [C.c_uint64, C.c_int]
@@ -109,6 +115,18 @@ def courant_dt(dx, dy, factor=0.5):
 
 
 PART_KEYS = ("x", "y", "ux", "uy", "uz", "q")
+
+
+class _DevMem:
+    """__cuda_array_interface__ carrier so torch can wrap library-owned device memory without a copy."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
+
+
+def device_bytes(ptr, nbytes, device):
+    import torch
+    return torch.as_tensor(_DevMem(ptr, nbytes), device=f"cuda:{device}")
 
 
 class Sim:
@@ -174,13 +192,40 @@ class Sim:
     def field_steps(self, n, fused=False):
         _chk((lib().mpic_field_steps_fused if fused else lib().mpic_field_steps)(self.h, n))
 
-    def halo_describe(self, which):
+    # ---- slab plumbing (nranks > 1); the torch tensors are zero-copy views of the library's device staging buffers
+    def halo_tensors(self):
+        """{"send": [to_lower, to_upper], "recv": [from_lower, from_upper]} as uint8 CUDA tensors."""
         d = HaloDesc()
-        _chk(lib().mpic_halo_describe(self.h, which, C.byref(d)))
-        return d
+        _chk(lib().mpic_halo_describe(self.h, C.byref(d)))
+        dev = self.p.device
+        return {"send": [device_bytes(d.send[k], d.bytes, dev) for k in range(2)],
+                "recv": [device_bytes(d.recv[k], d.bytes, dev) for k in range(2)]}
 
-    def halo_finish(self, which):
-        _chk(lib().mpic_halo_finish(self.h, which))
+    def halo_pack(self, which):
+        _chk(lib().mpic_halo_pack(self.h, which))
+
+    def halo_unpack(self, which):
+        _chk(lib().mpic_halo_unpack(self.h, which))
+
+    def migration_tensors(self):
+        d = MigrDesc()
+        _chk(lib().mpic_migration_describe(self.h, C.byref(d)))
+        dev, nb = self.p.device, d.cap * d.record_bytes
+        return {"send": [device_bytes(d.send[k], nb, dev) for k in range(2)],
+                "recv": [device_bytes(d.recv[k], nb, dev) for k in range(2)], "record_bytes": int(d.record_bytes)}
+
+    def migration_counts(self):
+        """(leave[2], arrive[2]) of the last push; one stream sync."""
+        lv, ar = (C.c_int * 2)(), (C.c_int * 2)()
+        _chk(lib().mpic_migration_counts(self.h, lv, ar))
+        return [lv[0], lv[1]], [ar[0], ar[1]]
+
+    def migration_absorb(self, n_from_lo, n_from_hi):
+        _chk(lib().mpic_migration_absorb(self.h, n_from_lo, n_from_hi))
+
+    def torch_stream(self):
+        import torch
+        return torch.cuda.ExternalStream(self.stream, device=self.p.device)
 
     # ---- particles
     def upload_particles(self, parts):

@@ -38,16 +38,25 @@ struct mpic_sim {
     int push_split = 4;
     int nsm = 148;
     bool counts_valid = false;     // cell_count holds the destination-cell histogram of the last push
+    // ---- slab plumbing (nranks > 1)
+    double* halo_send = nullptr;   // [2 sides][HALO_HDR + 3*g*pitch] values
+    double* halo_recv = nullptr;
+    int64_t halo_side = 0;         // values per side
+    LeaveBufs lv = {};             // leaver records written by the push kernel
+    double* arrive[2] = {};        // records received from the lower / upper neighbour
+    int64_t arrived = 0;           // records absorbed into the tail [n, n+arrived) and not yet sorted in
+    int64_t left = -1;             // leavers of the last push (host copy; -1: unknown)
     std::vector<int> owner;        // global tiles
 };
 
+#define HALO_HDR 16                /* values (128 B) of header in front of each halo message; [0] = leaver count to that side */
 #define REQUIRE(cond, code, ...) do { if (!(cond)) { mpic_set_error(__VA_ARGS__); return code; } } while (0)
 #define TRY(expr) do { int _r = (expr); if (_r) return _r; } while (0)
 
 extern "C" {
 
 const char* mpic_last_error(void) { return g_err; }
-int mpic_abi_version(void) { return 1; }
+int mpic_abi_version(void) { return 2; }
 int mpic_device_count(void) {
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
@@ -244,6 +253,25 @@ int mpic_create(const mpic_params* p, mpic_sim** out) {
         s->push_split = 1;
         while (ntiles * s->push_split < 8 * s->nsm && s->push_split < 64) s->push_split *= 2;
     }
+    if (p->nranks > 1) {
+        s->halo_side = HALO_HDR + (int64_t)3 * G.g * G.pitch;
+        CUDA_TRY(cudaMalloc(&s->halo_send, (size_t)2 * s->halo_side * 8));
+        CUDA_TRY(cudaMalloc(&s->halo_recv, (size_t)2 * s->halo_side * 8));
+        CUDA_TRY(cudaMemsetAsync(s->halo_send, 0, (size_t)2 * s->halo_side * 8, s->st));
+        CUDA_TRY(cudaMemsetAsync(s->halo_recv, 0, (size_t)2 * s->halo_side * 8, s->st));
+        if (s->cap > 0) {
+            int64_t lc = 4 * (s->cap / G.nyl + 1);
+            if (lc < 4096) lc = 4096;
+            if (lc > s->cap) lc = s->cap;
+            s->lv.cap = (int)lc;
+            for (int d = 0; d < 2; d++) {
+                CUDA_TRY(cudaMalloc(&s->lv.rec[d], (size_t)lc * MPIC_REC_DOUBLES * 8));
+                CUDA_TRY(cudaMalloc(&s->arrive[d], (size_t)lc * MPIC_REC_DOUBLES * 8));
+            }
+        }
+    }
+    CUDA_TRY(cudaMalloc(&s->lv.count, 2 * sizeof(int)));
+    CUDA_TRY(cudaMemsetAsync(s->lv.count, 0, 2 * sizeof(int), s->st));
     s->owner.resize((size_t)gtr * gtc);
     for (int r = 0; r < gtr; r++) {
         int owner_rank = 0;
@@ -263,6 +291,8 @@ int mpic_destroy(mpic_sim* s) {
     cudaFree(s->planes); cudaFree(s->jacc); cudaFree(s->rho); cudaFree(s->d_scratch);
     for (int k = 0; k < 2; k++) { cudaFree(s->pa[k].x); cudaFree(s->pa[k].tag); }
     cudaFree(s->cell_start); cudaFree(s->cell_count); cudaFree(s->scan_tmp);
+    cudaFree(s->halo_send); cudaFree(s->halo_recv); cudaFree(s->lv.count);
+    for (int d = 0; d < 2; d++) { cudaFree(s->lv.rec[d]); cudaFree(s->arrive[d]); }
     if (s->st) cudaStreamDestroy(s->st);
     delete s;
     return 0;
@@ -369,27 +399,72 @@ int mpic_field_steps(mpic_sim* s, int nsteps) {
 int mpic_field_steps_fused(mpic_sim* s, int nsteps) { return mpic_field_steps(s, nsteps); }   // fused kernel: see round notes
 
 // ------------------------------------------------------------------------------------------ halos
-int mpic_halo_describe(mpic_sim* s, int which, mpic_halo_desc* out) {
-    REQUIRE(s && out && which >= 0 && which <= 2, MPIC_EINVAL, "bad argument");
-    const FieldGeom& G = s->G;
-    char* base = which == 2 ? (char*)s->jacc : (char*)(s->planes + (which == 1 ? 3 * G.plane : 0));
-    const int64_t row = (int64_t)G.pitch * 8;
-    out->rows = G.g; out->row_values = G.pitch; out->plane_stride = G.plane;
-    if (which < 2) {   // fields: send interior edge rows, receive into guard rows
-        out->send_lo = base + (int64_t)G.g * row;
-        out->send_hi = base + (int64_t)G.nyl * row;
-        out->recv_lo = base;
-        out->recv_hi = base + (int64_t)(G.g + G.nyl) * row;
-    } else {           // current: send guard rows (deposits that belong to the neighbour), receive into scratch == same rows after send
-        out->send_lo = base;
-        out->send_hi = base + (int64_t)(G.g + G.nyl) * row;
-        out->recv_lo = nullptr; out->recv_hi = nullptr;
-    }
+static double* halo_base(mpic_sim* s, int which) {
+    return which == 2 ? (double*)s->jacc : s->planes + (which == 1 ? 3 * s->G.plane : 0);
+}
+int mpic_halo_describe(mpic_sim* s, mpic_halo_desc* out) {
+    REQUIRE(s && out, MPIC_EINVAL, "bad argument");
+    REQUIRE(s->halo_send, MPIC_ESTATE, "halos exist only for nranks > 1");
+    for (int d = 0; d < 2; d++) { out->send[d] = s->halo_send + d * s->halo_side; out->recv[d] = s->halo_recv + d * s->halo_side; }
+    out->bytes = s->halo_side * 8;
     return 0;
 }
-int mpic_halo_finish(mpic_sim* s, int which) {
+__global__ void halo_header_kernel(double* send, int64_t side_stride, const int* leave_count) {
+    if (threadIdx.x < 2) ((long long*)(send + threadIdx.x * side_stride))[0] = leave_count[threadIdx.x];
+}
+int mpic_halo_pack(mpic_sim* s, int which) {
     REQUIRE(s && which >= 0 && which <= 2, MPIC_EINVAL, "bad argument");
-    if (which < 2) { TRY(launch_wrap_guards(s->G, s->planes, which * 3, 3, 0, s->st)); s->launches++; }
+    REQUIRE(s->halo_send, MPIC_ESTATE, "halos exist only for nranks > 1");
+    TRY(launch_halo_pack(s->G, halo_base(s, which), which == 2, s->halo_send + HALO_HDR, s->halo_side, s->st));
+    s->launches++;
+    if (which == 2) { halo_header_kernel<<<1, 32, 0, s->st>>>(s->halo_send, s->halo_side, s->lv.count); s->launches++; }
+    return 0;
+}
+int mpic_halo_unpack(mpic_sim* s, int which) {
+    REQUIRE(s && which >= 0 && which <= 2, MPIC_EINVAL, "bad argument");
+    REQUIRE(s->halo_recv, MPIC_ESTATE, "halos exist only for nranks > 1");
+    TRY(launch_halo_unpack(s->G, halo_base(s, which), which == 2, s->halo_recv + HALO_HDR, s->halo_side, s->st));
+    s->launches++;
+    if (which == 2) { TRY(launch_fold_current(s->G, s->jacc, 3, 0, s->st)); s->launches++; }
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------ particle migration between slabs
+int mpic_migration_describe(mpic_sim* s, mpic_migr_desc* out) {
+    REQUIRE(s && out, MPIC_EINVAL, "bad argument");
+    REQUIRE(s->lv.rec[0], MPIC_ESTATE, "migration buffers exist only for nranks > 1 with particle storage");
+    for (int d = 0; d < 2; d++) { out->send[d] = s->lv.rec[d]; out->recv[d] = s->arrive[d]; }
+    out->cap = s->lv.cap; out->record_bytes = MPIC_REC_DOUBLES * 8;
+    return 0;
+}
+int mpic_migration_counts(mpic_sim* s, int leave[2], int arrive[2]) {
+    REQUIRE(s && leave && arrive, MPIC_EINVAL, "bad argument");
+    REQUIRE(s->lv.rec[0], MPIC_ESTATE, "migration buffers exist only for nranks > 1 with particle storage");
+    long long hdr[2];
+    CUDA_TRY(cudaMemcpyAsync(leave, s->lv.count, 2 * sizeof(int), cudaMemcpyDeviceToHost, s->st));
+    // the neighbours' leaver counts travelled in the header of the current (which=2) halo message
+    CUDA_TRY(cudaMemcpyAsync(&hdr[0], s->halo_recv, 8, cudaMemcpyDeviceToHost, s->st));
+    CUDA_TRY(cudaMemcpyAsync(&hdr[1], s->halo_recv + s->halo_side, 8, cudaMemcpyDeviceToHost, s->st));
+    CUDA_TRY(cudaStreamSynchronize(s->st));
+    arrive[0] = (int)hdr[0]; arrive[1] = (int)hdr[1];
+    for (int d = 0; d < 2; d++) {
+        REQUIRE(leave[d] <= s->lv.cap && arrive[d] <= s->lv.cap, MPIC_ENOMEM, "migration buffer overflow: %d leavers / %d arrivals > capacity %d",
+                leave[d], arrive[d], s->lv.cap);
+    }
+    s->left = (int64_t)leave[0] + leave[1];
+    return 0;
+}
+int mpic_migration_absorb(mpic_sim* s, int n_from_lo, int n_from_hi) {
+    REQUIRE(s && n_from_lo >= 0 && n_from_hi >= 0, MPIC_EINVAL, "bad argument");
+    REQUIRE(s->lv.rec[0], MPIC_ESTATE, "migration buffers exist only for nranks > 1 with particle storage");
+    REQUIRE(s->n + s->arrived + n_from_lo + n_from_hi <= s->cap, MPIC_ENOMEM, "particle capacity exceeded by arrivals");
+    REQUIRE(s->counts_valid, MPIC_ESTATE, "mpic_migration_absorb must follow mpic_push_deposit");
+    // arrivals are appended in (source rank order: lower, upper; source order) -- SURVEY.md B.8
+    TRY(launch_absorb(s->P, s->pa[s->cur], s->n + s->arrived, s->arrive[0], n_from_lo, s->cell_count, s->st));
+    s->arrived += n_from_lo;
+    TRY(launch_absorb(s->P, s->pa[s->cur], s->n + s->arrived, s->arrive[1], n_from_hi, s->cell_count, s->st));
+    s->arrived += n_from_hi;
+    s->launches += (n_from_lo > 0) + (n_from_hi > 0);
     return 0;
 }
 
@@ -399,13 +474,24 @@ static int sort_all(mpic_sim* s, bool counted) {
     s->counts_valid = false;
     if (!counted) {
         CUDA_TRY(cudaMemsetAsync(s->cell_count, 0, (size_t)s->n_entries * 4, s->st));
-        TRY(launch_count_keys(s->P, s->pa[s->cur], 0, s->n, s->cell_count, nullptr, s->st));
+        TRY(launch_count_keys(s->P, s->pa[s->cur], 0, s->n + s->arrived, s->cell_count, nullptr, s->st));
         s->launches++;
     }
+    const int64_t total = s->n + s->arrived;
     TRY(launch_scan_cells(s->cell_count, s->cell_start, s->n_entries, s->scan_tmp, s->st));
-    TRY(launch_scatter(s->P, s->pa[s->cur], s->pa[s->cur ^ 1], s->n, s->cell_start, s->cell_count, s->st));
+    TRY(launch_scatter(s->P, s->pa[s->cur], s->pa[s->cur ^ 1], total, s->cell_start, s->cell_count, s->st));
     s->launches += 4;
     s->cur ^= 1;
+    if (s->prm.nranks > 1) {       // particles whose key is a leaver bin were dropped by the scatter
+        if (counted && s->left >= 0) s->n = total - s->left;
+        else {
+            int kept = 0;
+            CUDA_TRY(cudaMemcpyAsync(&kept, s->cell_start + s->P.ncells, sizeof(int), cudaMemcpyDeviceToHost, s->st));
+            CUDA_TRY(cudaStreamSynchronize(s->st));
+            s->n = kept;
+        }
+    }
+    s->arrived = 0; s->left = -1;
     return 0;
 }
 int mpic_upload_particles(mpic_sim* s, int64_t n, const double* x, const double* y, const double* ux, const double* uy,
@@ -456,9 +542,12 @@ int mpic_load_uniform(mpic_sim* s, int ppc, double u_th, double d0, double d1, d
 
 int mpic_push_deposit(mpic_sim* s) {
     REQUIRE(s && s->cap > 0, MPIC_ESTATE, "no particle storage");
+    REQUIRE(s->arrived == 0, MPIC_ESTATE, "arrivals absorbed but not sorted in: call mpic_sort_tiles before the next push");
     CUDA_TRY(cudaMemsetAsync(s->cell_count, 0, (size_t)s->n_entries * 4, s->st));
-    TRY(launch_push_deposit(s->P, s->G, &s->tmap, s->planes, s->jacc, s->pa[s->cur], s->cell_start, s->cell_count, nullptr,
-                            s->push_split, s->nsm, s->st));
+    if (s->prm.nranks > 1) CUDA_TRY(cudaMemsetAsync(s->lv.count, 0, 2 * sizeof(int), s->st));
+    s->left = s->prm.nranks > 1 ? -1 : 0;
+    TRY(launch_push_deposit(s->P, s->G, &s->tmap, s->jacc, s->pa[s->cur], s->cell_start, s->cell_count, s->push_split,
+                            s->lv, s->st));
     s->launches++;
     s->counts_valid = true;
     return 0;

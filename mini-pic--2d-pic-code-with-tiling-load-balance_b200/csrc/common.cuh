@@ -50,6 +50,13 @@ struct Particles {
     int* tag;
 };
 
+#define MPIC_REC_DOUBLES 7                            /* migration record: x,y,ux,uy,uz,q,tag(as int64 bits) = 56 B */
+struct LeaveBufs {
+    double* rec[2];       // AoS records of particles that left the slab downwards (0) / upwards (1)
+    int* count;           // count[2]
+    int cap;              // records per buffer
+};
+
 void mpic_set_error(const char* fmt, ...);
 
 #define CUDA_TRY(expr)                                                                          \
@@ -71,6 +78,9 @@ int launch_fused_step(const FieldGeom& G, const double* src, double* dst, int64_
                       const YeeCoef& c, int scheme, cudaStream_t st);
 int launch_wrap_guards(const FieldGeom& G, double* planes, int first_plane, int nplanes, int do_y, cudaStream_t st);
 int launch_fold_current(const FieldGeom& G, int64_t* jacc, int nplanes, int do_y, cudaStream_t st);
+// slab halos: staging layout [side][3 planes][g rows][pitch] (+ header), side 0 = lower neighbour, 1 = upper neighbour
+int launch_halo_pack(const FieldGeom& G, const double* base3, int is_current, double* send, int64_t side_stride, cudaStream_t st);
+int launch_halo_unpack(const FieldGeom& G, double* base3, int is_current, const double* recv, int64_t side_stride, cudaStream_t st);
 int launch_planes_to_tiles(const FieldGeom& G, const double* planes, double* grid6, const int* lrow, const int* lcol,
                            int ntiles, int tnx, int tny, cudaStream_t st);
 int launch_tiles_to_planes(const FieldGeom& G, double* planes, const double* grid6, const int* lrow, const int* lcol,
@@ -83,10 +93,9 @@ int launch_gauss_residual(const FieldGeom& G, const double* planes, const int64_
                           double inv_dy, double* out_max, cudaStream_t st);
 
 // ---- kernel launchers implemented in particles.cu
-struct PushArgs;
-int launch_push_deposit(const PicConst& P, const FieldGeom& G, const CUtensorMap* tmap, const double* planes,
-                        int64_t* jacc, Particles p, const int* cell_start, int* cell_count_new, int64_t* leave_count,
-                        int split, int nsm, cudaStream_t st);
+int launch_push_deposit(const PicConst& P, const FieldGeom& G, const CUtensorMap* tmap, int64_t* jacc, Particles p,
+                        const int* cell_start, int* cell_count_new, int split, LeaveBufs lv, cudaStream_t st);
+int launch_absorb(const PicConst& P, Particles p, int64_t first, const double* rec, int n, int* cell_count, cudaStream_t st);
 int launch_count_keys(const PicConst& P, Particles p, int64_t first, int64_t n, int* cell_count, int* key_out, cudaStream_t st);
 int launch_scan_cells(int* cell_count, int* cell_start, int n_entries, int* block_tmp, cudaStream_t st);
 int launch_scatter(const PicConst& P, Particles src, Particles dst, int64_t n, const int* cell_start, int* cursor, cudaStream_t st);

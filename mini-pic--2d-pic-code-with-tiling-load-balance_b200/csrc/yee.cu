@@ -158,6 +158,36 @@ __global__ void fold_x_kernel(FieldGeom G, int64_t* __restrict__ jacc, int nplan
     }
 }
 
+// ---- slab halos (nranks > 1): edge rows <-> contiguous staging [side][3][g][pitch]; whole rows incl. x guards travel,
+// so received guard rows need no x rebuild.  Fields: interior edge rows out, guard rows in (copy = the reference's
+// updateGuardRegion).  Current: guard rows out, ADDED into the neighbour's interior edge rows, own guard
+// rows zeroed.  One thread per value; blockIdx.y = side*3*g + plane*g + row.
+__global__ void halo_pack_kernel(FieldGeom G, const unsigned long long* __restrict__ base3, int is_current,
+                                 unsigned long long* __restrict__ send, int64_t side_stride) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= G.pitch) return;
+    const int g = G.g, r = blockIdx.y % g, p = (blockIdx.y / g) % 3, side = blockIdx.y / (3 * g);
+    const int row = is_current ? (side ? g + G.nyl + r : r) : (side ? G.nyl + r : g + r);
+    send[side * side_stride + ((int64_t)(p * g + r)) * G.pitch + c] = base3[(int64_t)p * G.plane + (int64_t)row * G.pitch + c];
+}
+__global__ void halo_unpack_kernel(FieldGeom G, unsigned long long* __restrict__ base3, int is_current,
+                                   const unsigned long long* __restrict__ recv, int64_t side_stride) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= G.pitch) return;
+    const int g = G.g, r = blockIdx.y % g, p = (blockIdx.y / g) % 3, side = blockIdx.y / (3 * g);
+    const unsigned long long v = recv[side * side_stride + ((int64_t)(p * g + r)) * G.pitch + c];
+    unsigned long long* plane = base3 + (int64_t)p * G.plane;
+    if (is_current) {
+        const int irow = side ? G.nyl + r : g + r;            // interior edge row that receives the neighbour's guard deposits
+        const int grow = side ? g + G.nyl + r : r;            // own guard row (already packed and sent): zero it
+        plane[(int64_t)irow * G.pitch + c] += v;
+        plane[(int64_t)grow * G.pitch + c] = 0ull;
+    } else {
+        const int grow = side ? g + G.nyl + r : r;
+        plane[(int64_t)grow * G.pitch + c] = v;
+    }
+}
+
 // ---- reference tile layout <-> planes.  One block per (tile, row of the patch).
 template <int TO_TILES>
 __global__ void tiles_kernel(FieldGeom G, double* __restrict__ f, double* __restrict__ grid6,
@@ -273,6 +303,18 @@ int launch_wrap_guards(const FieldGeom& G, double* planes, int first, int nplane
 int launch_fold_current(const FieldGeom& G, int64_t* jacc, int nplanes, int do_y, cudaStream_t st) {
     if (do_y) { fold_y_kernel<<<dim3(ceil_div(G.nx + 2 * G.g, 256), 2 * G.g), 256, 0, st>>>(G, jacc, nplanes); LAUNCH_CHECK(); }
     fold_x_kernel<<<ceil_div(G.rows, 128), 128, 0, st>>>(G, jacc, nplanes);
+    LAUNCH_CHECK();
+    return 0;
+}
+int launch_halo_pack(const FieldGeom& G, const double* base3, int is_current, double* send, int64_t side_stride, cudaStream_t st) {
+    halo_pack_kernel<<<dim3(ceil_div(G.pitch, 256), 6 * G.g), 256, 0, st>>>(G, (const unsigned long long*)base3, is_current,
+                                                                         (unsigned long long*)send, side_stride);
+    LAUNCH_CHECK();
+    return 0;
+}
+int launch_halo_unpack(const FieldGeom& G, double* base3, int is_current, const double* recv, int64_t side_stride, cudaStream_t st) {
+    halo_unpack_kernel<<<dim3(ceil_div(G.pitch, 256), 6 * G.g), 256, 0, st>>>(G, (unsigned long long*)base3, is_current,
+                                                                           (const unsigned long long*)recv, side_stride);
     LAUNCH_CHECK();
     return 0;
 }

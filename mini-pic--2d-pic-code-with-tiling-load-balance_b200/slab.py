@@ -1,0 +1,241 @@
+"""Slab decomposition over tile rows: the host-side orchestration of one process per GPU.
+
+Replaces, for N > 1 ranks, the MPI part of the reference loop -- the three exchange phases (PIC_2D.cpp:200-248, 276-319,
+348-396: 8 Isend/Irecv per tile per phase, 2 barriers each) and the tile hand-off (Auxiliar_functions.cpp:242-272) -- by
+a periodic RING of slabs (R = N, C = 1): per exchange each rank moves one contiguous message to each of its two
+neighbours; there is no barrier and no collective on the step path.  The reference's 8-direction tile exchange collapses
+because x-periodicity and all tile-to-tile guards inside a slab are handled in the kernels.
+
+The orchestration is transport-agnostic: `Ring` uses torch.distributed point-to-point ops (NCCL over NVLink on the GPUs,
+gloo in the CPU tests), and `SlabStepper` only needs an object with the Sim slab interface (halo_tensors, halo_pack,
+halo_unpack, push_deposit, step_b_half, step_e_full, migration_tensors, migration_counts, migration_absorb, sort_tiles).
+"""
+import contextlib
+import importlib
+import json
+import os
+import time
+
+import numpy as np
+
+
+class Ring:
+    """Periodic neighbour exchange: send_lo -> lower neighbour's recv_hi, send_hi -> upper neighbour's recv_lo."""
+
+    def __init__(self, rank, world, dist=None, group=None):
+        if dist is None:
+            import torch.distributed as dist
+        self.dist, self.group = dist, group
+        self.rank, self.world = rank, world
+        self.lo, self.hi = (rank - 1) % world, (rank + 1) % world
+
+    def sendrecv(self, send_lo, send_hi, recv_lo, recv_hi):
+        """Any argument may be None (nothing to move in that direction; both ends must agree).  Between one pair of ranks
+        NCCL matches sends and receives in issue order and has no tags, so for world == 2 (both neighbours are the same
+        rank) the receives are posted in the order the peer posts its sends: its send_lo lands in my recv_hi first."""
+        d = self.dist
+        ops = []
+        if send_lo is not None:
+            ops.append(d.P2POp(d.isend, send_lo, self.lo, self.group))
+        if send_hi is not None:
+            ops.append(d.P2POp(d.isend, send_hi, self.hi, self.group))
+        if recv_hi is not None:
+            ops.append(d.P2POp(d.irecv, recv_hi, self.hi, self.group))
+        if recv_lo is not None:
+            ops.append(d.P2POp(d.irecv, recv_lo, self.lo, self.group))
+        if not ops:
+            return
+        for w in d.batch_isend_irecv(ops):
+            w.wait()
+
+
+class SlabStepper:
+    """One rank's time step with its ring exchanges.
+
+    step():  P1/P2 push+deposit -> P3 current guard rows ADDED into the neighbours (message header carries the leaver
+    counts) -> A half-B, exchange B -> C E sweep with -dt*J, exchange E -> E half-B, exchange B -> particle hand-off
+    (one stream sync to learn the counts) -> S count/scan/scatter with the arrivals merged in."""
+
+    def __init__(self, sim, ring):
+        self.sim, self.ring = sim, ring
+        self.h = sim.halo_tensors()
+        self.m = None
+        self.moved = 0            # records sent so far (diagnostic)
+
+    def exchange(self, which):
+        s, h = self.sim, self.h
+        s.halo_pack(which)
+        self.ring.sendrecv(h["send"][0], h["send"][1], h["recv"][0], h["recv"][1])
+        s.halo_unpack(which)
+
+    def refresh_guards(self):
+        """After an upload: y guards of E and B from the neighbours (the reference fills them analytically, W3)."""
+        self.exchange(0)
+        self.exchange(1)
+
+    def field_step(self):
+        s = self.sim
+        s.step_b_half()
+        self.exchange(1)
+        s.step_e_full()
+        self.exchange(0)
+        s.step_b_half()
+        self.exchange(1)
+
+    def migrate(self):
+        s = self.sim
+        if self.m is None:
+            self.m = s.migration_tensors()
+        m, rb = self.m, self.m["record_bytes"]
+        leave, arrive = s.migration_counts()
+        cut = lambda t, n: t[: n * rb] if n > 0 else None
+        self.ring.sendrecv(cut(m["send"][0], leave[0]), cut(m["send"][1], leave[1]),
+                           cut(m["recv"][0], arrive[0]), cut(m["recv"][1], arrive[1]))
+        s.migration_absorb(arrive[0], arrive[1])
+        self.moved += leave[0] + leave[1]
+
+    def step(self):
+        s = self.sim
+        s.push_deposit()
+        self.exchange(2)
+        self.field_step()
+        self.migrate()
+        s.sort_tiles()
+
+
+def tile_row_costs(counts, gtc, cells_per_tile, w_particle=1.0, w_cell=0.25):
+    """Cost model of the rebalancer: cost of a tile row = particles + w_cell * cells (the Yee sweeps and
+    the per-tile patch staging do not vanish in empty tiles)."""
+    counts = np.asarray(counts, dtype=np.float64).reshape(-1, gtc)
+    return w_particle * counts.sum(axis=1) + w_cell * gtc * cells_per_tile
+
+
+def balanced_slab_rows(row_costs, nranks):
+    """Contiguous partition of tile rows into `nranks` slabs minimising the maximum slab cost (exact: binary search on the
+    bottleneck + greedy sweep).  Returns [(row0, nrows)] with every slab non-empty.  This is the policy the reference
+    leaves as future work (Report p.10); the mechanism it offers is removeTileFromRank/addTileToRank."""
+    c = np.asarray(row_costs, dtype=np.float64)
+    n = len(c)
+    if nranks > n:
+        raise ValueError("more ranks than tile rows")
+
+    def cuts(limit):
+        out, start, acc = [], 0, 0.0
+        for i in range(n):
+            remaining_ranks = nranks - len(out) - 1            # slabs still to open after the current one
+            must_cut = (n - i) == remaining_ranks and i > start  # leave one row for each remaining slab
+            if i > start and (acc + c[i] > limit or must_cut):
+                out.append((start, i - start))
+                start, acc = i, 0.0
+            acc += c[i]
+        out.append((start, n - start))
+        return out
+
+    lo, hi = float(c.max()), float(c.sum())
+    for _ in range(60):
+        mid = 0.5 * (lo + hi)
+        if len(cuts(mid)) <= nranks:
+            hi = mid
+        else:
+            lo = mid
+    parts = cuts(hi)
+    while len(parts) < nranks:                                  # split the widest slab until every rank owns rows
+        k = max(range(len(parts)), key=lambda j: parts[j][1])
+        r0, nr = parts[k]
+        if nr < 2:
+            raise ValueError("cannot give every rank a tile row")
+        parts[k:k + 1] = [(r0, nr // 2), (r0 + nr // 2, nr - nr // 2)]
+    return parts
+
+
+# ------------------------------------------------------------------------------------------------ multi-GPU bench
+def bench_main(args, w, rank, world, local, peak, peak_how):
+    """bench.py for N > 1 (torchrun, one rank per GPU): weak scaling -- every rank owns an (ny x nx) slab of an
+    (N*ny x nx) domain.  Timed on the device (CUDA events on the library stream), max over ranks."""
+    import torch
+    import torch.distributed as dist
+    m = importlib.import_module(__package__)
+    bench = importlib.import_module("bench")
+    dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    nx, ny, tn, ppc = w["nx"], w["ny"] * world, w["tn"], w["ppc"]
+    dx = dy = w["dx"]
+    dt = m.courant_dt(dx, dy)
+    n_local = nx * w["ny"] * ppc
+    sim = m.Sim(nx, ny, tn, tn, dx, dy, dt, max_particles=int(n_local * 1.05) + 4096, rank=rank, nranks=world, device=local)
+    sim.load_uniform(ppc, u_th=w["u_th"], two_stream=w["two_stream"], seed=12345)
+    sim.sync()
+    st = sim.torch_stream()
+    K, W = args.steps, max(args.warmup, 3)
+    with torch.cuda.stream(st):
+        stepper = SlabStepper(sim, Ring(rank, world))
+        stepper.refresh_guards()
+        for _ in range(W):
+            stepper.step()
+        sim.sync()
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = sim.kernel_launches
+        clk = bench.ClockSampler(local) if rank == 0 else contextlib.nullcontext()
+        with clk:
+            e0.record(st)
+            for _ in range(K):
+                stepper.step()
+            e1.record(st)
+            sim.sync()
+            torch.cuda.synchronize()
+        dist.barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=f"cuda:{local}", dtype=torch.float64)
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        npart = torch.tensor([sim.num_particles], device=f"cuda:{local}", dtype=torch.int64)
+        dist.all_reduce(npart)
+        launches = sim.kernel_launches - l0
+
+        # end to end: every rank uploads its slab (fields + particles) from pinned host memory, steps once, reads it back
+        e2e = None
+        if not args.no_e2e:
+            parts = sim.download_particles()
+            planes = sim.download_planes()
+            hp = {k: torch.from_numpy(v).pin_memory() for k, v in parts.items()}
+            hf = [torch.from_numpy(a).pin_memory() for a in planes]
+            ke = max(2, min(K, 3))
+
+            def host_step():
+                sim.upload_planes([t.numpy() for t in hf])
+                stepper.refresh_guards()
+                sim.upload_particles({k: v.numpy() for k, v in hp.items()})
+                stepper.step()
+                p2 = sim.download_particles()
+                f2 = sim.download_planes()
+                return p2["x"].shape[0], f2
+
+            host_step()
+            torch.cuda.synchronize()
+            dist.barrier()
+            t0 = time.perf_counter()
+            for _ in range(ke):
+                host_step()
+            torch.cuda.synchronize()
+            tw = torch.tensor([time.perf_counter() - t0], device=f"cuda:{local}", dtype=torch.float64)
+            dist.all_reduce(tw, op=dist.ReduceOp.MAX)
+            nbytes = 6 * nx * w["ny"] * 8 + n_local * 52
+            e2e = {"value": float(npart.item()) * ke / tw.item(), "unit": "particles/s", "h2d_bytes_per_step": nbytes * world,
+                   "d2h_bytes_per_step": nbytes * world, "steps": ke, "ms_per_step": 1e3 * tw.item() / ke,
+                   "api": "per rank: mpic_upload_planes + mpic_upload_particles, SlabStepper.step, mpic_download_*"}
+    if rank == 0:
+        value = float(npart.item()) * K / (ms.item() * 1e-3)
+        out = {"metric": "particle-pushes/s (push+deposit+sort)", "value": value, "unit": "particles/s", "n_gpus": world,
+               "steps": K, "warmup": W, "ms_per_step": ms.item() / K, "higher_is_better": True, "scaling": "weak",
+               "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+               "config": {"workload": args.workload, **w, "ny_global": ny, "particles": int(npart.item()),
+                          "decomposition": f"{world} slabs of {w['ny']} cell rows (ring, NCCL send/recv)",
+                          "l2": "per-rank particle state >> 126 MB L2 (no flush needed)"},
+               "gpu_launches": int(launches), "clocks": clk.summary(), "migrated_records_rank0": int(stepper.moved),
+               "roofline": {"bound": "hbm", "kernel": "whole step", "achieved": value * (88.0 + 120.0) / 1e9 / world, "peak": peak,
+                            "unit": "GB/s", "frac": value * (88.0 + 120.0) / 1e9 / world / peak, "traffic": None,
+                            "bytes_per_particle": 208.0, "peak_source": peak_how, "note": "per GPU, push 88 B + sort 120 B per particle"}}
+        if e2e:
+            out["e2e"] = e2e
+        print(json.dumps(out))
+    sim.close()
+    dist.destroy_process_group()

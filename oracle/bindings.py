@@ -214,3 +214,18 @@ def deposit_rho(lib, P, parts):
     rho = np.zeros((P.ny, P.nx), dtype=np.int64)
     lib.orc_deposit_rho(C.byref(P), _dp(parts["x"]), _dp(parts["y"]), _dp(parts["q"]), parts["x"].shape[0], _lp(rho))
     return rho
+
+
+def b_sweep(lib, planes, dt, dx, dy, scheme=0, mode=0):
+    ny, nx = planes[0].shape
+    lib.orc_b_sweep_global(*[_dp(a) for a in planes], nx, ny, dt, dx, dy, scheme, mode)
+
+
+def e_sweep(lib, planes, dt, dx, dy, mode=0):
+    ny, nx = planes[0].shape
+    lib.orc_e_sweep_global(*[_dp(a) for a in planes], nx, ny, dt, dx, dy, mode)
+
+
+def apply_current(lib, P, planes, J):
+    """E <- E - dt*J (J: int64 (3,ny,nx) fixed point), as in orc_pic_steps."""
+    lib.orc_apply_current(C.byref(P), _dp(planes[0]), _dp(planes[1]), _dp(planes[2]), _lp(J[0]), _lp(J[1]), _lp(J[2]))

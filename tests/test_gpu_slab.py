@@ -1,0 +1,131 @@
+"""GPU tests of the slab (N > 1) kernels and protocol.
+
+1. N slab handles on ONE GPU, one thread per rank, product SlabStepper with an in-process ring (tests/util.ThreadRing):
+   halo pack/unpack kernels, J guard-row add, leaver records written by the push kernel, arrival absorb + merged sort.
+   Bit-exact versus the single-rank CPU oracle and versus the single-slab GPU path.
+2. (needs >= 2 GPUs, skipped otherwise) the same through torchrun + NCCL, one process per GPU.
+"""
+import importlib
+import os
+import subprocess
+import sys
+import threading
+
+import numpy as np
+import pytest
+from oracle import bindings as ob
+from util import pkg, plasma, by_tag, copy_parts, PKG, ROOT, ThreadHub, ThreadRing
+
+pytestmark = pytest.mark.gpu
+
+
+def _problem(nx, ny, tn, ppc, u_th, seed=11):
+    dx = dy = 0.1
+    dt = pkg().courant_dt(dx, dy)
+    parts = plasma().load_uniform(nx, ny, tn, tn, dx, dy, ppc, u_th=u_th, seed=seed, two_stream=0.2)
+    rng = np.random.default_rng(seed)
+    planes = [0.02 * rng.standard_normal((ny, nx)) for _ in range(6)]
+    return dx, dy, dt, parts, planes
+
+
+@pytest.mark.parametrize("world,shape", [(2, (64, 64, 16, 6, 0.6)), (3, (48, 96, 8, 5, 0.9)), (4, (32, 64, 16, 4, 0.5))])
+def test_slabs_on_one_gpu_bit_exact(world, shape):
+    m = pkg()
+    slab = importlib.import_module(PKG + ".slab")
+    nx, ny, tn, ppc, u_th = shape
+    dx, dy, dt, parts, planes = _problem(nx, ny, tn, ppc, u_th)
+    steps = 8
+    hub = ThreadHub(world)
+    sims, errs = [None] * world, []
+
+    def run(rank):
+        try:
+            s = m.Sim(nx, ny, tn, tn, dx, dy, dt, max_particles=parts["x"].shape[0], rank=rank, nranks=world)
+            sims[rank] = s
+            r0, r1 = s.row0 * tn, (s.row0 + s.nrows) * tn
+            s.upload_planes([a[r0:r1] for a in planes])
+            s.upload_particles(parts)                      # the device keeps only the particles of its slab
+            st = slab.SlabStepper(s, ThreadRing(rank, hub))
+            st.refresh_guards()
+            for _ in range(steps):
+                st.step()
+            s.sync()
+            s.moved = st.moved
+        except Exception as e:                              # noqa: BLE001
+            errs.append((rank, repr(e)))
+
+    th = [threading.Thread(target=run, args=(r,)) for r in range(world)]
+    [t.start() for t in th]
+    [t.join(300) for t in th]
+    assert not errs, errs
+    lib = ob.load_oracle()
+    P = ob.make_params(lib, nx, ny, tn, tn, dx, dy, dt)
+    want, wf = copy_parts(parts), [a.copy() for a in planes]
+    counts, _ = ob.pic_steps(lib, P, wf, want, steps)
+    got = by_tag({k: np.concatenate([s.download_particles()[k] for s in sims]) for k in ("x", "y", "ux", "uy", "uz", "q", "tag")})
+    want = by_tag(want)
+    assert np.array_equal(got["tag"], want["tag"])
+    for k in ("x", "y", "ux", "uy", "uz", "q"):
+        assert np.array_equal(got[k], want[k]), k
+    gf = [np.concatenate([s.download_planes()[k] for s in sims]) for k in range(6)]
+    for k in range(6):
+        assert np.array_equal(gf[k], wf[k]), k
+    assert np.array_equal(np.concatenate([s.tile_counts() for s in sims]), counts)
+    assert sum(s.moved for s in sims) > 0
+    assert sum(s.num_particles for s in sims) == parts["x"].shape[0]
+    # tile patches WITH guards (what a dump holds) agree with the single-slab device path
+    one = m.Sim(nx, ny, tn, tn, dx, dy, dt, max_particles=parts["x"].shape[0])
+    one.upload_planes(planes)
+    one.upload_particles(parts)
+    one.pic_steps(steps)
+    gtc = nx // tn
+    for s in sims:
+        gids = np.arange(s.row0 * gtc, (s.row0 + s.nrows) * gtc, dtype=np.int32)
+        assert np.array_equal(s.download_tiles(gids), one.download_tiles(gids))
+
+
+def test_field_only_slabs_match_reference_loop_fixture():
+    """Yee loop on 2 slabs == the reference's own tile loop (fixture from oracle/_ref/libref.so)."""
+    m = pkg()
+    slab = importlib.import_module(PKG + ".slab")
+    f = dict(np.load(os.path.join(ROOT, "tests", "golden", "ref_current.npz")))     # materialise: NpzFile is not thread-safe
+    nx, ny, R, C, tr, tc, g, steps = [int(v) for v in f["meta"]]
+    tnx, tny = nx // (C * tc), ny // (R * tr)
+    world = 2
+    hub = ThreadHub(world)
+    outs, errs = [None] * world, []
+
+    def run(rank):
+        try:
+            s = m.Sim(nx, ny, tnx, tny, float(f["dx"]), float(f["dy"]), float(f["dt"]), rank=rank, nranks=world)
+            r0, r1 = s.row0 * tny, (s.row0 + s.nrows) * tny
+            s.upload_planes([f["ic"][r0:r1, :, k] for k in range(6)])
+            st = slab.SlabStepper(s, ThreadRing(rank, hub))
+            st.refresh_guards()
+            for _ in range(steps):
+                st.field_step()
+            gtc = nx // tnx
+            gids = np.arange(s.row0 * gtc, (s.row0 + s.nrows) * gtc, dtype=np.int32)
+            outs[rank] = (s.download_planes(), gids, s.download_tiles(gids))
+        except Exception as e:                              # noqa: BLE001
+            errs.append((rank, repr(e)))
+
+    th = [threading.Thread(target=run, args=(r,)) for r in range(world)]
+    [t.start() for t in th]
+    [t.join(300) for t in th]
+    assert not errs, errs
+    for k in range(6):
+        assert np.array_equal(np.concatenate([o[0][k] for o in outs]), f["out"][..., k]), k
+    for _, gids, tiles in outs:
+        assert np.array_equal(tiles, f["tiles"][gids])
+
+
+def test_nccl_slabs_two_processes():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29611", os.path.join(ROOT, "tests", "run_slab_nccl.py")],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert "SLAB_NCCL_PARITY_OK" in r.stdout

@@ -1,0 +1,104 @@
+"""N > 1 path on CPU: the product's slab orchestration (slab.SlabStepper / slab.Ring) over torch.distributed with the
+gloo backend, world_size 2 and 3, with the per-rank compute supplied by the CPU oracle stand-in (tests/cpu_slab.py).
+Bar: after K full PIC steps the union of the ranks' particles and field rows is BIT-IDENTICAL to the single-rank oracle
+run (partition independence: SURVEY.md F8 for the fields, fixed-point current for the deposit)."""
+import importlib
+import os
+import socket
+import sys
+import tempfile
+
+import numpy as np
+import pytest
+import torch.multiprocessing as mp
+
+from util import PKG, ROOT, plasma, by_tag, copy_parts
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _problem(seed=5, nx=32, ny=48, tnx=8, tny=8, ppc=6, u_th=0.7):
+    dx, dy = 0.1, 0.125
+    dt = 0.5 / np.sqrt(1 / dx ** 2 + 1 / dy ** 2)
+    parts = plasma().load_uniform(nx, ny, tnx, tny, dx, dy, ppc, u_th=u_th, seed=seed, two_stream=0.3)
+    rng = np.random.default_rng(seed)
+    planes = [0.02 * rng.standard_normal((ny, nx)) for _ in range(6)]
+    return dict(nx=nx, ny=ny, tnx=tnx, tny=tny, dx=dx, dy=dy, dt=dt), parts, planes
+
+
+def _worker(rank, world, port, steps, rows, outdir):
+    for p in (ROOT, os.path.join(ROOT, "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import torch.distributed as dist
+    from cpu_slab import CpuSlabSim
+    slab = importlib.import_module(PKG + ".slab")
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        g, parts, planes = _problem()
+        row0, nrows = rows[rank]
+        sim = CpuSlabSim(g["nx"], g["ny"], g["tnx"], g["tny"], g["dx"], g["dy"], g["dt"], rank, world, row0, nrows)
+        sim.set_interior(planes)
+        sim.set_particles(parts)
+        st = slab.SlabStepper(sim, slab.Ring(rank, world))
+        st.refresh_guards()
+        for _ in range(steps):
+            st.step()
+        np.savez(os.path.join(outdir, f"rank{rank}.npz"), rows=sim.rows_int, moved=st.moved,
+                 **{f"f{k}": sim.planes[k][sim.rows_int] for k in range(6)}, **sim.parts)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,rows", [(2, [(0, 3), (3, 3)]), (3, [(0, 1), (1, 3), (4, 2)])])
+def test_slab_ring_matches_single_rank_oracle(world, rows):
+    from oracle import bindings as ob
+    steps = 6
+    with tempfile.TemporaryDirectory() as d:
+        mp.spawn(_worker, args=(world, _free_port(), steps, rows, d), nprocs=world, join=True)
+        outs = [np.load(os.path.join(d, f"rank{r}.npz")) for r in range(world)]
+        g, parts, planes = _problem()
+        lib = ob.load_oracle()
+        P = ob.make_params(lib, g["nx"], g["ny"], g["tnx"], g["tny"], g["dx"], g["dy"], g["dt"])
+        want, wf = copy_parts(parts), [a.copy() for a in planes]
+        ob.pic_steps(lib, P, wf, want, steps)
+        got = by_tag({k: np.concatenate([o[k] for o in outs]) for k in ("x", "y", "ux", "uy", "uz", "q", "tag")})
+        want = by_tag(want)
+        assert got["tag"].shape == want["tag"].shape and np.array_equal(got["tag"], want["tag"])   # nobody lost or duplicated
+        for k in ("x", "y", "ux", "uy", "uz", "q"):
+            assert np.array_equal(got[k], want[k]), k
+        for o in outs:
+            for k in range(6):
+                assert np.array_equal(o[f"f{k}"], wf[k][o["rows"]]), k
+        assert sum(int(o["moved"]) for o in outs) > 0          # the hand-off path really ran
+        # every particle sits on the rank that owns its cell row
+        for r, o in enumerate(outs):
+            cy = np.floor(o["y"] * (1.0 / g["dy"])).astype(int)
+            assert ((cy >= o["rows"][0]) & (cy <= o["rows"][-1])).all()
+
+
+def test_balanced_slab_rows_policy():
+    slab = importlib.import_module(PKG + ".slab")
+    # uniform load -> even split
+    assert slab.balanced_slab_rows(np.ones(16), 4) == [(0, 4), (4, 4), (8, 4), (12, 4)]
+    # beam: 55 % of the load in 10 % of the rows -> the hot rows get narrow slabs
+    c = np.full(40, 8.0)
+    c[18:22] = 88.0
+    parts = slab.balanced_slab_rows(c, 8)
+    assert len(parts) == 8 and parts[0][0] == 0 and sum(nr for _, nr in parts) == 40
+    assert all(parts[k][0] + parts[k][1] == parts[k + 1][0] for k in range(7))
+    load = [c[r0:r0 + nr].sum() for r0, nr in parts]
+    even = [c[r0:r0 + 5].sum() for r0 in range(0, 40, 5)]
+    assert max(load) < 0.6 * max(even)
+    assert max(load) <= 1.25 * c.sum() / 8 + c.max()
+    # more ranks than heavy rows, every rank still owns a row
+    assert all(nr >= 1 for _, nr in slab.balanced_slab_rows(np.array([100.0, 1, 1, 1]), 4))
+    costs = slab.tile_row_costs(np.arange(12), 3, 64)
+    assert costs.shape == (4,) and costs[1] > costs[0]
