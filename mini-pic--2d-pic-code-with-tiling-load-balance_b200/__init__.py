@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libminipic_b200.so")
+LIB_PATH = os.environ.get("MPIC_LIB") or os.path.join(_HERE, "libminipic_b200.so")   # MPIC_LIB: kernel-variant A/B runs
 
 c_dp = C.POINTER(C.c_double)
 c_ip = C.POINTER(C.c_int)

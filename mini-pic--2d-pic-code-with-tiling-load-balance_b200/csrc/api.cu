@@ -5,6 +5,7 @@
 #include "common.cuh"
 #include <stdarg.h>
 #include <string.h>
+#include <stdlib.h>
 #include <math.h>
 #include <vector>
 #include <string>
@@ -251,7 +252,8 @@ int mpic_create(const mpic_params* p, mpic_sim** out) {
         // enough CTAs per tile that the grid covers >= 4 waves of 2 CTAs/SM even for few tiles
         int ntiles = P.ltr * P.gtc;
         s->push_split = 1;
-        while (ntiles * s->push_split < 8 * s->nsm && s->push_split < 64) s->push_split *= 2;
+        while (ntiles * s->push_split < 16 * s->nsm && s->push_split < 64) s->push_split *= 2;
+        if (const char* e = getenv("MPIC_PUSH_SPLIT")) { int v = atoi(e); if (v >= 1 && v <= 256) s->push_split = v; }   // tuning knob
     }
     if (p->nranks > 1) {
         s->halo_side = HALO_HDR + (int64_t)3 * G.g * G.pitch;
