@@ -226,6 +226,7 @@ int mpic_create(const mpic_params* p, mpic_sim** out) {
     P.box_x = p->nx * p->dx; P.box_y = p->ny * p->dy;
     P.h = 0.5 * p->dt * p->qm;
     P.cjx = 1.0 / (p->dy * p->dt); P.cjy = 1.0 / (p->dx * p->dt); P.cjz = 1.0 / (p->dx * p->dy);
+    P.sjx = P.cjx * MPIC_JSCALE; P.sjy = P.cjy * MPIC_JSCALE; P.sjz = P.cjz * MPIC_JSCALE; P.dnx = (double)p->nx; P.dny = (double)p->ny;
     YeeCoef& c = s->cf;
     c.bx = p->scheme ? p->dt / p->dx : p->dt / (2 * p->dx);
     c.by = p->scheme ? p->dt / p->dy : p->dt / (2 * p->dy);

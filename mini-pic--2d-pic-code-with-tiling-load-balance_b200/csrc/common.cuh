@@ -43,6 +43,8 @@ struct PicConst {
     double box_x, box_y;
     double h;             // 0.5*dt*qm
     double cjx, cjy, cjz; // 1/(dy*dt), 1/(dx*dt), 1/(dx*dy)
+    double sjx, sjy, sjz; // the same times 2^52 (exact): fixed-point scale folded into the charge factor
+    double dnx, dny;      // (double)nx, (double)ny
 };
 
 struct Particles {
