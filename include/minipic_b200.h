@@ -172,7 +172,32 @@ int mpic_diagnostics(mpic_sim* s, double out[5]);
 /* ---- tile ownership (owner[] map, PIC_2D.cpp:55,144-148; removeTileFromRank/addTileToRank, Auxiliar_functions.cpp:242-272).
  * On one GPU ownership is bookkeeping only (fields never change); it drives currentRank in the dumps. */
 int mpic_get_owner(mpic_sim* s, int* owner /* global tiles */);
+int mpic_set_owner(mpic_sim* s, const int* owner /* global tiles */);
 int mpic_migrate_tile(mpic_sim* s, int gid, int dest_rank);
+
+/* ---- single-process ring: one host thread drives N slab handles (sims[r] is rank r of N, one per GPU; handles may
+ * share a device) and moves halo messages and migrating particles with CUDA peer copies over NVLink, ordered by events
+ * -- no host synchronisation on the field path.  Replaces the MPI exchange phases (PIC_2D.cpp:200-248,276-319,348-396)
+ * for the C++ driver; the one-process-per-GPU NCCL path (slab.py) uses the same kernels and gives the same bits. */
+int mpic_ring_enable_peer_access(mpic_sim* const* sims, int n);
+int mpic_ring_exchange(mpic_sim* const* sims, int n, int which);
+int mpic_ring_refresh_guards(mpic_sim* const* sims, int n);          /* after uploads: y guards of E and B */
+int mpic_ring_field_steps(mpic_sim* const* sims, int n, int nsteps);  /* phases A..F with ring exchanges */
+int mpic_ring_migrate(mpic_sim* const* sims, int n);                  /* particle hand-off after a push */
+int mpic_ring_pic_steps(mpic_sim* const* sims, int n, int nsteps);    /* full PIC steps */
+
+/* ---- field dumps in the reference's HDF5 layout, written without libhdf5 (host code; works without a GPU).
+ * mpic_save_rank_data replaces saveRankData (HDF5_output.h:11, HDF5_output.cpp:10-79): one file, for each listed tile a
+ * group /Tile_<gid> with dataset `fields` (interior_ny+2g, interior_nx+2g) of the 48-byte compound {Ex,Ey,Ez,Bx,By,Bz}
+ * (guards included) and int32 attributes tileRow, tileCol, currentRank.  grid6: ntiles patches, AoS, as Tile::grid. */
+int mpic_save_rank_data(const char* filename, int ntiles, const int* gids, const int* tile_rows, const int* tile_cols,
+                        const int* current_rank, int interior_nx, int interior_ny, int guard, const double* grid6);
+/* Dump the tiles of this slab whose owner[] entry equals `rank` (all local tiles if rank < 0) to `filename`:
+ * device -> tile patches with guards -> mpic_save_rank_data.  Phase H of the loop (PIC_2D.cpp:414-419). */
+int mpic_dump_fields(mpic_sim* s, const char* filename, int rank);
+/* params.txt next to the dumps (PIC_2D.cpp:425-438), consumed by File_reader.py:read_params. */
+int mpic_write_params(const char* path, double box_x, double box_y, int nx, int ny, int guard, int interior_nx,
+                      int interior_ny, double sim_time, double dt, int total_steps);
 
 /* ---- whole-step host-buffer entry point (the e2e path): upload fields+particles, nsteps PIC steps, download both. */
 int mpic_pic_steps_host(mpic_sim* s, int nsteps, double* const planes[6], int64_t n, double* x, double* y, double* ux,

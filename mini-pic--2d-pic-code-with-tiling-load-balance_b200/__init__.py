@@ -84,6 +84,15 @@ def lib():
     L.mpic_update_e_full.argtypes = [c_dp, c_dp, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double]
     L.mpic_pack_send_buffer.argtypes = [c_dp, C.c_int, C.c_int, C.c_int, C.c_int, c_dp]
     L.mpic_update_guard_region.argtypes = [c_dp, C.c_int, C.c_int, C.c_int, C.c_int, c_dp]
+    L.mpic_save_rank_data.argtypes = [C.c_char_p, C.c_int, c_ip, c_ip, c_ip, c_ip, C.c_int, C.c_int, C.c_int, c_dp]
+    L.mpic_dump_fields.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
+    L.mpic_write_params.argtypes = [C.c_char_p, C.c_double, C.c_double, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                    C.c_double, C.c_double, C.c_int]
+    for name in ("mpic_ring_enable_peer_access", "mpic_ring_refresh_guards", "mpic_ring_migrate"):
+        getattr(L, name).argtypes = [C.POINTER(C.c_void_p), C.c_int]
+    for name in ("mpic_ring_exchange", "mpic_ring_field_steps", "mpic_ring_pic_steps"):
+        getattr(L, name).argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int]
+    L.mpic_set_owner.argtypes = [C.c_void_p, c_ip]
     L.mpic_slab_rows.argtypes = [C.c_int, C.c_int, C.c_int, c_ip, c_ip]
     _lib = L
     return L
@@ -295,11 +304,18 @@ class Sim:
         return {"field_energy": out[0], "kinetic_energy": out[1], "gauss_residual": out[2], "charge": out[3],
                 "particles": int(out[4])}
 
+    def dump_fields(self, filename, rank=-1):
+        """Phase H: fields_rank_<r>_step_<s>.h5 in the reference layout (HDF5_output.cpp:10-79)."""
+        _chk(lib().mpic_dump_fields(self.h, os.fsencode(filename), rank))
+
     # ---- ownership
     def owner(self):
         out = np.empty(self.gtr * self.gtc, dtype=np.int32)
         _chk(lib().mpic_get_owner(self.h, _ip(out)))
         return out
+
+    def set_owner(self, owner):
+        _chk(lib().mpic_set_owner(self.h, _ip(np.ascontiguousarray(owner, dtype=np.int32))))
 
     def migrate_tile(self, gid, dest):
         _chk(lib().mpic_migrate_tile(self.h, gid, dest))
@@ -334,3 +350,42 @@ def pack_send_buffer(grid6, tnx, tny, guard, d):
 
 def update_guard_region(grid6, tnx, tny, guard, d, strip):
     _chk(lib().mpic_update_guard_region(_dp(grid6), tnx, tny, guard, d, _dp(np.ascontiguousarray(strip))))
+
+
+def save_rank_data(filename, gids, tile_rows, tile_cols, current_rank, tnx, tny, guard, grid6):
+    """saveRankData (HDF5_output.h:11) on host arrays; works without a GPU."""
+    a = [np.ascontiguousarray(v, dtype=np.int32) for v in (gids, tile_rows, tile_cols, current_rank)]
+    grid6 = np.ascontiguousarray(grid6, dtype=np.float64)
+    assert grid6.shape == (len(a[0]), tny + 2 * guard, tnx + 2 * guard, 6)
+    _chk(lib().mpic_save_rank_data(os.fsencode(filename), len(a[0]), *[_ip(v) for v in a], tnx, tny, guard, _dp(grid6)))
+
+
+def write_params(path, box_x, box_y, nx, ny, guard, tnx, tny, sim_time, dt, total_steps):
+    _chk(lib().mpic_write_params(os.fsencode(path), box_x, box_y, nx, ny, guard, tnx, tny, sim_time, dt, total_steps))
+
+
+class SlabRing:
+    """N slab handles driven by ONE host process with CUDA peer copies (csrc/ring.cu) -- what the C++ driver uses for
+    --gpus N.  sims[r] must be rank r of len(sims)."""
+
+    def __init__(self, sims):
+        self.sims = list(sims)
+        self.arr = (C.c_void_p * len(self.sims))(*[s.h for s in self.sims])
+        self.n = len(self.sims)
+        _chk(lib().mpic_ring_enable_peer_access(self.arr, self.n))
+
+    def refresh_guards(self):
+        _chk(lib().mpic_ring_refresh_guards(self.arr, self.n))
+
+    def exchange(self, which):
+        _chk(lib().mpic_ring_exchange(self.arr, self.n, which))
+
+    def field_steps(self, nsteps):
+        _chk(lib().mpic_ring_field_steps(self.arr, self.n, nsteps))
+
+    def pic_steps(self, nsteps):
+        _chk(lib().mpic_ring_pic_steps(self.arr, self.n, nsteps))
+
+    def sync(self):
+        for s in self.sims:
+            s.sync()

@@ -15,44 +15,7 @@ void mpic_set_error(const char* fmt, ...) {
     va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof g_err, fmt, ap); va_end(ap);
 }
 
-struct mpic_sim {
-    mpic_params prm;
-    FieldGeom G;
-    PicConst P;
-    YeeCoef cf;
-    cudaStream_t st = nullptr;
-    double* planes = nullptr;      // 6 field planes
-    int64_t* jacc = nullptr;       // 3 current accumulators
-    int64_t* rho = nullptr;        // 1 plane, diagnostics only (lazy)
-    Particles pa[2] = {};
-    int cur = 0;
-    int64_t n = 0, cap = 0;
-    int* cell_start = nullptr;     // n_entries + 1
-    int* cell_count = nullptr;     // n_entries (doubles as scatter cursor)
-    int* scan_tmp = nullptr;
-    int n_entries = 0;             // ncells + 2 (leave-down, leave-up bins)
-    CUtensorMap tmap;
-    bool has_tmap = false;
-    double* d_scratch = nullptr;   // 8 doubles
-    int64_t tag_base = 0;
-    int64_t launches = 0;
-    int push_split = 4;
-    int nsm = 148;
-    bool counts_valid = false;     // cell_count holds the destination-cell histogram of the last push
-    // ---- slab plumbing (nranks > 1)
-    double* halo_send = nullptr;   // [2 sides][HALO_HDR + 3*g*pitch] values
-    double* halo_recv = nullptr;
-    int64_t halo_side = 0;         // values per side
-    LeaveBufs lv = {};             // leaver records written by the push kernel
-    double* arrive[2] = {};        // records received from the lower / upper neighbour
-    int64_t arrived = 0;           // records absorbed into the tail [n, n+arrived) and not yet sorted in
-    int64_t left = -1;             // leavers of the last push (host copy; -1: unknown)
-    std::vector<int> owner;        // global tiles
-};
-
-#define HALO_HDR 16                /* values (128 B) of header in front of each halo message; [0] = leaver count to that side */
-#define REQUIRE(cond, code, ...) do { if (!(cond)) { mpic_set_error(__VA_ARGS__); return code; } } while (0)
-#define TRY(expr) do { int _r = (expr); if (_r) return _r; } while (0)
+#include "sim.cuh"
 
 extern "C" {
 
@@ -288,9 +251,11 @@ int mpic_create(const mpic_params* p, mpic_sim** out) {
 }
 
 int mpic_destroy(mpic_sim* s) {
+    if (s) cudaSetDevice(s->prm.device);
     if (!s) return 0;
     cudaSetDevice(s->prm.device);
     if (s->st) cudaStreamSynchronize(s->st);
+    mpic_ring_release(s);
     cudaFree(s->planes); cudaFree(s->jacc); cudaFree(s->rho); cudaFree(s->d_scratch);
     for (int k = 0; k < 2; k++) { cudaFree(s->pa[k].x); cudaFree(s->pa[k].tag); }
     cudaFree(s->cell_start); cudaFree(s->cell_count); cudaFree(s->scan_tmp);
@@ -300,10 +265,13 @@ int mpic_destroy(mpic_sim* s) {
     delete s;
     return 0;
 }
-int mpic_sync(mpic_sim* s) { REQUIRE(s, MPIC_EINVAL, "null handle"); CUDA_TRY(cudaStreamSynchronize(s->st)); return 0; }
+int mpic_sync(mpic_sim* s) {
+    if (s) cudaSetDevice(s->prm.device); REQUIRE(s, MPIC_EINVAL, "null handle"); CUDA_TRY(cudaStreamSynchronize(s->st)); return 0; }
 void* mpic_stream(mpic_sim* s) { return s ? (void*)s->st : nullptr; }
-int64_t mpic_kernel_launches(mpic_sim* s) { return s ? s->launches : 0; }
-int64_t mpic_num_particles(mpic_sim* s) { return s ? s->n : 0; }
+int64_t mpic_kernel_launches(mpic_sim* s) {
+    if (s) cudaSetDevice(s->prm.device); return s ? s->launches : 0; }
+int64_t mpic_num_particles(mpic_sim* s) {
+    if (s) cudaSetDevice(s->prm.device); return s ? s->n : 0; }
 
 // ------------------------------------------------------------------------------------------ fields
 static int refresh_all_guards(mpic_sim* s) {
@@ -312,6 +280,7 @@ static int refresh_all_guards(mpic_sim* s) {
     return 0;
 }
 int mpic_upload_planes(mpic_sim* s, const double* const planes[6]) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && planes, MPIC_EINVAL, "null argument");
     const FieldGeom& G = s->G;
     for (int p = 0; p < 6; p++)
@@ -322,6 +291,7 @@ int mpic_upload_planes(mpic_sim* s, const double* const planes[6]) {
     return 0;
 }
 int mpic_download_planes(mpic_sim* s, double* const planes[6]) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && planes, MPIC_EINVAL, "null argument");
     const FieldGeom& G = s->G;
     for (int p = 0; p < 6; p++)
@@ -343,6 +313,7 @@ static int tile_lists(mpic_sim* s, const int* gids, int ntiles, int** d_lists) {
     return 0;
 }
 int mpic_upload_tiles(mpic_sim* s, const double* grid6, const int* gids, int ntiles) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && grid6 && gids && ntiles >= 0, MPIC_EINVAL, "bad argument");
     if (!ntiles) return 0;
     int* lists = nullptr;
@@ -359,6 +330,7 @@ int mpic_upload_tiles(mpic_sim* s, const double* grid6, const int* gids, int nti
     return r;
 }
 int mpic_download_tiles(mpic_sim* s, double* grid6, const int* gids, int ntiles) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && grid6 && gids && ntiles >= 0, MPIC_EINVAL, "bad argument");
     if (!ntiles) return 0;
     int* lists = nullptr;
@@ -375,6 +347,7 @@ int mpic_download_tiles(mpic_sim* s, double* grid6, const int* gids, int ntiles)
 }
 
 int mpic_step_b_half(mpic_sim* s) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s, MPIC_EINVAL, "null handle");
     TRY(launch_b_sweep(s->G, s->planes, s->cf, s->st));
     s->launches++;
@@ -386,10 +359,12 @@ static int e_sweep(mpic_sim* s, int with_j) {
     return 0;
 }
 int mpic_step_e_full(mpic_sim* s) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s, MPIC_EINVAL, "null handle");
-    return e_sweep(s, s->n > 0);
+    return e_sweep(s, s->cap > 0);      // J may have arrived from a neighbour slab even if this one holds no particle
 }
 int mpic_field_steps(mpic_sim* s, int nsteps) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && nsteps >= 0, MPIC_EINVAL, "bad argument");
     REQUIRE(s->prm.nranks == 1, MPIC_ESTATE, "mpic_field_steps needs a single slab; drive the phases + halos from the host for nranks>1");
     for (int k = 0; k < nsteps; k++) {
@@ -399,13 +374,15 @@ int mpic_field_steps(mpic_sim* s, int nsteps) {
     }
     return 0;
 }
-int mpic_field_steps_fused(mpic_sim* s, int nsteps) { return mpic_field_steps(s, nsteps); }   // fused kernel: see round notes
+int mpic_field_steps_fused(mpic_sim* s, int nsteps) {
+    if (s) cudaSetDevice(s->prm.device); return mpic_field_steps(s, nsteps); }   // fused kernel: see round notes
 
 // ------------------------------------------------------------------------------------------ halos
 static double* halo_base(mpic_sim* s, int which) {
     return which == 2 ? (double*)s->jacc : s->planes + (which == 1 ? 3 * s->G.plane : 0);
 }
 int mpic_halo_describe(mpic_sim* s, mpic_halo_desc* out) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && out, MPIC_EINVAL, "bad argument");
     REQUIRE(s->halo_send, MPIC_ESTATE, "halos exist only for nranks > 1");
     for (int d = 0; d < 2; d++) { out->send[d] = s->halo_send + d * s->halo_side; out->recv[d] = s->halo_recv + d * s->halo_side; }
@@ -416,6 +393,7 @@ __global__ void halo_header_kernel(double* send, int64_t side_stride, const int*
     if (threadIdx.x < 2) ((long long*)(send + threadIdx.x * side_stride))[0] = leave_count[threadIdx.x];
 }
 int mpic_halo_pack(mpic_sim* s, int which) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && which >= 0 && which <= 2, MPIC_EINVAL, "bad argument");
     REQUIRE(s->halo_send, MPIC_ESTATE, "halos exist only for nranks > 1");
     TRY(launch_halo_pack(s->G, halo_base(s, which), which == 2, s->halo_send + HALO_HDR, s->halo_side, s->st));
@@ -424,6 +402,7 @@ int mpic_halo_pack(mpic_sim* s, int which) {
     return 0;
 }
 int mpic_halo_unpack(mpic_sim* s, int which) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && which >= 0 && which <= 2, MPIC_EINVAL, "bad argument");
     REQUIRE(s->halo_recv, MPIC_ESTATE, "halos exist only for nranks > 1");
     TRY(launch_halo_unpack(s->G, halo_base(s, which), which == 2, s->halo_recv + HALO_HDR, s->halo_side, s->st));
@@ -434,6 +413,7 @@ int mpic_halo_unpack(mpic_sim* s, int which) {
 
 // ------------------------------------------------------------------------------------------ particle migration between slabs
 int mpic_migration_describe(mpic_sim* s, mpic_migr_desc* out) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && out, MPIC_EINVAL, "bad argument");
     REQUIRE(s->lv.rec[0], MPIC_ESTATE, "migration buffers exist only for nranks > 1 with particle storage");
     for (int d = 0; d < 2; d++) { out->send[d] = s->lv.rec[d]; out->recv[d] = s->arrive[d]; }
@@ -441,6 +421,7 @@ int mpic_migration_describe(mpic_sim* s, mpic_migr_desc* out) {
     return 0;
 }
 int mpic_migration_counts(mpic_sim* s, int leave[2], int arrive[2]) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && leave && arrive, MPIC_EINVAL, "bad argument");
     REQUIRE(s->lv.rec[0], MPIC_ESTATE, "migration buffers exist only for nranks > 1 with particle storage");
     long long hdr[2];
@@ -458,6 +439,7 @@ int mpic_migration_counts(mpic_sim* s, int leave[2], int arrive[2]) {
     return 0;
 }
 int mpic_migration_absorb(mpic_sim* s, int n_from_lo, int n_from_hi) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && n_from_lo >= 0 && n_from_hi >= 0, MPIC_EINVAL, "bad argument");
     REQUIRE(s->lv.rec[0], MPIC_ESTATE, "migration buffers exist only for nranks > 1 with particle storage");
     REQUIRE(s->n + s->arrived + n_from_lo + n_from_hi <= s->cap, MPIC_ENOMEM, "particle capacity exceeded by arrivals");
@@ -499,6 +481,7 @@ static int sort_all(mpic_sim* s, bool counted) {
 }
 int mpic_upload_particles(mpic_sim* s, int64_t n, const double* x, const double* y, const double* ux, const double* uy,
                           const double* uz, const double* q, const int* tag) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && n >= 0, MPIC_EINVAL, "bad argument");
     REQUIRE(n <= s->cap, MPIC_ENOMEM, "particle capacity %lld exceeded (%lld)", (long long)s->cap, (long long)n);
     Particles& p = s->pa[s->cur];
@@ -512,6 +495,7 @@ int mpic_upload_particles(mpic_sim* s, int64_t n, const double* x, const double*
 }
 int mpic_download_particles(mpic_sim* s, int64_t cap, double* x, double* y, double* ux, double* uy, double* uz, double* q,
                             int* tag, int64_t* n_out) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s, MPIC_EINVAL, "null handle");
     REQUIRE(cap >= s->n, MPIC_ENOMEM, "host buffers too small");
     Particles& p = s->pa[s->cur];
@@ -525,6 +509,7 @@ int mpic_download_particles(mpic_sim* s, int64_t cap, double* x, double* y, doub
 }
 int mpic_load_uniform(mpic_sim* s, int ppc, double u_th, double d0, double d1, double d2, double two_stream, double density,
                       double band_lo, double band_hi, uint64_t seed, int append) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && ppc > 0 && s->cap > 0, MPIC_EINVAL, "bad argument");
     const PicConst& P = s->P;
     int lo = (int)nearbyint(band_lo * P.ny), hi = (int)nearbyint(band_hi * P.ny);
@@ -544,6 +529,7 @@ int mpic_load_uniform(mpic_sim* s, int ppc, double u_th, double d0, double d1, d
 }
 
 int mpic_push_deposit(mpic_sim* s) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && s->cap > 0, MPIC_ESTATE, "no particle storage");
     REQUIRE(s->arrived == 0, MPIC_ESTATE, "arrivals absorbed but not sorted in: call mpic_sort_tiles before the next push");
     CUDA_TRY(cudaMemsetAsync(s->cell_count, 0, (size_t)s->n_entries * 4, s->st));
@@ -556,6 +542,7 @@ int mpic_push_deposit(mpic_sim* s) {
     return 0;
 }
 int mpic_sort_tiles(mpic_sim* s) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && s->cap > 0, MPIC_ESTATE, "no particle storage");
     return sort_all(s, true);      // reuses the histogram the push produced when there is one
 }
@@ -565,6 +552,7 @@ static int fold_current(mpic_sim* s) {
     return 0;
 }
 int mpic_pic_steps(mpic_sim* s, int nsteps) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && nsteps >= 0, MPIC_EINVAL, "bad argument");
     REQUIRE(s->cap > 0, MPIC_ESTATE, "no particle storage");
     REQUIRE(s->prm.nranks == 1, MPIC_ESTATE, "mpic_pic_steps needs a single slab; drive phases + halos from the host for nranks>1");
@@ -580,6 +568,7 @@ int mpic_pic_steps(mpic_sim* s, int nsteps) {
 }
 int mpic_pic_steps_host(mpic_sim* s, int nsteps, double* const planes[6], int64_t n, double* x, double* y, double* ux,
                         double* uy, double* uz, double* q, int* tag, int64_t* n_out) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && planes, MPIC_EINVAL, "bad argument");
     const FieldGeom& G = s->G;
     for (int p = 0; p < 6; p++)
@@ -595,6 +584,7 @@ int mpic_pic_steps_host(mpic_sim* s, int nsteps, double* const planes[6], int64_
 }
 
 int mpic_get_tile_counts(mpic_sim* s, int* counts) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && counts && s->cap > 0, MPIC_EINVAL, "bad argument");
     const int nt = s->P.ltr * s->P.gtc;
     int* d;
@@ -607,6 +597,7 @@ int mpic_get_tile_counts(mpic_sim* s, int* counts) {
     return r;
 }
 int mpic_get_particle_tile_index(mpic_sim* s, int* gid) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && gid && s->cap > 0, MPIC_EINVAL, "bad argument");
     if (!s->n) return 0;
     int* d;
@@ -619,6 +610,7 @@ int mpic_get_particle_tile_index(mpic_sim* s, int* gid) {
     return r;
 }
 int mpic_download_current(mpic_sim* s, int64_t* const jplanes[3]) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && jplanes, MPIC_EINVAL, "bad argument");
     const FieldGeom& G = s->G;
     for (int p = 0; p < 3; p++)
@@ -627,9 +619,11 @@ int mpic_download_current(mpic_sim* s, int64_t* const jplanes[3]) {
     CUDA_TRY(cudaStreamSynchronize(s->st));
     return 0;
 }
-int mpic_fold_current(mpic_sim* s) { REQUIRE(s, MPIC_EINVAL, "null handle"); return fold_current(s); }
+int mpic_fold_current(mpic_sim* s) {
+    if (s) cudaSetDevice(s->prm.device); REQUIRE(s, MPIC_EINVAL, "null handle"); return fold_current(s); }
 
 int mpic_diagnostics(mpic_sim* s, double out[5]) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && out, MPIC_EINVAL, "bad argument");
     const FieldGeom& G = s->G;
     CUDA_TRY(cudaMemsetAsync(s->d_scratch, 0, 64, s->st));
@@ -663,12 +657,37 @@ int mpic_diagnostics(mpic_sim* s, double out[5]) {
     return 0;
 }
 
+int mpic_dump_fields(mpic_sim* s, const char* filename, int rank) {
+    if (s) cudaSetDevice(s->prm.device);
+    REQUIRE(s && filename, MPIC_EINVAL, "bad argument");
+    const int gtc = s->P.gtc;
+    std::vector<int> gids, rows, cols, cur;
+    for (int r = s->prm.row0; r < s->prm.row0 + s->prm.nrows; r++)
+        for (int c = 0; c < gtc; c++) {
+            const int gid = r * gtc + c;
+            if (rank >= 0 && s->owner[gid] != rank) continue;
+            gids.push_back(gid); rows.push_back(r); cols.push_back(c); cur.push_back(s->owner[gid]);
+        }
+    const size_t per = (size_t)(s->P.tnx + 4) * (s->P.tny + 4) * 6;
+    std::vector<double> grid(per * gids.size());
+    if (!gids.empty()) TRY(mpic_download_tiles(s, grid.data(), gids.data(), (int)gids.size()));
+    return mpic_save_rank_data(filename, (int)gids.size(), gids.data(), rows.data(), cols.data(), cur.data(), s->P.tnx, s->P.tny,
+                               s->prm.guard, grid.data());
+}
+
 int mpic_get_owner(mpic_sim* s, int* owner) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && owner, MPIC_EINVAL, "bad argument");
     memcpy(owner, s->owner.data(), s->owner.size() * sizeof(int));
     return 0;
 }
+int mpic_set_owner(mpic_sim* s, const int* owner) {
+    REQUIRE(s && owner, MPIC_EINVAL, "bad argument");
+    memcpy(s->owner.data(), owner, s->owner.size() * sizeof(int));
+    return 0;
+}
 int mpic_migrate_tile(mpic_sim* s, int gid, int dest) {
+    if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && gid >= 0 && gid < (int)s->owner.size() && dest >= 0, MPIC_EINVAL, "bad tile/rank");
     s->owner[gid] = dest;     // on one device the fields and particles of the tile do not move
     return 0;

@@ -1,0 +1,46 @@
+// sim.cuh -- the handle behind mpic_sim* and the small macros shared by api.cu and ring.cu (internal).
+#pragma once
+#include "common.cuh"
+#include <vector>
+
+struct mpic_sim {
+    mpic_params prm;
+    FieldGeom G;
+    PicConst P;
+    YeeCoef cf;
+    cudaStream_t st = nullptr;
+    double* planes = nullptr;      // 6 field planes
+    int64_t* jacc = nullptr;       // 3 current accumulators
+    int64_t* rho = nullptr;        // 1 plane, diagnostics only (lazy)
+    Particles pa[2] = {};
+    int cur = 0;
+    int64_t n = 0, cap = 0;
+    int* cell_start = nullptr;     // n_entries + 1
+    int* cell_count = nullptr;     // n_entries (doubles as scatter cursor)
+    int* scan_tmp = nullptr;
+    int n_entries = 0;             // ncells + 2 (leave-down, leave-up bins)
+    CUtensorMap tmap;
+    bool has_tmap = false;
+    double* d_scratch = nullptr;   // 8 doubles
+    int64_t tag_base = 0;
+    int64_t launches = 0;
+    int push_split = 4;
+    int nsm = 148;
+    bool counts_valid = false;     // cell_count holds the destination-cell histogram of the last push
+    // ---- slab plumbing (nranks > 1)
+    double* halo_send = nullptr;   // [2 sides][HALO_HDR + 3*g*pitch] values
+    double* halo_recv = nullptr;
+    int64_t halo_side = 0;         // values per side
+    LeaveBufs lv = {};             // leaver records written by the push kernel
+    double* arrive[2] = {};        // records received from the lower / upper neighbour
+    int64_t arrived = 0;           // records absorbed into the tail [n, n+arrived) and not yet sorted in
+    int64_t left = -1;             // leavers of the last push (host copy; -1: unknown)
+    std::vector<int> owner;        // global tiles
+    void* ring_events = nullptr;   // ring.cu: per-handle events of the single-process peer-copy ring
+};
+
+void mpic_ring_release(mpic_sim* s);
+#define HALO_HDR 16                /* values (128 B) of header in front of each halo message; [0] = leaver count to that side */
+#define REQUIRE(cond, code, ...) do { if (!(cond)) { mpic_set_error(__VA_ARGS__); return code; } } while (0)
+#define TRY(expr) do { int _r = (expr); if (_r) return _r; } while (0)
+

@@ -120,6 +120,49 @@ def test_field_only_slabs_match_reference_loop_fixture():
         assert np.array_equal(tiles, f["tiles"][gids])
 
 
+@pytest.mark.parametrize("world,shape", [(2, (64, 64, 16, 6, 0.6)), (3, (48, 96, 8, 5, 0.9)), (5, (32, 80, 16, 3, 0.7))])
+def test_single_process_peer_copy_ring_bit_exact(world, shape):
+    """csrc/ring.cu (the C++ driver's multi-GPU path): N handles, one host thread, peer copies ordered by events.
+    Uses every visible GPU round-robin (all handles share the device on a one-GPU box)."""
+    import torch
+    m = pkg()
+    nx, ny, tn, ppc, u_th = shape
+    dx, dy, dt, parts, planes = _problem(nx, ny, tn, ppc, u_th, seed=17)
+    ndev = max(1, torch.cuda.device_count())
+    sims = [m.Sim(nx, ny, tn, tn, dx, dy, dt, max_particles=parts["x"].shape[0], rank=r, nranks=world, device=r % ndev)
+            for r in range(world)]
+    for s in sims:
+        r0, r1 = s.row0 * tn, (s.row0 + s.nrows) * tn
+        s.upload_planes([a[r0:r1] for a in planes])
+        s.upload_particles(parts)
+    ring = m.SlabRing(sims)
+    ring.refresh_guards()
+    steps = 9
+    ring.pic_steps(steps)
+    ring.sync()
+    lib = ob.load_oracle()
+    P = ob.make_params(lib, nx, ny, tn, tn, dx, dy, dt)
+    want, wf = copy_parts(parts), [a.copy() for a in planes]
+    counts, _ = ob.pic_steps(lib, P, wf, want, steps)
+    got = by_tag({k: np.concatenate([s.download_particles()[k] for s in sims]) for k in ("x", "y", "ux", "uy", "uz", "q", "tag")})
+    want = by_tag(want)
+    assert np.array_equal(got["tag"], want["tag"])
+    for k in ("x", "y", "ux", "uy", "uz", "q"):
+        assert np.array_equal(got[k], want[k]), k
+    for k in range(6):
+        assert np.array_equal(np.concatenate([s.download_planes()[k] for s in sims]), wf[k]), k
+    assert np.array_equal(np.concatenate([s.tile_counts() for s in sims]), counts)
+    # field-only ring == single-slab field loop
+    one = m.Sim(nx, ny, tn, tn, dx, dy, dt)
+    one.upload_planes(wf)
+    one.field_steps(5)
+    ring.field_steps(5)
+    ring.sync()
+    ref = one.download_planes()
+    for k in range(6):
+        assert np.array_equal(np.concatenate([s.download_planes()[k] for s in sims]), ref[k]), k
+
+
 def test_nccl_slabs_two_processes():
     import torch
     if torch.cuda.device_count() < 2:
