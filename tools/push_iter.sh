@@ -1,3 +1,3 @@
-# one tuning iteration of the push kernel on the GPU box: parity, timing, instruction count
-timeout 300 python -m pytest tests/test_gpu_pic.py -m gpu -x -q 2>&1 | tail -2
-timeout 100 python bench.py --steps 10 --warmup 3 --no-yee --no-cpu --no-e2e > gpurun_out/plain.log 2>&1 && python -c "import json; d=json.loads(open('gpurun_out/plain.log').read().strip().splitlines()[-1]); print(d['phases_ms'], d['roofline']['frac'])" && timeout 300 ncu --metrics gpu__time_duration.sum,smsp__inst_executed.sum,smsp__issue_active.avg.pct_of_peak_sustained_active,sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active,sm__warps_active.avg.pct_of_peak_sustained_active --clock-control none -k regex:push_deposit -s 4 -c 1 python bench.py --steps 10 --warmup 3 --no-yee --no-cpu --no-e2e 2>&1 | grep -E "duration|inst_executed|issue_active|fp64|warps_active"
+# one tuning iteration of the push kernel on the GPU box: parity, then timing in the bimodal / sustained / thermal regimes
+timeout 600 python -m pytest tests/test_gpu_pic.py tests/test_gpu_slab.py -m gpu -x -q 2>&1 | tail -2
+timeout 300 python tools/push_gap.py 2>&1 | cut -c1-420 | tee gpurun_out/push_gap.log
