@@ -211,6 +211,8 @@ int mpic_create(const mpic_params* p, mpic_sim** out) {
         CUDA_TRY(cudaMalloc(&s->cell_start, (size_t)(s->n_entries + 1) * 4));
         CUDA_TRY(cudaMalloc(&s->cell_count, (size_t)s->n_entries * 4));
         CUDA_TRY(cudaMalloc(&s->scan_tmp, (size_t)(s->n_entries / 2048 + 2) * 4));
+        CUDA_TRY(cudaMalloc(&s->keys, (size_t)s->cap * 4));
+        CUDA_TRY(cudaMalloc(&s->perm, (size_t)s->cap * 4));
         CUDA_TRY(cudaMemsetAsync(s->cell_start, 0, (size_t)(s->n_entries + 1) * 4, s->st));
         TRY(make_tensor_map(s));
         // enough CTAs per tile that the grid covers >= 4 waves of 2 CTAs/SM even for few tiles
@@ -258,7 +260,7 @@ int mpic_destroy(mpic_sim* s) {
     mpic_ring_release(s);
     cudaFree(s->planes); cudaFree(s->jacc); cudaFree(s->rho); cudaFree(s->d_scratch);
     for (int k = 0; k < 2; k++) { cudaFree(s->pa[k].x); cudaFree(s->pa[k].tag); }
-    cudaFree(s->cell_start); cudaFree(s->cell_count); cudaFree(s->scan_tmp);
+    cudaFree(s->cell_start); cudaFree(s->cell_count); cudaFree(s->scan_tmp); cudaFree(s->keys); cudaFree(s->perm);
     cudaFree(s->halo_send); cudaFree(s->halo_recv); cudaFree(s->lv.count);
     for (int d = 0; d < 2; d++) { cudaFree(s->lv.rec[d]); cudaFree(s->arrive[d]); }
     if (s->st) cudaStreamDestroy(s->st);
@@ -445,29 +447,48 @@ int mpic_migration_absorb(mpic_sim* s, int n_from_lo, int n_from_hi) {
     REQUIRE(s->n + s->arrived + n_from_lo + n_from_hi <= s->cap, MPIC_ENOMEM, "particle capacity exceeded by arrivals");
     REQUIRE(s->counts_valid, MPIC_ESTATE, "mpic_migration_absorb must follow mpic_push_deposit");
     // arrivals are appended in (source rank order: lower, upper; source order) -- SURVEY.md B.8
-    TRY(launch_absorb(s->P, s->pa[s->cur], s->n + s->arrived, s->arrive[0], n_from_lo, s->cell_count, s->st));
+    TRY(launch_absorb(s->P, s->pa[s->cur], s->n + s->arrived, s->arrive[0], n_from_lo, s->cell_count, s->keys, s->st));
     s->arrived += n_from_lo;
-    TRY(launch_absorb(s->P, s->pa[s->cur], s->n + s->arrived, s->arrive[1], n_from_hi, s->cell_count, s->st));
+    TRY(launch_absorb(s->P, s->pa[s->cur], s->n + s->arrived, s->arrive[1], n_from_hi, s->cell_count, s->keys, s->st));
     s->arrived += n_from_hi;
     s->launches += (n_from_lo > 0) + (n_from_hi > 0);
     return 0;
 }
 
 // ------------------------------------------------------------------------------------------ particles
+// physical reorder on demand: after this pa[cur][0..n) is itself in sorted order
+static int materialise(mpic_sim* s) {
+    if (!s->perm_valid) return 0;
+    TRY(launch_gather(s->pa[s->cur], s->pa[s->cur ^ 1], s->perm, s->n, s->st));
+    s->launches++;
+    s->cur ^= 1;
+    s->perm_valid = false;
+    return 0;
+}
+// counted (after a push): the push/absorb kernels left the destination-key histogram in cell_count and every stored
+// particle's key in keys[] -> scan + permutation build, no particle data moves (the next push gathers through perm).
+// Otherwise (uploads, loads): count from the stored positions, scan, physical scatter.
 static int sort_all(mpic_sim* s, bool counted) {
     counted = counted && s->counts_valid;
     s->counts_valid = false;
     if (!counted) {
+        if (s->perm_valid && s->arrived == 0) return 0;          // already sorted, nothing new
+        TRY(materialise(s));
         CUDA_TRY(cudaMemsetAsync(s->cell_count, 0, (size_t)s->n_entries * 4, s->st));
         TRY(launch_count_keys(s->P, s->pa[s->cur], 0, s->n + s->arrived, s->cell_count, nullptr, s->st));
         s->launches++;
     }
     const int64_t total = s->n + s->arrived;
     TRY(launch_scan_cells(s->cell_count, s->cell_start, s->n_entries, s->scan_tmp, s->st));
-    TRY(launch_scatter(s->P, s->pa[s->cur], s->pa[s->cur ^ 1], total, s->cell_start, s->cell_count, s->st));
+    if (counted) {
+        TRY(launch_perm_build(s->P, s->keys, total, s->cell_count, s->perm, s->st));
+        s->perm_valid = true;
+    } else {
+        TRY(launch_scatter(s->P, s->pa[s->cur], s->pa[s->cur ^ 1], total, s->cell_start, s->cell_count, s->st));
+        s->cur ^= 1;
+    }
     s->launches += 4;
-    s->cur ^= 1;
-    if (s->prm.nranks > 1) {       // particles whose key is a leaver bin were dropped by the scatter
+    if (s->prm.nranks > 1) {       // particles whose key is a leaver bin are dropped by the scatter / not entered in perm
         if (counted && s->left >= 0) s->n = total - s->left;
         else {
             int kept = 0;
@@ -484,6 +505,7 @@ int mpic_upload_particles(mpic_sim* s, int64_t n, const double* x, const double*
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && n >= 0, MPIC_EINVAL, "bad argument");
     REQUIRE(n <= s->cap, MPIC_ENOMEM, "particle capacity %lld exceeded (%lld)", (long long)s->cap, (long long)n);
+    s->perm_valid = false; s->counts_valid = false; s->arrived = 0;
     Particles& p = s->pa[s->cur];
     const double* src[6] = { x, y, ux, uy, uz, q };
     double* dst[6] = { p.x, p.y, p.ux, p.uy, p.uz, p.q };
@@ -498,6 +520,7 @@ int mpic_download_particles(mpic_sim* s, int64_t cap, double* x, double* y, doub
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s, MPIC_EINVAL, "null handle");
     REQUIRE(cap >= s->n, MPIC_ENOMEM, "host buffers too small");
+    TRY(materialise(s));
     Particles& p = s->pa[s->cur];
     double* dst[6] = { x, y, ux, uy, uz, q };
     const double* src[6] = { p.x, p.y, p.ux, p.uy, p.uz, p.q };
@@ -515,7 +538,9 @@ int mpic_load_uniform(mpic_sim* s, int ppc, double u_th, double d0, double d1, d
     int lo = (int)nearbyint(band_lo * P.ny), hi = (int)nearbyint(band_hi * P.ny);
     REQUIRE(lo >= 0 && hi <= P.ny && lo <= hi, MPIC_EINVAL, "bad band");
     const int64_t tag0 = append ? s->tag_base : 0;
-    if (!append) { s->n = 0; s->tag_base = 0; }
+    if (!append) { s->n = 0; s->tag_base = 0; s->perm_valid = false; }
+    TRY(materialise(s));
+    s->counts_valid = false;
     const int slo = lo > P.cy0 ? lo : P.cy0, shi = hi < P.cy0 + P.nyl ? hi : P.cy0 + P.nyl;
     const int64_t nsel = shi > slo ? (int64_t)(shi - slo) * P.nx : 0;
     REQUIRE(s->n + nsel * ppc <= s->cap, MPIC_ENOMEM, "particle capacity exceeded");
@@ -535,9 +560,11 @@ int mpic_push_deposit(mpic_sim* s) {
     CUDA_TRY(cudaMemsetAsync(s->cell_count, 0, (size_t)s->n_entries * 4, s->st));
     if (s->prm.nranks > 1) CUDA_TRY(cudaMemsetAsync(s->lv.count, 0, 2 * sizeof(int), s->st));
     s->left = s->prm.nranks > 1 ? -1 : 0;
-    TRY(launch_push_deposit(s->P, s->G, &s->tmap, s->jacc, s->pa[s->cur], s->cell_start, s->cell_count, s->push_split,
-                            s->lv, s->st));
+    TRY(launch_push_deposit(s->P, s->G, &s->tmap, s->jacc, s->pa[s->cur], s->pa[s->cur ^ 1], s->perm_valid ? s->perm : nullptr,
+                            s->cell_start, s->cell_count, s->keys, s->push_split, s->lv, s->st));
     s->launches++;
+    s->cur ^= 1;                    // the push wrote the other buffer in slot order
+    s->perm_valid = false;
     s->counts_valid = true;
     return 0;
 }
@@ -600,6 +627,7 @@ int mpic_get_particle_tile_index(mpic_sim* s, int* gid) {
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && gid && s->cap > 0, MPIC_EINVAL, "bad argument");
     if (!s->n) return 0;
+    TRY(materialise(s));
     int* d;
     CUDA_TRY(cudaMalloc(&d, (size_t)s->n * 4));
     int r = launch_particle_tiles(s->P, s->pa[s->cur], s->n, s->prm.row0, d, s->st);
@@ -632,6 +660,7 @@ int mpic_diagnostics(mpic_sim* s, double out[5]) {
     double h[8] = { 0 };
     double mean_rho = 0.0;
     if (s->cap > 0 && s->n > 0) {
+        TRY(materialise(s));
         TRY(launch_kinetic(s->pa[s->cur], s->n, s->d_scratch + 1, s->st));
         if (!s->rho) CUDA_TRY(cudaMalloc(&s->rho, (size_t)G.plane * 8));
         CUDA_TRY(cudaMemsetAsync(s->rho, 0, (size_t)G.plane * 8, s->st));

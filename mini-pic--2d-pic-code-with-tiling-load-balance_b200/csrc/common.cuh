@@ -95,9 +95,13 @@ int launch_gauss_residual(const FieldGeom& G, const double* planes, const int64_
                           double inv_dy, double* out_max, cudaStream_t st);
 
 // ---- kernel launchers implemented in particles.cu
-int launch_push_deposit(const PicConst& P, const FieldGeom& G, const CUtensorMap* tmap, int64_t* jacc, Particles p,
-                        const int* cell_start, int* cell_count_new, int split, LeaveBufs lv, cudaStream_t st);
-int launch_absorb(const PicConst& P, Particles p, int64_t first, const double* rec, int n, int* cell_count, cudaStream_t st);
+int launch_push_deposit(const PicConst& P, const FieldGeom& G, const CUtensorMap* tmap, int64_t* jacc, Particles src,
+                        Particles dst, const int* perm, const int* cell_start, int* cell_count_new, int* keys, int split,
+                        LeaveBufs lv, cudaStream_t st);
+int launch_perm_build(const PicConst& P, const int* keys, int64_t n, int* cursor, int* perm, cudaStream_t st);
+int launch_gather(Particles src, Particles dst, const int* perm, int64_t n, cudaStream_t st);
+int launch_absorb(const PicConst& P, Particles p, int64_t first, const double* rec, int n, int* cell_count, int* keys,
+                  cudaStream_t st);
 int launch_count_keys(const PicConst& P, Particles p, int64_t first, int64_t n, int* cell_count, int* key_out, cudaStream_t st);
 int launch_scan_cells(int* cell_count, int* cell_start, int n_entries, int* block_tmp, cudaStream_t st);
 int launch_scatter(const PicConst& P, Particles src, Particles dst, int64_t n, const int* cell_start, int* cursor, cudaStream_t st);

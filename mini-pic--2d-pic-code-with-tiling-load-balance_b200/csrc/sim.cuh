@@ -27,6 +27,10 @@ struct mpic_sim {
     int push_split = 4;
     int nsm = 148;
     bool counts_valid = false;     // cell_count holds the destination-cell histogram of the last push
+    int* keys = nullptr;           // cap: destination key of every stored particle (written by the push / absorb kernels)
+    int* perm = nullptr;           // cap: slot of the sorted order -> storage index in pa[cur]
+    bool perm_valid = false;       // true: the sorted order is pa[cur] READ THROUGH perm (the sort moved no data; the next push
+                                   // gathers); false: pa[cur][0..n) is itself in sorted order
     // ---- slab plumbing (nranks > 1)
     double* halo_send = nullptr;   // [2 sides][HALO_HDR + 3*g*pitch] values
     double* halo_recv = nullptr;

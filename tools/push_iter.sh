@@ -1,3 +1,3 @@
 # one tuning iteration of the push kernel on the GPU box: parity, then timing in the bimodal / sustained / thermal regimes
-timeout 600 python -m pytest tests/test_gpu_pic.py tests/test_gpu_slab.py -m gpu -x -q 2>&1 | tail -2
+timeout 900 python -m pytest tests/test_gpu_pic.py tests/test_gpu_slab.py -m gpu -x -q 2>&1 | tail -3
 timeout 300 python tools/push_gap.py 2>&1 | cut -c1-420 | tee gpurun_out/push_gap.log
