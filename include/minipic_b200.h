@@ -204,6 +204,9 @@ int mpic_pic_steps_host(mpic_sim* s, int nsteps, double* const planes[6], int64_
                         double* uy, double* uz, double* q, int* tag, int64_t* n_out);
 
 /* ---- counters for the harness */
+/* Device self-test: the push kernel's branch-free 1/sqrt(x) and a/b sequences against the compiler's IEEE sqrt/division
+ * on n pseudo-random arguments of the range the push uses; *mismatches must come back 0.  (No reference counterpart.) */
+int mpic_selftest_math(int64_t n, uint64_t seed, int64_t* mismatches);
 int64_t mpic_kernel_launches(mpic_sim* s);   /* kernels launched by this handle so far */
 
 #ifdef __cplusplus

@@ -94,6 +94,7 @@ def lib():
         getattr(L, name).argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int]
     L.mpic_set_owner.argtypes = [C.c_void_p, c_ip]
     L.mpic_slab_rows.argtypes = [C.c_int, C.c_int, C.c_int, c_ip, c_ip]
+    L.mpic_selftest_math.argtypes = [C.c_int64, C.c_uint64, c_lp]
     _lib = L
     return L
 
@@ -334,6 +335,13 @@ class Sim:
 
 
 # ---- L0 compat (one tile, host buffers): Field_update.h:36,54 and Auxiliar_functions.h:68-69
+def selftest_math(n, seed=1):
+    """Mismatches between the push kernel's branch-free 1/sqrt, a/b sequences and the compiler's IEEE ones (must be 0)."""
+    bad = C.c_int64(-1)
+    _chk(lib().mpic_selftest_math(int(n), int(seed), C.byref(bad)))
+    return bad.value
+
+
 def update_b_half(E3, Bold3, Bnew3, tnx, tny, guard, dt, dx, dy):
     _chk(lib().mpic_update_b_half(_dp(E3), _dp(Bold3), _dp(Bnew3), tnx, tny, guard, dt, dx, dy))
 

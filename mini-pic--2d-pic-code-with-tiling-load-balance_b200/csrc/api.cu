@@ -484,7 +484,7 @@ static int sort_all(mpic_sim* s, bool counted) {
         TRY(launch_perm_build(s->P, s->keys, total, s->cell_count, s->perm, s->st));
         s->perm_valid = true;
     } else {
-        TRY(launch_scatter(s->P, s->pa[s->cur], s->pa[s->cur ^ 1], total, s->cell_start, s->cell_count, s->st));
+        TRY(launch_scatter(s->P, s->pa[s->cur], s->pa[s->cur ^ 1], total, s->perm, s->cell_count, s->st));
         s->cur ^= 1;
     }
     s->launches += 4;
@@ -557,10 +557,11 @@ int mpic_push_deposit(mpic_sim* s) {
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && s->cap > 0, MPIC_ESTATE, "no particle storage");
     REQUIRE(s->arrived == 0, MPIC_ESTATE, "arrivals absorbed but not sorted in: call mpic_sort_tiles before the next push");
+    REQUIRE(!s->counts_valid, MPIC_ESTATE, "particles moved but not re-sorted: call mpic_sort_tiles between pushes");
     CUDA_TRY(cudaMemsetAsync(s->cell_count, 0, (size_t)s->n_entries * 4, s->st));
     if (s->prm.nranks > 1) CUDA_TRY(cudaMemsetAsync(s->lv.count, 0, 2 * sizeof(int), s->st));
     s->left = s->prm.nranks > 1 ? -1 : 0;
-    TRY(launch_push_deposit(s->P, s->G, &s->tmap, s->jacc, s->pa[s->cur], s->pa[s->cur ^ 1], s->perm_valid ? s->perm : nullptr,
+    TRY(launch_push_deposit(s->P, s->G, &s->tmap, s->jacc, s->pa[s->cur], s->pa[s->cur ^ 1], s->perm,
                             s->cell_start, s->cell_count, s->keys, s->push_split, s->lv, s->st));
     s->launches++;
     s->cur ^= 1;                    // the push wrote the other buffer in slot order
@@ -702,6 +703,20 @@ int mpic_dump_fields(mpic_sim* s, const char* filename, int rank) {
     if (!gids.empty()) TRY(mpic_download_tiles(s, grid.data(), gids.data(), (int)gids.size()));
     return mpic_save_rank_data(filename, (int)gids.size(), gids.data(), rows.data(), cols.data(), cur.data(), s->P.tnx, s->P.tny,
                                s->prm.guard, grid.data());
+}
+
+int mpic_selftest_math(int64_t n, uint64_t seed, int64_t* mismatches) {
+    REQUIRE(n > 0 && mismatches, MPIC_EINVAL, "bad argument");
+    TRY(need_device());
+    unsigned long long* d;
+    CUDA_TRY(cudaMalloc(&d, 8));
+    CUDA_TRY(cudaMemset(d, 0, 8));
+    int r = launch_selftest_math(n, seed, d, 0);
+    unsigned long long h = 0;
+    if (!r) { cudaError_t e = cudaMemcpy(&h, d, 8, cudaMemcpyDeviceToHost); if (e != cudaSuccess) { mpic_set_error("selftest: %s", cudaGetErrorString(e)); r = MPIC_ECUDA; } }
+    cudaFree(d);
+    *mismatches = (int64_t)h;
+    return r;
 }
 
 int mpic_get_owner(mpic_sim* s, int* owner) {

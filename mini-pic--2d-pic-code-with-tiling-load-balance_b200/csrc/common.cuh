@@ -99,12 +99,12 @@ int launch_push_deposit(const PicConst& P, const FieldGeom& G, const CUtensorMap
                         Particles dst, const int* perm, const int* cell_start, int* cell_count_new, int* keys, int split,
                         LeaveBufs lv, cudaStream_t st);
 int launch_perm_build(const PicConst& P, const int* keys, int64_t n, int* cursor, int* perm, cudaStream_t st);
-int launch_gather(Particles src, Particles dst, const int* perm, int64_t n, cudaStream_t st);
+int launch_gather(Particles src, Particles dst, int* perm, int64_t n, cudaStream_t st);
 int launch_absorb(const PicConst& P, Particles p, int64_t first, const double* rec, int n, int* cell_count, int* keys,
                   cudaStream_t st);
 int launch_count_keys(const PicConst& P, Particles p, int64_t first, int64_t n, int* cell_count, int* key_out, cudaStream_t st);
 int launch_scan_cells(int* cell_count, int* cell_start, int n_entries, int* block_tmp, cudaStream_t st);
-int launch_scatter(const PicConst& P, Particles src, Particles dst, int64_t n, const int* cell_start, int* cursor, cudaStream_t st);
+int launch_scatter(const PicConst& P, Particles src, Particles dst, int64_t n, int* perm_identity_out, int* cursor, cudaStream_t st);
 int launch_tile_counts(const PicConst& P, const int* cell_start, int* counts, cudaStream_t st);
 int launch_particle_tiles(const PicConst& P, Particles p, int64_t n, int row0, int* gid, cudaStream_t st);
 int launch_kinetic(Particles p, int64_t n, double* out2, cudaStream_t st);
@@ -115,3 +115,4 @@ int launch_load_uniform(const PicConst& P, Particles p, int64_t first, int64_t n
 size_t push_smem_bytes(int tnx, int tny);
 void push_box_dims(int tnx, int tny, int* pw, int* ph);
 int launch_sum_i64(const int64_t* a, int64_t n, double* out, cudaStream_t st);
+int launch_selftest_math(int64_t n, uint64_t seed, unsigned long long* bad, cudaStream_t st);

@@ -154,3 +154,12 @@ def test_host_buffer_entry_point_matches_resident_path():
         assert np.array_equal(hp[k], want[k]), k
     for k in range(6):
         assert np.array_equal(hf[k], wf[k])
+
+
+@pytest.mark.gpu
+def test_branch_free_division_and_sqrt_are_ieee():
+    """The push kernel's transcribed fast-path sequences (1/sqrt(x), 2/x for x >= 1) must be bit-identical to the
+    compiler's IEEE sqrt.rn / div.rn on 2^31 pseudo-random arguments -- otherwise parity with the oracle's `/` and sqrt()
+    would only be statistical."""
+    for seed in (1, 0xC0FFEE):
+        assert pkg().selftest_math(1 << 30, seed) == 0
