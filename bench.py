@@ -3,8 +3,8 @@
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl native|reference] [--workload NAME]
 
-Native arm: one "step" = one full PIC iteration (gather+Boris push+deposit, J fold, half-B, E with -dt*J, half-B,
-per-cell count/scan/scatter sort) over the synthetic workload, state resident in HBM.  N=1 workload = BASELINE.json
+Native arm: one "step" = one full PIC iteration (gather+Boris push+deposit fused with the reorder, J fold, half-B, E with
+-dt*J, half-B, per-cell count/scan/permutation sort) over the synthetic workload, state resident in HBM.  N=1 workload = BASELINE.json
 configs[1] (two-stream, 512x512 cells, 64 ppc = 16.8 M particles, 0.87 GB of particle state >> 126 MB L2).  N>1: weak
 scaling, every rank owns a 512-row slab of a (512N x 512) domain (halo exchange, J reduce and particle migration over
 NCCL).  Prints ONE JSON line on rank 0.
@@ -35,8 +35,14 @@ WORKLOADS = {
     # configs[3] per-GPU share at 8 GPUs
     "uniform_2048": dict(nx=2048, ny=2048, tn=16, ppc=64, u_th=0.05, two_stream=0.0, dx=0.1),
 }
-PUSH_BYTES_PER_PARTICLE = 88.0     # read x,y,ux,uy,uz,q (48) + write x,y,ux,uy,uz (40); SURVEY.md section 8(d)
-SORT_BYTES_PER_PARTICLE = 120.0    # key pass reads x,y (16) + payload 52 read + 52 write
+# push_deposit_kernel is fused with the sort's data movement: it gathers every particle through the slot->storage
+# permutation and writes the other buffer in sorted order, so its algorithmic traffic is one full read + one full write
+# of the particle state: x,y,ux,uy,uz,q,tag = 52 B each way.  (SURVEY.md section 8(d) counts 88 B for an in-place push
+# PLUS 116 B for a separate reorder; the fused kernel replaces both.  `frac_88B` reports the stricter push-only figure.)
+PUSH_BYTES_PER_PARTICLE = 104.0
+PUSH_ONLY_BYTES = 88.0
+NCU_TRAFFIC_BYTES_PER_PARTICLE = 117.0   # measured: (1.041 GB read + 0.923 GB written) / 16.8 M particles
+SORT_BYTES_PER_PARTICLE = 8.0      # what is left of the sort: keys read (4) + permutation written (4); scan is per cell
 YEE_BYTES_3SWEEP = 216.0           # reference-faithful half-B, E, half-B: 3 x 72 B per cell
 YEE_BYTES_ALGO = 144.0             # SURVEY.md section 8(d) algorithmic figure (2 sweeps)
 
@@ -245,9 +251,12 @@ def main():
                    "l2": "particle state 0.87 GB per pass >> 126 MB L2 (no flush needed)"},
         "phases_ms": {"push_deposit": push_ms, "fields_and_fold": field_ms, "sort": sort_ms},
         "roofline": {"bound": "hbm", "kernel": "push_deposit_kernel", "achieved": push_gbs, "peak": peak, "unit": "GB/s",
-                     "frac": push_gbs / peak, "traffic": None, "bytes_per_particle": PUSH_BYTES_PER_PARTICLE,
+                     "frac": push_gbs / peak, "traffic": NCU_TRAFFIC_BYTES_PER_PARTICLE * n, "bytes_per_particle": PUSH_BYTES_PER_PARTICLE,
+                     "frac_88B": push_gbs / peak * PUSH_ONLY_BYTES / PUSH_BYTES_PER_PARTICLE,
+                     "traffic_source": "ncu --set full dram__bytes_read+write of one launch, profiles/r01c_ncu_push_thermal.csv (117 B/particle)",
                      "pushes_per_s_kernel_only": n / (push_ms * 1e-3), "peak_source": peak_how,
-                     "sort_gbs": n * SORT_BYTES_PER_PARTICLE / (sort_ms * 1e-3) / 1e9},
+                     "sort_gbs": n * SORT_BYTES_PER_PARTICLE / (sort_ms * 1e-3) / 1e9,
+                     "note": "fused gather+push+deposit+reorder: 52 B read + 52 B written per particle; the sort that remains (scan + permutation build) moves 8 B/particle"},
         "gpu_launches": int(launches), "clocks": clk.summary(),
         "diagnostics_after": {k: float(v) for k, v in diag.items()},
     }

@@ -231,9 +231,9 @@ def bench_main(args, w, rank, world, local, peak, peak_how):
                           "decomposition": f"{world} slabs of {w['ny']} cell rows (ring, NCCL send/recv)",
                           "l2": "per-rank particle state >> 126 MB L2 (no flush needed)"},
                "gpu_launches": int(launches), "clocks": clk.summary(), "migrated_records_rank0": int(stepper.moved),
-               "roofline": {"bound": "hbm", "kernel": "whole step", "achieved": value * (88.0 + 120.0) / 1e9 / world, "peak": peak,
-                            "unit": "GB/s", "frac": value * (88.0 + 120.0) / 1e9 / world / peak, "traffic": None,
-                            "bytes_per_particle": 208.0, "peak_source": peak_how, "note": "per GPU, push 88 B + sort 120 B per particle"}}
+               "roofline": {"bound": "hbm", "kernel": "whole step", "achieved": value * 112.0 / 1e9 / world, "peak": peak,
+                            "unit": "GB/s", "frac": value * 112.0 / 1e9 / world / peak, "traffic": None,
+                            "bytes_per_particle": 112.0, "peak_source": peak_how, "note": "per GPU: fused push+reorder 104 B + permutation sort 8 B per particle"}}
         if e2e:
             out["e2e"] = e2e
         print(json.dumps(out))
