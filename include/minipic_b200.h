@@ -140,6 +140,29 @@ int mpic_migration_describe(mpic_sim* s, mpic_migr_desc* out);
 int mpic_migration_counts(mpic_sim* s, int leave[2], int arrive[2]);
 int mpic_migration_absorb(mpic_sim* s, int n_from_lo, int n_from_hi);
 
+/* ---- peer-memory slab ring (nranks > 1; replaces, on the step path, the pack / transfer / unpack protocol above and
+ * with it the reference's exchange phases PIC_2D.cpp:200-248,276-319,348-396 and MPI_Barriers :200,226,...).
+ * Every handle maps its two ring neighbours' device memory (CUDA IPC between processes -- one process per GPU under
+ * torchrun --, plain pointers inside one process) and the kernels talk over NVLink directly:
+ *   - the Yee sweeps store their edge rows straight into the neighbours' guard rows (no pack, no copy, no unpack);
+ *   - the current guard rows are added into the neighbours' edge rows with remote 64-bit integer atomics;
+ *   - leaver records and their counts are written into the neighbours' arrival buffers;
+ *   - phases are ordered by epoch flags in peer memory (release store / acquire spin), not by host barriers.
+ * mpic_peer_info is an opaque, fixed-size, trivially copyable blob: move it between ranks with any transport
+ * (torch.distributed all_gather in slab.py).  One host synchronisation per step remains (migration counts), placed so
+ * that it overlaps the field sweeps. */
+typedef struct mpic_peer_info { unsigned char bytes[512]; } mpic_peer_info;
+int mpic_peer_export(mpic_sim* s, mpic_peer_info* out);
+/* lo = rank-1, hi = rank+1 (periodic).  Blobs exported by handles of this very process are recognised (no IPC). */
+int mpic_peer_connect(mpic_sim* s, const mpic_peer_info* lo, const mpic_peer_info* hi);
+/* All ranks call these collectively (each on its own handle).  Split in two so that one host thread can drive several
+ * handles: call begin on every handle, then end on every handle. */
+int mpic_peer_refresh_begin(mpic_sim* s);   /* after uploads: y guards of E and B from the neighbours */
+int mpic_peer_refresh_end(mpic_sim* s);
+int mpic_peer_field_step(mpic_sim* s);      /* phases A..F of one step; no host synchronisation at all */
+int mpic_peer_step_begin(mpic_sim* s);      /* push+deposit, hand-off, J add, Yee phases: everything enqueued, no host wait */
+int mpic_peer_step_end(mpic_sim* s);        /* migration counts (the one host wait), arrivals absorbed, tile sort */
+
 /* ---- particles (struct Particle, Auxiliar_functions.h:16-21, as SoA: x,y,px,py,pz,q doubles and int tag).
  * Upload accepts any order; the device sorts by (tile gid, cell) before the first push. */
 int mpic_upload_particles(mpic_sim* s, int64_t n, const double* x, const double* y, const double* ux, const double* uy,

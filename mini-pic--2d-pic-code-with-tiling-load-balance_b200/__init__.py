@@ -17,6 +17,9 @@ c_ip = C.POINTER(C.c_int)
 c_lp = C.POINTER(C.c_int64)
 
 
+PEER_INFO_BYTES = 512   # sizeof(mpic_peer_info)
+
+
 class MpicError(RuntimeError):
     pass
 
@@ -95,6 +98,11 @@ def lib():
     L.mpic_set_owner.argtypes = [C.c_void_p, c_ip]
     L.mpic_slab_rows.argtypes = [C.c_int, C.c_int, C.c_int, c_ip, c_ip]
     L.mpic_selftest_math.argtypes = [C.c_int64, C.c_uint64, c_lp]
+    L.mpic_peer_export.argtypes = [C.c_void_p, C.c_char_p]
+    L.mpic_peer_connect.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p]
+    for name in ("mpic_peer_refresh_begin", "mpic_peer_refresh_end", "mpic_peer_field_step", "mpic_peer_step_begin",
+                 "mpic_peer_step_end"):
+        getattr(L, name).argtypes = [C.c_void_p]
     _lib = L
     return L
 
@@ -232,6 +240,31 @@ class Sim:
 
     def migration_absorb(self, n_from_lo, n_from_hi):
         _chk(lib().mpic_migration_absorb(self.h, n_from_lo, n_from_hi))
+
+    # ---- peer-memory ring (nranks > 1): neighbours' device memory mapped, halos / current / leavers move inside the kernels
+    def peer_export(self):
+        """512-byte blob describing this handle's peer-visible memory (CUDA IPC handles); give it to the two neighbours."""
+        buf = C.create_string_buffer(PEER_INFO_BYTES)
+        _chk(lib().mpic_peer_export(self.h, buf))
+        return buf.raw
+
+    def peer_connect(self, lo_blob, hi_blob):
+        _chk(lib().mpic_peer_connect(self.h, lo_blob, hi_blob))
+
+    def peer_refresh_begin(self):
+        _chk(lib().mpic_peer_refresh_begin(self.h))
+
+    def peer_refresh_end(self):
+        _chk(lib().mpic_peer_refresh_end(self.h))
+
+    def peer_field_step(self):
+        _chk(lib().mpic_peer_field_step(self.h))
+
+    def peer_step_begin(self):
+        _chk(lib().mpic_peer_step_begin(self.h))
+
+    def peer_step_end(self):
+        _chk(lib().mpic_peer_step_end(self.h))
 
     def torch_stream(self):
         import torch
@@ -393,6 +426,40 @@ class SlabRing:
 
     def pic_steps(self, nsteps):
         _chk(lib().mpic_ring_pic_steps(self.arr, self.n, nsteps))
+
+    def sync(self):
+        for s in self.sims:
+            s.sync()
+
+
+class PeerRing:
+    """Several slab handles of ONE process (one per GPU, or all on one GPU in the tests) connected as a peer-memory ring:
+    the split begin/end calls let a single host thread drive all of them (mpic_peer_*; csrc/peer.cu)."""
+
+    def __init__(self, sims):
+        self.sims = list(sims)
+        n = len(self.sims)
+        blobs = [s.peer_export() for s in self.sims]
+        for r, s in enumerate(self.sims):
+            s.peer_connect(blobs[(r - 1) % n], blobs[(r + 1) % n])
+
+    def refresh_guards(self):
+        for s in self.sims:
+            s.peer_refresh_begin()
+        for s in self.sims:
+            s.peer_refresh_end()
+
+    def field_steps(self, nsteps):
+        for _ in range(nsteps):
+            for s in self.sims:
+                s.peer_field_step()
+
+    def pic_steps(self, nsteps):
+        for _ in range(nsteps):
+            for s in self.sims:
+                s.peer_step_begin()
+            for s in self.sims:
+                s.peer_step_end()
 
     def sync(self):
         for s in self.sims:

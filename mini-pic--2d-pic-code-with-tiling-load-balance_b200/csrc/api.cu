@@ -232,9 +232,11 @@ int mpic_create(const mpic_params* p, mpic_sim** out) {
             if (lc < 4096) lc = 4096;
             if (lc > s->cap) lc = s->cap;
             s->lv.cap = (int)lc;
+            // arrival block: [2 step parities][2 sides][lc records]; the staged transports use parity 0
+            CUDA_TRY(cudaMalloc(&s->arrive_blk, (size_t)4 * lc * MPIC_REC_DOUBLES * 8));
             for (int d = 0; d < 2; d++) {
                 CUDA_TRY(cudaMalloc(&s->lv.rec[d], (size_t)lc * MPIC_REC_DOUBLES * 8));
-                CUDA_TRY(cudaMalloc(&s->arrive[d], (size_t)lc * MPIC_REC_DOUBLES * 8));
+                s->arrive[d] = s->arrive_blk + (size_t)d * lc * MPIC_REC_DOUBLES;
             }
         }
     }
@@ -258,17 +260,21 @@ int mpic_destroy(mpic_sim* s) {
     cudaSetDevice(s->prm.device);
     if (s->st) cudaStreamSynchronize(s->st);
     mpic_ring_release(s);
+    mpic_peer_release(s);
     cudaFree(s->planes); cudaFree(s->jacc); cudaFree(s->rho); cudaFree(s->d_scratch);
     for (int k = 0; k < 2; k++) { cudaFree(s->pa[k].x); cudaFree(s->pa[k].tag); }
     cudaFree(s->cell_start); cudaFree(s->cell_count); cudaFree(s->scan_tmp); cudaFree(s->keys); cudaFree(s->perm);
     cudaFree(s->halo_send); cudaFree(s->halo_recv); cudaFree(s->lv.count);
-    for (int d = 0; d < 2; d++) { cudaFree(s->lv.rec[d]); cudaFree(s->arrive[d]); }
+    for (int d = 0; d < 2; d++) cudaFree(s->lv.rec[d]);
+    cudaFree(s->arrive_blk);
     if (s->st) cudaStreamDestroy(s->st);
     delete s;
     return 0;
 }
 int mpic_sync(mpic_sim* s) {
-    if (s) cudaSetDevice(s->prm.device); REQUIRE(s, MPIC_EINVAL, "null handle"); CUDA_TRY(cudaStreamSynchronize(s->st)); return 0; }
+    if (s) cudaSetDevice(s->prm.device); REQUIRE(s, MPIC_EINVAL, "null handle"); CUDA_TRY(cudaStreamSynchronize(s->st));
+    if (s->peer_on) return mpic_peer_refresh_end(s);     // surfaces a timed-out neighbour wait
+    return 0; }
 void* mpic_stream(mpic_sim* s) { return s ? (void*)s->st : nullptr; }
 int64_t mpic_kernel_launches(mpic_sim* s) {
     if (s) cudaSetDevice(s->prm.device); return s ? s->launches : 0; }
@@ -351,12 +357,12 @@ int mpic_download_tiles(mpic_sim* s, double* grid6, const int* gids, int ntiles)
 int mpic_step_b_half(mpic_sim* s) {
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s, MPIC_EINVAL, "null handle");
-    TRY(launch_b_sweep(s->G, s->planes, s->cf, s->st));
+    TRY(launch_b_sweep(s->G, s->planes, s->cf, PeerHalo(), s->st));
     s->launches++;
     return 0;
 }
 static int e_sweep(mpic_sim* s, int with_j) {
-    TRY(launch_e_sweep(s->G, s->planes, s->jacc, with_j, s->cf, s->st));
+    TRY(launch_e_sweep(s->G, s->planes, s->jacc, with_j, s->cf, PeerHalo(), s->st));
     s->launches++;
     return 0;
 }
@@ -569,6 +575,7 @@ int mpic_push_deposit(mpic_sim* s) {
     s->counts_valid = true;
     return 0;
 }
+int mpic_sort_after_push(mpic_sim* s) { return sort_all(s, true); }
 int mpic_sort_tiles(mpic_sim* s) {
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && s->cap > 0, MPIC_ESTATE, "no particle storage");

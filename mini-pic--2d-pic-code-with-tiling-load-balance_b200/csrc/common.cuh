@@ -29,6 +29,15 @@ struct FieldGeom {
     int ywrap;            // 1: y guards are the local periodic image (single slab)
 };
 
+// Peer-memory halo: where the Yee sweeps store the images of their edge rows in the two ring neighbours' guard rows
+// (device pointers into the neighbours' 6-plane blocks, mapped by peer.cu).  All null: single slab or staged transport.
+struct PeerHalo {
+    double* lo = nullptr;     // lower neighbour's planes; my interior rows [0,g) -> its rows g+nyl_lo+j (its upper guard)
+    double* hi = nullptr;     // upper neighbour's planes; my interior rows [nyl-g,nyl) -> its rows j-(nyl-g) (its lower guard)
+    int64_t lo_plane = 0, hi_plane = 0;
+    int lo_row0 = 0;          // g + nyl_lo
+};
+
 struct PicConst {
     int nx, ny;           // GLOBAL cells
     int tnx, tny;         // tile interior
@@ -74,8 +83,8 @@ static inline int ceil_div(int64_t a, int64_t b) { return (int)((a + b - 1) / b)
 
 // ---- kernel launchers implemented in yee.cu
 struct YeeCoef { double bx, by, ex, ey, dt; int fma; };   // bx = dt/(2dx) or dt/dx ; ex = dt/dx
-int launch_b_sweep(const FieldGeom& G, double* planes, const YeeCoef& c, cudaStream_t st);
-int launch_e_sweep(const FieldGeom& G, double* planes, int64_t* jacc, int with_j, const YeeCoef& c, cudaStream_t st);
+int launch_b_sweep(const FieldGeom& G, double* planes, const YeeCoef& c, const PeerHalo& ph, cudaStream_t st);
+int launch_e_sweep(const FieldGeom& G, double* planes, int64_t* jacc, int with_j, const YeeCoef& c, const PeerHalo& ph, cudaStream_t st);
 int launch_fused_step(const FieldGeom& G, const double* src, double* dst, int64_t* jacc, int with_j,
                       const YeeCoef& c, int scheme, cudaStream_t st);
 int launch_wrap_guards(const FieldGeom& G, double* planes, int first_plane, int nplanes, int do_y, cudaStream_t st);
@@ -116,3 +125,5 @@ size_t push_smem_bytes(int tnx, int tny);
 void push_box_dims(int tnx, int tny, int* pw, int* ph);
 int launch_sum_i64(const int64_t* a, int64_t n, double* out, cudaStream_t st);
 int launch_selftest_math(int64_t n, uint64_t seed, unsigned long long* bad, cudaStream_t st);
+int yee_preload();
+int particles_preload();

@@ -1,0 +1,326 @@
+// peer.cu -- the slab ring over peer-mapped device memory (NVLink / NVSwitch): no staging, no copies, no host barriers.
+//
+// Replaces, on the step path of a multi-GPU run, the reference's exchange phases (PIC_2D.cpp:200-248,276-319,348-396:
+// packSendBuffer -> MPI_Isend/Irecv -> updateGuardRegion, two MPI_Barriers each) and the particle hand-off that the
+// reference's tile migration lacks (Auxiliar_functions.cpp:244-246 drops particles).  Each handle maps its two ring
+// neighbours' field planes, current accumulators, arrival buffers and control block (CUDA IPC between the torchrun
+// processes; plain pointers when the handles share a process) and then
+//   * the Yee sweeps (yee.cu, store_images) write their edge rows straight into the neighbours' guard rows,
+//   * peer_jsend_kernel adds the current guard rows into the neighbours' edge rows with remote 64-bit integer atomics
+//     (order-independent, so still bit-identical to the single-slab result),
+//   * peer_ship_kernel writes the leaver records and their count into the neighbours' arrival buffers,
+//   * peer_sync_kernel orders the phases: release-store of an epoch into both neighbours' control blocks, acquire-spin on
+//     the own control block (bounded by a timeout that raises an error word instead of hanging the GPU).
+// Why no write-after-read hazard exists on the guard rows: every remote write of phase P is issued only after the
+// neighbour signalled the phase that last READ those rows (J before the first half-B, B1 before E, E before the second
+// half-B, B2 before the next push) -- see DESIGN.md section 4.
+#include "sim.cuh"
+#include <unistd.h>
+#include <string.h>
+
+namespace {
+
+enum Phase { PH_J = 0, PH_B1 = 1, PH_E = 2, PH_B2 = 3, PH_R1 = 4, PH_R2 = 5, PH_COUNT = 6 };
+constexpr int CTL_WORDS = 64;
+constexpr int CTL_ARRIVE = 16;        // + parity*2 + from_side : record count written by that neighbour
+constexpr int CTL_ERROR = 24;         // non-zero: a wait timed out (value = 1 + phase)
+constexpr unsigned long long PEER_MAGIC = 0x4d50494350454552ull;   // "MPICPEER"
+
+struct PeerBlob {                     // what travels inside mpic_peer_info
+    unsigned long long magic;
+    int pid, device, rank, nyl, lcap, pad;
+    int64_t plane;
+    void* raw[4];                     // planes, jacc, arrive block, control block (valid inside the exporting process)
+    cudaIpcMemHandle_t h[4];
+    unsigned long long has[4];
+};
+static_assert(sizeof(PeerBlob) <= sizeof(mpic_peer_info), "peer blob does not fit");
+
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long gtimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+// thread 0 <-> lower neighbour, thread 1 <-> upper neighbour: signal `sig` (all remote stores of the kernels before this
+// one on the stream are ordered before it), then wait until that neighbour signalled `want`.
+__global__ void peer_sync_kernel(unsigned long long* lo_flag, unsigned long long* hi_flag, unsigned long long sig,
+                                 const unsigned long long* my_flags, unsigned long long want, unsigned long long* err,
+                                 int phase, unsigned long long timeout_ns) {
+    const int t = threadIdx.x;
+    if (t > 1) return;
+    unsigned long long* out = t ? hi_flag : lo_flag;
+    __threadfence_system();
+    if (sig) st_release_sys(out, sig);
+    if (!want) return;
+    const unsigned long long t0 = gtimer_ns();
+    while (ld_acquire_sys(my_flags + t) < want) {
+        if (gtimer_ns() - t0 > timeout_ns) { atomicExch(err, 1ull + phase); return; }
+        __nanosleep(64);
+    }
+}
+
+// current guard rows -> neighbours' interior edge rows (ADD), own guard rows zeroed.  blockIdx.y = side*3g + plane*g + r.
+__global__ void peer_jsend_kernel(FieldGeom G, unsigned long long* __restrict__ jacc, unsigned long long* lo_j, int64_t lo_plane,
+                                  int lo_nyl, unsigned long long* hi_j, int64_t hi_plane) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= G.pitch) return;
+    const int g = G.g, r = blockIdx.y % g, p = (blockIdx.y / g) % 3, side = blockIdx.y / (3 * g);
+    unsigned long long* mine = jacc + (int64_t)p * G.plane + (int64_t)(side ? g + G.nyl + r : r) * G.pitch + c;
+    const unsigned long long v = *mine;
+    if (!v) return;
+    unsigned long long* dst = side ? hi_j + (int64_t)p * hi_plane + (int64_t)(g + r) * G.pitch + c
+                                   : lo_j + (int64_t)p * lo_plane + (int64_t)(lo_nyl + r) * G.pitch + c;
+    atomicAdd(dst, v);
+    *mine = 0ull;
+}
+
+// leaver records (written by the push kernel) -> the neighbours' arrival buffers, plus the count.  blockIdx.y = direction.
+__global__ void peer_ship_kernel(LeaveBufs lv, double* lo_dst, unsigned long long* lo_cnt, int lo_cap, double* hi_dst,
+                                 unsigned long long* hi_cnt, int hi_cap) {
+    const int dir = blockIdx.y;
+    const int raw = lv.count[dir];
+    const int cap = dir ? hi_cap : lo_cap;
+    const int n = raw < lv.cap ? (raw < cap ? raw : cap) : (lv.cap < cap ? lv.cap : cap);
+    double* dst = dir ? hi_dst : lo_dst;
+    const double* src = lv.rec[dir];
+    const int64_t total = (int64_t)n * MPIC_REC_DOUBLES;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) dst[e] = src[e];
+    if (blockIdx.x == 0 && threadIdx.x == 0) *(dir ? hi_cnt : lo_cnt) = (unsigned long long)raw;
+}
+
+// whole edge rows (x guards included) of `nplanes` planes -> neighbours' guard rows; used after uploads
+__global__ void peer_halo_push_kernel(FieldGeom G, const double* __restrict__ f, int nplanes, PeerHalo H) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= G.pitch) return;
+    const int g = G.g, r = blockIdx.y % g, p = (blockIdx.y / g) % nplanes, side = blockIdx.y / (nplanes * g);
+    const double v = f[(int64_t)p * G.plane + (int64_t)(side ? G.nyl + r : g + r) * G.pitch + c];
+    if (side) H.hi[(int64_t)p * H.hi_plane + (int64_t)r * G.pitch + c] = v;
+    else H.lo[(int64_t)p * H.lo_plane + (int64_t)(H.lo_row0 + r) * G.pitch + c] = v;
+}
+
+}  // namespace
+
+#define LAUNCH_CHECK() do { cudaError_t _e = cudaGetLastError(); if (_e != cudaSuccess) { mpic_set_error("%s:%d: launch failed: %s", __FILE__, __LINE__, cudaGetErrorString(_e)); return MPIC_ECUDA; } } while (0)
+
+namespace {
+
+PeerHalo halo_of(const mpic_sim* s) {
+    PeerHalo h;
+    h.lo = s->peer[0].planes; h.hi = s->peer[1].planes;
+    h.lo_plane = s->peer[0].plane; h.hi_plane = s->peer[1].plane;
+    h.lo_row0 = s->G.g + s->peer[0].nyl;
+    return h;
+}
+
+unsigned long long timeout_ns() {
+    static unsigned long long t = 0;
+    if (!t) { const char* e = getenv("MPIC_PEER_TIMEOUT_MS"); t = (unsigned long long)(e ? atoll(e) : 8000) * 1000000ull; }
+    return t;
+}
+
+// signal phase `ph` with the next epoch to both neighbours and wait for theirs
+int phase_sync(mpic_sim* s, int ph) {
+    const unsigned long long e = ++s->epoch[ph];
+    // I am the lower neighbour's UPPER side (word 1) and the upper neighbour's LOWER side (word 0)
+    peer_sync_kernel<<<1, 32, 0, s->st>>>(s->peer[0].ctl + ph * 2 + 1, s->peer[1].ctl + ph * 2 + 0, e, s->ctl + ph * 2, e,
+                                          s->ctl + CTL_ERROR, ph, timeout_ns());
+    LAUNCH_CHECK();
+    s->launches++;
+    return 0;
+}
+
+int check_error_word(mpic_sim* s, unsigned long long w) {
+    REQUIRE(w == 0, MPIC_ESTATE, "peer ring: rank %d timed out waiting for a neighbour in phase %d (a rank died, or the ranks "
+            "do not call the same sequence)", s->prm.rank, (int)w - 1);
+    return 0;
+}
+
+int open_side(mpic_sim* s, int side, const PeerBlob& b, const mpic_sim::PeerSide* same) {
+    mpic_sim::PeerSide& p = s->peer[side];
+    p.plane = b.plane; p.nyl = b.nyl; p.lcap = b.lcap;
+    if (same) { p.planes = same->planes; p.jacc = same->jacc; p.arrive = same->arrive; p.ctl = same->ctl; p.ipc = false; return 0; }
+    void* ptr[4] = { nullptr, nullptr, nullptr, nullptr };
+    if (b.pid == (int)getpid()) {                       // same process: plain pointers (+ peer access across devices)
+        if (b.device != s->prm.device) {
+            int can = 0;
+            CUDA_TRY(cudaDeviceCanAccessPeer(&can, s->prm.device, b.device));
+            REQUIRE(can, MPIC_ESTATE, "device %d cannot access device %d", s->prm.device, b.device);
+            cudaError_t e = cudaDeviceEnablePeerAccess(b.device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) CUDA_TRY(e);
+            cudaGetLastError();
+        }
+        for (int k = 0; k < 4; k++) ptr[k] = b.raw[k];
+    } else {
+        for (int k = 0; k < 4; k++)
+            if (b.has[k]) CUDA_TRY(cudaIpcOpenMemHandle(&ptr[k], b.h[k], cudaIpcMemLazyEnablePeerAccess));
+        p.ipc = true;
+    }
+    p.planes = (double*)ptr[0]; p.jacc = (unsigned long long*)ptr[1]; p.arrive = (double*)ptr[2]; p.ctl = (unsigned long long*)ptr[3];
+    return 0;
+}
+
+}  // namespace
+
+void mpic_peer_release(mpic_sim* s) {
+    if (!s) return;
+    for (int side = 0; side < 2; side++) {
+        mpic_sim::PeerSide& p = s->peer[side];
+        if (p.ipc) { cudaIpcCloseMemHandle(p.planes); cudaIpcCloseMemHandle(p.jacc); if (p.arrive) cudaIpcCloseMemHandle(p.arrive); cudaIpcCloseMemHandle(p.ctl); }
+        p = mpic_sim::PeerSide();
+    }
+    s->peer_on = false;
+    if (s->h_counts) { cudaFreeHost(s->h_counts); s->h_counts = nullptr; }
+    if (s->ev_counts) { cudaEventDestroy(s->ev_counts); s->ev_counts = nullptr; }
+    if (s->ctl) { cudaFree(s->ctl); s->ctl = nullptr; }
+}
+
+extern "C" {
+
+int mpic_peer_export(mpic_sim* s, mpic_peer_info* out) {
+    if (s) cudaSetDevice(s->prm.device);
+    REQUIRE(s && out, MPIC_EINVAL, "bad argument");
+    REQUIRE(s->prm.nranks > 1, MPIC_ESTATE, "the peer ring exists only for nranks > 1");
+    if (!s->ctl) {
+        CUDA_TRY(cudaMalloc(&s->ctl, CTL_WORDS * 8));
+        CUDA_TRY(cudaMemset(s->ctl, 0, CTL_WORDS * 8));
+        CUDA_TRY(cudaMallocHost(&s->h_counts, 16 * sizeof(long long)));
+        CUDA_TRY(cudaEventCreateWithFlags(&s->ev_counts, cudaEventDisableTiming));
+    }
+    memset(out, 0, sizeof *out);
+    PeerBlob b;
+    memset(&b, 0, sizeof b);
+    b.magic = PEER_MAGIC; b.pid = (int)getpid(); b.device = s->prm.device; b.rank = s->prm.rank; b.nyl = s->G.nyl;
+    b.lcap = s->lv.cap; b.plane = s->G.plane;
+    b.raw[0] = s->planes; b.raw[1] = s->jacc; b.raw[2] = s->arrive_blk; b.raw[3] = s->ctl;
+    for (int k = 0; k < 4; k++)
+        if (b.raw[k]) { CUDA_TRY(cudaIpcGetMemHandle(&b.h[k], b.raw[k])); b.has[k] = 1; }
+    memcpy(out->bytes, &b, sizeof b);
+    return 0;
+}
+
+int mpic_peer_connect(mpic_sim* s, const mpic_peer_info* lo, const mpic_peer_info* hi) {
+    if (s) cudaSetDevice(s->prm.device);
+    REQUIRE(s && lo && hi, MPIC_EINVAL, "bad argument");
+    REQUIRE(s->ctl, MPIC_ESTATE, "call mpic_peer_export first");
+    PeerBlob bl, bh;
+    memcpy(&bl, lo->bytes, sizeof bl); memcpy(&bh, hi->bytes, sizeof bh);
+    REQUIRE(bl.magic == PEER_MAGIC && bh.magic == PEER_MAGIC, MPIC_EINVAL, "not a peer blob");
+    const int n = s->prm.nranks;
+    REQUIRE(bl.rank == (s->prm.rank + n - 1) % n && bh.rank == (s->prm.rank + 1) % n, MPIC_EINVAL,
+            "rank %d: neighbours must be ranks %d and %d (got %d, %d)", s->prm.rank, (s->prm.rank + n - 1) % n, (s->prm.rank + 1) % n, bl.rank, bh.rank);
+    TRY(open_side(s, 0, bl, nullptr));
+    TRY(open_side(s, 1, bh, bh.rank == bl.rank ? &s->peer[0] : nullptr));       // two ranks: both neighbours are the same handle
+    // no kernel may be loaded lazily once flag waits can spin (see yee_preload)
+    TRY(yee_preload());
+    TRY(particles_preload());
+    {
+        cudaFuncAttributes a;
+        const void* fs[] = { (const void*)peer_sync_kernel, (const void*)peer_jsend_kernel, (const void*)peer_ship_kernel,
+                             (const void*)peer_halo_push_kernel };
+        for (const void* f : fs) CUDA_TRY(cudaFuncGetAttributes(&a, f));
+    }
+    s->peer_on = true;
+    return 0;
+}
+
+int mpic_peer_refresh_begin(mpic_sim* s) {
+    if (s) cudaSetDevice(s->prm.device);
+    REQUIRE(s && s->peer_on, MPIC_ESTATE, "peer ring not connected");
+    TRY(phase_sync(s, PH_R1));                           // both neighbours finished writing their own planes
+    peer_halo_push_kernel<<<dim3(ceil_div(s->G.pitch, 256), 2 * 6 * s->G.g), 256, 0, s->st>>>(s->G, s->planes, 6, halo_of(s));
+    LAUNCH_CHECK();
+    s->launches++;
+    return phase_sync(s, PH_R2);
+}
+int mpic_peer_refresh_end(mpic_sim* s) {
+    if (s) cudaSetDevice(s->prm.device);
+    REQUIRE(s && s->peer_on, MPIC_ESTATE, "peer ring not connected");
+    unsigned long long w = 0;
+    CUDA_TRY(cudaMemcpyAsync(&w, s->ctl + CTL_ERROR, 8, cudaMemcpyDeviceToHost, s->st));
+    CUDA_TRY(cudaStreamSynchronize(s->st));
+    return check_error_word(s, w);
+}
+
+static int yee_phases(mpic_sim* s, int with_j) {
+    const PeerHalo h = halo_of(s);
+    TRY(launch_b_sweep(s->G, s->planes, s->cf, h, s->st));
+    TRY(phase_sync(s, PH_B1));
+    TRY(launch_e_sweep(s->G, s->planes, s->jacc, with_j, s->cf, h, s->st));
+    TRY(phase_sync(s, PH_E));
+    s->launches += 2;
+    if (s->prm.scheme == 0) {
+        TRY(launch_b_sweep(s->G, s->planes, s->cf, h, s->st));
+        s->launches++;
+    }
+    return phase_sync(s, PH_B2);
+}
+
+int mpic_peer_field_step(mpic_sim* s) {
+    if (s) cudaSetDevice(s->prm.device);
+    REQUIRE(s && s->peer_on, MPIC_ESTATE, "peer ring not connected");
+    return yee_phases(s, 0);
+}
+
+int mpic_peer_step_begin(mpic_sim* s) {
+    if (s) cudaSetDevice(s->prm.device);
+    REQUIRE(s && s->peer_on, MPIC_ESTATE, "peer ring not connected");
+    REQUIRE(s->cap > 0 && s->arrive_blk, MPIC_ESTATE, "no particle storage");
+    const int par = (int)(++s->step_no & 1);
+    const FieldGeom& G = s->G;
+    TRY(mpic_push_deposit(s));
+    const int64_t rec = MPIC_REC_DOUBLES;
+    // my leavers going DOWN arrive at the lower neighbour "from above" (side 1); going UP: at the upper neighbour's side 0
+    peer_ship_kernel<<<dim3(32, 2), 256, 0, s->st>>>(s->lv,
+        s->peer[0].arrive + (int64_t)(par * 2 + 1) * s->peer[0].lcap * rec, s->peer[0].ctl + CTL_ARRIVE + par * 2 + 1, s->peer[0].lcap,
+        s->peer[1].arrive + (int64_t)(par * 2 + 0) * s->peer[1].lcap * rec, s->peer[1].ctl + CTL_ARRIVE + par * 2 + 0, s->peer[1].lcap);
+    LAUNCH_CHECK();
+    peer_jsend_kernel<<<dim3(ceil_div(G.pitch, 256), 6 * G.g), 256, 0, s->st>>>(G, (unsigned long long*)s->jacc, s->peer[0].jacc,
+        s->peer[0].plane, s->peer[0].nyl, s->peer[1].jacc, s->peer[1].plane);
+    LAUNCH_CHECK();
+    s->launches += 2;
+    TRY(phase_sync(s, PH_J));                            // neighbours pushed, shipped and added their current
+    // the one host wait of the step (taken in step_end, i.e. after the field phases have been enqueued)
+    CUDA_TRY(cudaMemcpyAsync(s->h_counts, s->lv.count, 2 * sizeof(int), cudaMemcpyDeviceToHost, s->st));
+    CUDA_TRY(cudaMemcpyAsync(s->h_counts + 4, s->ctl + CTL_ARRIVE + par * 2, 16, cudaMemcpyDeviceToHost, s->st));
+    CUDA_TRY(cudaMemcpyAsync(s->h_counts + 8, s->ctl + CTL_ERROR, 8, cudaMemcpyDeviceToHost, s->st));
+    CUDA_TRY(cudaEventRecord(s->ev_counts, s->st));
+    TRY(launch_fold_current(G, s->jacc, 3, 0, s->st));
+    s->launches++;
+    return yee_phases(s, 1);
+}
+
+int mpic_peer_step_end(mpic_sim* s) {
+    if (s) cudaSetDevice(s->prm.device);
+    REQUIRE(s && s->peer_on, MPIC_ESTATE, "peer ring not connected");
+    REQUIRE(s->counts_valid, MPIC_ESTATE, "mpic_peer_step_end must follow mpic_peer_step_begin");
+    CUDA_TRY(cudaEventSynchronize(s->ev_counts));
+    const int par = (int)(s->step_no & 1);
+    unsigned long long arr[2], err;
+    memcpy(arr, s->h_counts + 4, 16); memcpy(&err, s->h_counts + 8, 8);
+    TRY(check_error_word(s, err));
+    const int leave[2] = { s->h_counts[0], s->h_counts[1] };
+    for (int d = 0; d < 2; d++)
+        REQUIRE(leave[d] <= s->lv.cap && leave[d] <= s->peer[d].lcap && (int64_t)arr[d] <= s->lv.cap, MPIC_ENOMEM,
+                "migration buffer overflow: %d leavers / %lld arrivals > capacity %d", leave[d], (long long)arr[d], s->lv.cap);
+    s->left = (int64_t)leave[0] + leave[1];
+    REQUIRE(s->n + (int64_t)arr[0] + (int64_t)arr[1] <= s->cap, MPIC_ENOMEM, "particle capacity exceeded by arrivals");
+    for (int side = 0; side < 2; side++) {               // appended in (lower, upper) order -- SURVEY.md B.8
+        const int n = (int)arr[side];
+        TRY(launch_absorb(s->P, s->pa[s->cur], s->n + s->arrived, s->arrive_blk + (int64_t)(par * 2 + side) * s->lv.cap * MPIC_REC_DOUBLES,
+                          n, s->cell_count, s->keys, s->st));
+        s->arrived += n;
+        s->launches += n > 0;
+    }
+    return mpic_sort_after_push(s);
+}
+
+}  // extern "C"

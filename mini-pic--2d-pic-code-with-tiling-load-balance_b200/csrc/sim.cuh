@@ -39,11 +39,31 @@ struct mpic_sim {
     double* arrive[2] = {};        // records received from the lower / upper neighbour
     int64_t arrived = 0;           // records absorbed into the tail [n, n+arrived) and not yet sorted in
     int64_t left = -1;             // leavers of the last push (host copy; -1: unknown)
+    // ---- peer-memory ring (peer.cu)
+    struct PeerSide {
+        double* planes = nullptr;          // neighbour's 6 field planes
+        unsigned long long* jacc = nullptr; // neighbour's 3 current accumulators
+        double* arrive = nullptr;          // neighbour's arrival block: [parity][from side][cap records]
+        unsigned long long* ctl = nullptr; // neighbour's control block (flags + arrival counts)
+        int64_t plane = 0;                 // neighbour's values per plane
+        int nyl = 0;                       // neighbour's interior rows
+        int lcap = 0;                      // neighbour's records per arrival buffer
+        bool ipc = false;                  // pointers came from cudaIpcOpenMemHandle
+    } peer[2];                             // 0 = lower neighbour, 1 = upper neighbour
+    bool peer_on = false;
+    double* arrive_blk = nullptr;          // own arrival block [2 parities][2 sides][lv.cap records] (arrive[] alias parity 0)
+    unsigned long long* ctl = nullptr;     // own control block, written by the neighbours
+    unsigned long long epoch[8] = {};      // per phase: last epoch signalled
+    unsigned long long step_no = 0;        // PIC steps begun on the peer path (parity of the arrival buffers)
+    int* h_counts = nullptr;               // pinned: leave[2], arrive[2], error word
+    cudaEvent_t ev_counts = nullptr;
     std::vector<int> owner;        // global tiles
     void* ring_events = nullptr;   // ring.cu: per-handle events of the single-process peer-copy ring
 };
 
 void mpic_ring_release(mpic_sim* s);
+void mpic_peer_release(mpic_sim* s);
+extern "C" int mpic_sort_after_push(mpic_sim* s);   // api.cu: sort_all(counted)
 #define HALO_HDR 16                /* values (128 B) of header in front of each halo message; [0] = leaver count to that side */
 #define REQUIRE(cond, code, ...) do { if (!(cond)) { mpic_set_error(__VA_ARGS__); return code; } } while (0)
 #define TRY(expr) do { int _r = (expr); if (_r) return _r; } while (0)

@@ -17,9 +17,11 @@ __device__ __forceinline__ int64_t fidx(const FieldGeom& G, int i, int j) {
     return (int64_t)(G.g + j) * G.pitch + (MPIC_X0 + i);
 }
 
-// store v at interior cell (i,j) and at every guard-ring image of it
+// store v at interior cell (i,j) and at every guard-ring image of it -- including, on a peer-memory slab ring, the image
+// in the neighbour slab's guard rows (a remote store over NVLink: the halo exchange is fused into the sweep)
 template <typename T>
-__device__ __forceinline__ void store_images(const FieldGeom& G, T* __restrict__ p, int i, int j, T v) {
+__device__ __forceinline__ void store_images(const FieldGeom& G, T* __restrict__ p, int i, int j, T v,
+                                             T* __restrict__ rlo = nullptr, T* __restrict__ rhi = nullptr, int lo_row0 = 0) {
     const int64_t k = fidx(G, i, j);
     p[k] = v;
     const int g = G.g;
@@ -32,10 +34,20 @@ __device__ __forceinline__ void store_images(const FieldGeom& G, T* __restrict__
         p[k + (int64_t)ys * G.pitch] = v;
         if (xs) p[k + (int64_t)ys * G.pitch + xs] = v;
     }
+    if (rlo && j < g) {
+        const int64_t kr = (int64_t)(lo_row0 + j) * G.pitch + (MPIC_X0 + i);
+        rlo[kr] = v;
+        if (xs) rlo[kr + xs] = v;
+    }
+    if (rhi && j >= G.nyl - g) {
+        const int64_t kr = (int64_t)(j - (G.nyl - g)) * G.pitch + (MPIC_X0 + i);
+        rhi[kr] = v;
+        if (xs) rhi[kr + xs] = v;
+    }
 }
 
 template <int FMA>
-__global__ void __launch_bounds__(256) b_sweep_kernel(FieldGeom G, double* __restrict__ f, double cx, double cy) {
+__global__ void __launch_bounds__(256) b_sweep_kernel(FieldGeom G, double* __restrict__ f, double cx, double cy, PeerHalo H) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int j = blockIdx.y * blockDim.y + threadIdx.y;
     if (i >= G.nx || j >= G.nyl) return;
@@ -59,14 +71,14 @@ __global__ void __launch_bounds__(256) b_sweep_kernel(FieldGeom G, double* __res
         nby = by[k] + cx * dEz_x;
         nbz = bz[k] - cx * dEy_x + cy * dEx_y;
     }
-    store_images(G, bx, i, j, nbx);
-    store_images(G, by, i, j, nby);
-    store_images(G, bz, i, j, nbz);
+    store_images(G, bx, i, j, nbx, H.lo ? H.lo + 3 * H.lo_plane : nullptr, H.hi ? H.hi + 3 * H.hi_plane : nullptr, H.lo_row0);
+    store_images(G, by, i, j, nby, H.lo ? H.lo + 4 * H.lo_plane : nullptr, H.hi ? H.hi + 4 * H.hi_plane : nullptr, H.lo_row0);
+    store_images(G, bz, i, j, nbz, H.lo ? H.lo + 5 * H.lo_plane : nullptr, H.hi ? H.hi + 5 * H.hi_plane : nullptr, H.lo_row0);
 }
 
 template <int FMA, int WITH_J>
 __global__ void __launch_bounds__(256) e_sweep_kernel(FieldGeom G, double* __restrict__ f, int64_t* __restrict__ jacc,
-                                                      double cx, double cy, double dt) {
+                                                      double cx, double cy, double dt, PeerHalo H) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int j = blockIdx.y * blockDim.y + threadIdx.y;
     if (i >= G.nx || j >= G.nyl) return;
@@ -99,9 +111,9 @@ __global__ void __launch_bounds__(256) e_sweep_kernel(FieldGeom G, double* __res
         nez = fma(-dt, __ll2double_rn(jz[k]) * MPIC_INV_JSCALE, nez);
         jx[k] = 0; jy[k] = 0; jz[k] = 0;
     }
-    store_images(G, ex, i, j, nex);
-    store_images(G, ey, i, j, ney);
-    store_images(G, ez, i, j, nez);
+    store_images(G, ex, i, j, nex, H.lo, H.hi, H.lo_row0);
+    store_images(G, ey, i, j, ney, H.lo ? H.lo + H.lo_plane : nullptr, H.hi ? H.hi + H.hi_plane : nullptr, H.lo_row0);
+    store_images(G, ez, i, j, nez, H.lo ? H.lo + 2 * H.lo_plane : nullptr, H.hi ? H.hi + 2 * H.hi_plane : nullptr, H.lo_row0);
 }
 
 // ---- guard ring rebuild for `nplanes` planes starting at `first` (after uploads / halo receives)
@@ -275,21 +287,21 @@ __global__ void gauss_kernel(FieldGeom G, const double* __restrict__ f, const in
 
 #define LAUNCH_CHECK() do { cudaError_t _e = cudaGetLastError(); if (_e != cudaSuccess) { mpic_set_error("%s:%d: launch failed: %s", __FILE__, __LINE__, cudaGetErrorString(_e)); return MPIC_ECUDA; } } while (0)
 
-int launch_b_sweep(const FieldGeom& G, double* planes, const YeeCoef& c, cudaStream_t st) {
+int launch_b_sweep(const FieldGeom& G, double* planes, const YeeCoef& c, const PeerHalo& ph, cudaStream_t st) {
     dim3 b(64, 4), g(ceil_div(G.nx, 64), ceil_div(G.nyl, 4));
-    if (c.fma) b_sweep_kernel<1><<<g, b, 0, st>>>(G, planes, c.bx, c.by);
-    else b_sweep_kernel<0><<<g, b, 0, st>>>(G, planes, c.bx, c.by);
+    if (c.fma) b_sweep_kernel<1><<<g, b, 0, st>>>(G, planes, c.bx, c.by, ph);
+    else b_sweep_kernel<0><<<g, b, 0, st>>>(G, planes, c.bx, c.by, ph);
     LAUNCH_CHECK();
     return 0;
 }
-int launch_e_sweep(const FieldGeom& G, double* planes, int64_t* jacc, int with_j, const YeeCoef& c, cudaStream_t st) {
+int launch_e_sweep(const FieldGeom& G, double* planes, int64_t* jacc, int with_j, const YeeCoef& c, const PeerHalo& ph, cudaStream_t st) {
     dim3 b(64, 4), g(ceil_div(G.nx, 64), ceil_div(G.nyl, 4));
     if (c.fma) {
-        if (with_j) e_sweep_kernel<1, 1><<<g, b, 0, st>>>(G, planes, jacc, c.ex, c.ey, c.dt);
-        else e_sweep_kernel<1, 0><<<g, b, 0, st>>>(G, planes, jacc, c.ex, c.ey, c.dt);
+        if (with_j) e_sweep_kernel<1, 1><<<g, b, 0, st>>>(G, planes, jacc, c.ex, c.ey, c.dt, ph);
+        else e_sweep_kernel<1, 0><<<g, b, 0, st>>>(G, planes, jacc, c.ex, c.ey, c.dt, ph);
     } else {
-        if (with_j) e_sweep_kernel<0, 1><<<g, b, 0, st>>>(G, planes, jacc, c.ex, c.ey, c.dt);
-        else e_sweep_kernel<0, 0><<<g, b, 0, st>>>(G, planes, jacc, c.ex, c.ey, c.dt);
+        if (with_j) e_sweep_kernel<0, 1><<<g, b, 0, st>>>(G, planes, jacc, c.ex, c.ey, c.dt, ph);
+        else e_sweep_kernel<0, 0><<<g, b, 0, st>>>(G, planes, jacc, c.ex, c.ey, c.dt, ph);
     }
     LAUNCH_CHECK();
     return 0;
@@ -358,5 +370,19 @@ int launch_gauss_residual(const FieldGeom& G, const double* planes, const int64_
                           double inv_dy, double* out_max, cudaStream_t st) {
     gauss_kernel<<<296, 256, 0, st>>>(G, planes, rho, mean_rho, inv_dx, inv_dy, out_max);
     LAUNCH_CHECK();
+    return 0;
+}
+
+// CUDA loads kernels lazily, and a load can wait for the device to go idle: every kernel of the step path is loaded before
+// the first flag wait of the peer ring can spin (peer.cu), otherwise a rank could block inside a load while its neighbour
+// waits for it.
+int yee_preload() {
+    cudaFuncAttributes a;
+    const void* fs[] = { (const void*)b_sweep_kernel<0>, (const void*)b_sweep_kernel<1>, (const void*)e_sweep_kernel<0, 0>,
+                         (const void*)e_sweep_kernel<0, 1>, (const void*)e_sweep_kernel<1, 0>, (const void*)e_sweep_kernel<1, 1>,
+                         (const void*)wrap_y_kernel, (const void*)wrap_x_kernel, (const void*)fold_y_kernel, (const void*)fold_x_kernel,
+                         (const void*)halo_pack_kernel, (const void*)halo_unpack_kernel, (const void*)tiles_kernel<0>,
+                         (const void*)tiles_kernel<1>, (const void*)field_energy_kernel, (const void*)gauss_kernel };
+    for (const void* f : fs) CUDA_TRY(cudaFuncGetAttributes(&a, f));
     return 0;
 }

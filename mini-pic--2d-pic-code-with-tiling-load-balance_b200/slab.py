@@ -103,6 +103,33 @@ class SlabStepper:
         s.sort_tiles()
 
 
+class PeerStepper:
+    """One rank's time step over the peer-memory ring (csrc/peer.cu): the neighbours' device memory is mapped with CUDA
+    IPC, halos / current rows / leaver records are moved by the kernels themselves over NVLink and the phases are ordered
+    by flags in peer memory.  torch.distributed is used ONCE, to hand the IPC blobs around.  Same interface as SlabStepper."""
+
+    def __init__(self, sim, rank, world, dist=None, group=None):
+        if dist is None:
+            import torch.distributed as dist
+        self.sim = sim
+        blobs = [None] * world
+        dist.all_gather_object(blobs, sim.peer_export(), group=group)
+        sim.peer_connect(blobs[(rank - 1) % world], blobs[(rank + 1) % world])
+        dist.barrier(group=group)              # everyone mapped everyone before the first remote store
+        self.moved = 0
+
+    def refresh_guards(self):
+        self.sim.peer_refresh_begin()
+        self.sim.peer_refresh_end()
+
+    def field_step(self):
+        self.sim.peer_field_step()
+
+    def step(self):
+        self.sim.peer_step_begin()
+        self.sim.peer_step_end()
+
+
 def tile_row_costs(counts, gtc, cells_per_tile, w_particle=1.0, w_cell=0.25):
     """Cost model of the rebalancer: cost of a tile row = particles + w_cell * cells (the Yee sweeps and
     the per-tile patch staging do not vanish in empty tiles)."""
@@ -167,7 +194,8 @@ def bench_main(args, w, rank, world, local, peak, peak_how):
     st = sim.torch_stream()
     K, W = args.steps, max(args.warmup, 3)
     with torch.cuda.stream(st):
-        stepper = SlabStepper(sim, Ring(rank, world))
+        transport = os.environ.get("MPIC_TRANSPORT", "peer")
+        stepper = PeerStepper(sim, rank, world) if transport == "peer" else SlabStepper(sim, Ring(rank, world))
         stepper.refresh_guards()
         for _ in range(W):
             stepper.step()
@@ -228,7 +256,7 @@ def bench_main(args, w, rank, world, local, peak, peak_how):
                "steps": K, "warmup": W, "ms_per_step": ms.item() / K, "higher_is_better": True, "scaling": "weak",
                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                "config": {"workload": args.workload, **w, "ny_global": ny, "particles": int(npart.item()),
-                          "decomposition": f"{world} slabs of {w['ny']} cell rows (ring, NCCL send/recv)",
+                          "decomposition": f"{world} slabs of {w['ny']} cell rows, periodic ring, transport={transport}" + (" (CUDA-IPC peer memory: halos fused into the sweeps, remote atomics for J, flags for ordering)" if transport == "peer" else " (NCCL send/recv)"),
                           "l2": "per-rank particle state >> 126 MB L2 (no flush needed)"},
                "gpu_launches": int(launches), "clocks": clk.summary(), "migrated_records_rank0": int(stepper.moved),
                "roofline": {"bound": "hbm", "kernel": "whole step", "achieved": value * 112.0 / 1e9 / world, "peak": peak,

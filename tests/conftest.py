@@ -2,6 +2,9 @@ import os
 import sys
 import pytest
 
+# several slab handles share one GPU in the ring tests: give their streams distinct hardware queues (a flag wait in one
+# stream must never sit in front of the kernel that raises the flag)
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 for p in (ROOT, os.path.join(ROOT, "tests")):
     if p not in sys.path:

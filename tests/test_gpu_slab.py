@@ -163,6 +163,68 @@ def test_single_process_peer_copy_ring_bit_exact(world, shape):
         assert np.array_equal(np.concatenate([s.download_planes()[k] for s in sims]), ref[k]), k
 
 
+@pytest.mark.parametrize("world,shape", [(2, (64, 64, 16, 6, 0.6)), (3, (48, 96, 8, 5, 0.9)), (4, (32, 64, 16, 4, 0.5))])
+def test_peer_memory_ring_bit_exact(world, shape):
+    """csrc/peer.cu: halos stored by the Yee sweeps straight into the neighbours' guard rows, current rows added with remote
+    atomics, leaver records shipped into the neighbours' arrival buffers, phases ordered by flags.  N handles driven by one
+    host thread (begin on all, end on all), spread over every visible GPU (all on one device on a one-GPU box).
+    Bit-exact versus the single-rank CPU oracle, fields, particles and tile occupancy."""
+    import torch
+    m = pkg()
+    nx, ny, tn, ppc, u_th = shape
+    dx, dy, dt, parts, planes = _problem(nx, ny, tn, ppc, u_th, seed=23)
+    ndev = max(1, torch.cuda.device_count())
+    sims = [m.Sim(nx, ny, tn, tn, dx, dy, dt, max_particles=parts["x"].shape[0], rank=r, nranks=world, device=r % ndev)
+            for r in range(world)]
+    for s in sims:
+        r0, r1 = s.row0 * tn, (s.row0 + s.nrows) * tn
+        s.upload_planes([a[r0:r1] for a in planes])
+        s.upload_particles(parts)
+    ring = m.PeerRing(sims)
+    ring.refresh_guards()
+    steps = 9
+    ring.pic_steps(steps)
+    ring.sync()
+    lib = ob.load_oracle()
+    P = ob.make_params(lib, nx, ny, tn, tn, dx, dy, dt)
+    want, wf = copy_parts(parts), [a.copy() for a in planes]
+    counts, _ = ob.pic_steps(lib, P, wf, want, steps)
+    got = by_tag({k: np.concatenate([s.download_particles()[k] for s in sims]) for k in ("x", "y", "ux", "uy", "uz", "q", "tag")})
+    want = by_tag(want)
+    assert np.array_equal(got["tag"], want["tag"])
+    for k in ("x", "y", "ux", "uy", "uz", "q"):
+        assert np.array_equal(got[k], want[k]), k
+    for k in range(6):
+        assert np.array_equal(np.concatenate([s.download_planes()[k] for s in sims]), wf[k]), k
+    assert np.array_equal(np.concatenate([s.tile_counts() for s in sims]), counts)
+    # guard rows too (what a dump holds): tile patches WITH guards == single-slab device path
+    one = m.Sim(nx, ny, tn, tn, dx, dy, dt)
+    one.upload_planes(wf)
+    gtc = nx // tn
+    for s in sims:
+        gids = np.arange(s.row0 * gtc, (s.row0 + s.nrows) * gtc, dtype=np.int32)
+        assert np.array_equal(s.download_tiles(gids), one.download_tiles(gids))
+    # field-only ring == single-slab field loop
+    one.field_steps(5)
+    ring.field_steps(5)
+    ring.sync()
+    ref = one.download_planes()
+    for k in range(6):
+        assert np.array_equal(np.concatenate([s.download_planes()[k] for s in sims]), ref[k]), k
+
+
+def test_peer_memory_ring_two_processes_cuda_ipc():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    env = dict(os.environ, MPIC_TEST_TRANSPORT="peer")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29613", os.path.join(ROOT, "tests", "run_slab_nccl.py")],
+                       capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert "SLAB_PEER_PARITY_OK" in r.stdout
+
+
 def test_nccl_slabs_two_processes():
     import torch
     if torch.cuda.device_count() < 2:
