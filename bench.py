@@ -210,8 +210,7 @@ def main():
         sim.push_deposit()
         if evs:
             evs[1].record(st)
-        sim.fold_current()
-        sim.step_b_half()
+        sim.step_b_half()                 # (the E sweep folds the J guard ring on the fly)
         sim.step_e_full()
         sim.step_b_half()
         if evs:

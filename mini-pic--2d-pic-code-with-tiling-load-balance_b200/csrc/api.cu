@@ -340,6 +340,7 @@ int mpic_upload_tiles(mpic_sim* s, const double* grid6, const int* gids, int nti
 int mpic_download_tiles(mpic_sim* s, double* grid6, const int* gids, int ntiles) {
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && grid6 && gids && ntiles >= 0, MPIC_EINVAL, "bad argument");
+    if (s->peer_on) TRY(mpic_sync(s));                   // guard rows are written by the neighbours: await their last phase
     if (!ntiles) return 0;
     int* lists = nullptr;
     TRY(tile_lists(s, gids, ntiles, &lists));
@@ -357,12 +358,12 @@ int mpic_download_tiles(mpic_sim* s, double* grid6, const int* gids, int ntiles)
 int mpic_step_b_half(mpic_sim* s) {
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s, MPIC_EINVAL, "null handle");
-    TRY(launch_b_sweep(s->G, s->planes, s->cf, PeerHalo(), s->st));
+    TRY(launch_b_sweep(s->G, s->planes, s->cf, PeerHalo(), PeerSync(), s->st));
     s->launches++;
     return 0;
 }
 static int e_sweep(mpic_sim* s, int with_j) {
-    TRY(launch_e_sweep(s->G, s->planes, s->jacc, with_j, s->cf, PeerHalo(), s->st));
+    TRY(launch_e_sweep(s->G, s->planes, s->jacc, with_j, s->cf, PeerHalo(), PeerSync(), s->st));
     s->launches++;
     return 0;
 }
@@ -415,7 +416,6 @@ int mpic_halo_unpack(mpic_sim* s, int which) {
     REQUIRE(s->halo_recv, MPIC_ESTATE, "halos exist only for nranks > 1");
     TRY(launch_halo_unpack(s->G, halo_base(s, which), which == 2, s->halo_recv + HALO_HDR, s->halo_side, s->st));
     s->launches++;
-    if (which == 2) { TRY(launch_fold_current(s->G, s->jacc, 3, 0, s->st)); s->launches++; }
     return 0;
 }
 
@@ -593,8 +593,7 @@ int mpic_pic_steps(mpic_sim* s, int nsteps) {
     REQUIRE(s->prm.nranks == 1, MPIC_ESTATE, "mpic_pic_steps needs a single slab; drive phases + halos from the host for nranks>1");
     for (int k = 0; k < nsteps; k++) {
         TRY(mpic_push_deposit(s));
-        TRY(fold_current(s));
-        TRY(mpic_step_b_half(s));
+        TRY(mpic_step_b_half(s));                       // the E sweep folds the J guard ring on the fly (yee.cu)
         TRY(e_sweep(s, 1));
         TRY(mpic_step_b_half(s));
         TRY(sort_all(s, true));

@@ -38,6 +38,22 @@ struct PeerHalo {
     int lo_row0 = 0;          // g + nyl_lo
 };
 
+// Phase ordering fused into the sweeps of a peer-memory ring (peer.cu): only the CTAs that own slab-edge rows wait for the
+// neighbour's flag (before touching its guard rows or reading their own), the interior CTAs start at once -- the exchange
+// latency hides behind the interior of the sweep; the last edge CTA of each side raises this sweep's flag at the neighbour.
+struct PeerSync {
+    const unsigned long long* wait_flags = nullptr;   // own control words of the awaited phase: [0] lower, [1] upper neighbour
+    unsigned long long want = 0;                      // 0: nothing to await
+    unsigned long long* sig_lo = nullptr;             // this sweep's flag word at the lower / upper neighbour
+    unsigned long long* sig_hi = nullptr;
+    unsigned long long sig = 0;
+    unsigned int* done = nullptr;                     // [2] edge-CTA counters (self-resetting); null: no fused ordering
+    unsigned int n_lo = 0, n_hi = 0;                  // edge CTAs per side
+    unsigned long long* err = nullptr;
+    unsigned long long timeout_ns = 0;
+    int phase = 0;
+};
+
 struct PicConst {
     int nx, ny;           // GLOBAL cells
     int tnx, tny;         // tile interior
@@ -83,8 +99,8 @@ static inline int ceil_div(int64_t a, int64_t b) { return (int)((a + b - 1) / b)
 
 // ---- kernel launchers implemented in yee.cu
 struct YeeCoef { double bx, by, ex, ey, dt; int fma; };   // bx = dt/(2dx) or dt/dx ; ex = dt/dx
-int launch_b_sweep(const FieldGeom& G, double* planes, const YeeCoef& c, const PeerHalo& ph, cudaStream_t st);
-int launch_e_sweep(const FieldGeom& G, double* planes, int64_t* jacc, int with_j, const YeeCoef& c, const PeerHalo& ph, cudaStream_t st);
+int launch_b_sweep(const FieldGeom& G, double* planes, const YeeCoef& c, const PeerHalo& ph, PeerSync ps, cudaStream_t st);
+int launch_e_sweep(const FieldGeom& G, double* planes, int64_t* jacc, int with_j, const YeeCoef& c, const PeerHalo& ph, PeerSync ps, cudaStream_t st);
 int launch_fused_step(const FieldGeom& G, const double* src, double* dst, int64_t* jacc, int with_j,
                       const YeeCoef& c, int scheme, cudaStream_t st);
 int launch_wrap_guards(const FieldGeom& G, double* planes, int first_plane, int nplanes, int do_y, cudaStream_t st);

@@ -24,6 +24,7 @@ enum Phase { PH_J = 0, PH_B1 = 1, PH_E = 2, PH_B2 = 3, PH_R1 = 4, PH_R2 = 5, PH_
 constexpr int CTL_WORDS = 64;
 constexpr int CTL_ARRIVE = 16;        // + parity*2 + from_side : record count written by that neighbour
 constexpr int CTL_ERROR = 24;         // non-zero: a wait timed out (value = 1 + phase)
+constexpr int CTL_DONE = 32;          // two 32-bit edge-CTA counters of the fused sweep ordering (local use)
 constexpr unsigned long long PEER_MAGIC = 0x4d50494350454552ull;   // "MPICPEER"
 
 struct PeerBlob {                     // what travels inside mpic_peer_info
@@ -51,42 +52,58 @@ __device__ __forceinline__ unsigned long long gtimer_ns() {
 }
 
 // thread 0 <-> lower neighbour, thread 1 <-> upper neighbour: signal `sig` (all remote stores of the kernels before this
-// one on the stream are ordered before it), then wait until that neighbour signalled `want`.
+// one on the stream are ordered before it), then wait until that neighbour signalled `want`.  After the J phase the same
+// threads hand the migration counts to the host through mapped pinned memory (host_out: leave[2], arrive[2], error) --
+// no device-to-host copy sits on the stream.
 __global__ void peer_sync_kernel(unsigned long long* lo_flag, unsigned long long* hi_flag, unsigned long long sig,
                                  const unsigned long long* my_flags, unsigned long long want, unsigned long long* err,
-                                 int phase, unsigned long long timeout_ns) {
+                                 int phase, unsigned long long timeout_ns, const int* leave_cnt,
+                                 const unsigned long long* arrive_cnt, volatile long long* host_out) {
     const int t = threadIdx.x;
     if (t > 1) return;
     unsigned long long* out = t ? hi_flag : lo_flag;
     __threadfence_system();
     if (sig) st_release_sys(out, sig);
-    if (!want) return;
-    const unsigned long long t0 = gtimer_ns();
-    while (ld_acquire_sys(my_flags + t) < want) {
-        if (gtimer_ns() - t0 > timeout_ns) { atomicExch(err, 1ull + phase); return; }
-        __nanosleep(64);
+    if (want) {
+        const unsigned long long t0 = gtimer_ns();
+        while (ld_acquire_sys(my_flags + t) < want) {
+            if (gtimer_ns() - t0 > timeout_ns) { atomicExch(err, 1ull + phase); break; }
+            __nanosleep(32);
+        }
+    }
+    if (host_out) {
+        host_out[t] = leave_cnt[t];
+        host_out[2 + t] = (long long)ld_acquire_sys(arrive_cnt + t);
+        __syncwarp(0x3);
+        if (t == 0) host_out[4] = (long long)ld_acquire_sys(err);
+        __threadfence_system();
     }
 }
 
-// current guard rows -> neighbours' interior edge rows (ADD), own guard rows zeroed.  blockIdx.y = side*3g + plane*g + r.
-__global__ void peer_jsend_kernel(FieldGeom G, unsigned long long* __restrict__ jacc, unsigned long long* lo_j, int64_t lo_plane,
-                                  int lo_nyl, unsigned long long* hi_j, int64_t hi_plane) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= G.pitch) return;
-    const int g = G.g, r = blockIdx.y % g, p = (blockIdx.y / g) % 3, side = blockIdx.y / (3 * g);
-    unsigned long long* mine = jacc + (int64_t)p * G.plane + (int64_t)(side ? g + G.nyl + r : r) * G.pitch + c;
-    const unsigned long long v = *mine;
-    if (!v) return;
-    unsigned long long* dst = side ? hi_j + (int64_t)p * hi_plane + (int64_t)(g + r) * G.pitch + c
-                                   : lo_j + (int64_t)p * lo_plane + (int64_t)(lo_nyl + r) * G.pitch + c;
-    atomicAdd(dst, v);
-    *mine = 0ull;
-}
-
-// leaver records (written by the push kernel) -> the neighbours' arrival buffers, plus the count.  blockIdx.y = direction.
-__global__ void peer_ship_kernel(LeaveBufs lv, double* lo_dst, unsigned long long* lo_cnt, int lo_cap, double* hi_dst,
-                                 unsigned long long* hi_cnt, int hi_cap) {
-    const int dir = blockIdx.y;
+// After the push, ONE launch hands everything that crossed the slab edges to the neighbours:
+//   blockIdx.y <  6g : current guard rows -> neighbours' interior edge rows (remote 64-bit ADD), own guard rows zeroed
+//                      (blockIdx.y = side*3g + plane*g + r)
+//   blockIdx.y >= 6g : leaver records (written by the push kernel) -> the neighbours' arrival buffers, plus the count
+//                      (blockIdx.y - 6g = direction)
+__global__ void peer_handoff_kernel(FieldGeom G, unsigned long long* __restrict__ jacc, unsigned long long* lo_j, int64_t lo_plane,
+                                    int lo_nyl, unsigned long long* hi_j, int64_t hi_plane, LeaveBufs lv, double* lo_dst,
+                                    unsigned long long* lo_cnt, int lo_cap, double* hi_dst, unsigned long long* hi_cnt, int hi_cap) {
+    const int g = G.g;
+    if ((int)blockIdx.y < 6 * g) {
+        const int r = blockIdx.y % g, p = (blockIdx.y / g) % 3, side = blockIdx.y / (3 * g);
+        for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < G.pitch; c += gridDim.x * blockDim.x) {
+            unsigned long long* mine = jacc + (int64_t)p * G.plane + (int64_t)(side ? g + G.nyl + r : r) * G.pitch + c;
+            const unsigned long long v = *mine;
+            if (!v) continue;
+            unsigned long long* dst = side ? hi_j + (int64_t)p * hi_plane + (int64_t)(g + r) * G.pitch + c
+                                           : lo_j + (int64_t)p * lo_plane + (int64_t)(lo_nyl + r) * G.pitch + c;
+            atomicAdd(dst, v);
+            *mine = 0ull;
+        }
+        return;
+    }
+    if (!lo_dst) return;                                 // no particle storage
+    const int dir = blockIdx.y - 6 * g;
     const int raw = lv.count[dir];
     const int cap = dir ? hi_cap : lo_cap;
     const int n = raw < lv.cap ? (raw < cap ? raw : cap) : (lv.cap < cap ? lv.cap : cap);
@@ -127,15 +144,41 @@ unsigned long long timeout_ns() {
     return t;
 }
 
-// signal phase `ph` with the next epoch to both neighbours and wait for theirs
-int phase_sync(mpic_sim* s, int ph) {
-    const unsigned long long e = ++s->epoch[ph];
+// signal phase `ph` with the next epoch to both neighbours and/or wait for theirs.  Signal and wait may be issued apart
+// (B2: signalled after the sweep, awaited only before the next push, so the tile sort in between absorbs any skew).
+int phase_launch(mpic_sim* s, int ph, bool signal, bool wait, bool counts = false, int par = 0) {
+    if (signal) ++s->epoch[ph];
+    const unsigned long long e = s->epoch[ph];
     // I am the lower neighbour's UPPER side (word 1) and the upper neighbour's LOWER side (word 0)
-    peer_sync_kernel<<<1, 32, 0, s->st>>>(s->peer[0].ctl + ph * 2 + 1, s->peer[1].ctl + ph * 2 + 0, e, s->ctl + ph * 2, e,
-                                          s->ctl + CTL_ERROR, ph, timeout_ns());
+    peer_sync_kernel<<<1, 32, 0, s->st>>>(s->peer[0].ctl + ph * 2 + 1, s->peer[1].ctl + ph * 2 + 0, signal ? e : 0ull, s->ctl + ph * 2,
+                                          wait ? e : 0ull, s->ctl + CTL_ERROR, ph, timeout_ns(), counts ? s->lv.count : nullptr,
+                                          s->ctl + CTL_ARRIVE + par * 2, counts ? (volatile long long*)s->h_counts : nullptr);
     LAUNCH_CHECK();
     s->launches++;
     return 0;
+}
+int phase_sync(mpic_sim* s, int ph) { return phase_launch(s, ph, true, true); }
+int b2_wait_if_pending(mpic_sim* s) {
+    if (!s->b2_pending) return 0;
+    s->b2_pending = false;
+    return phase_launch(s, s->pending_ph, false, true);
+}
+
+const char* k_trace_names[12] = { "b2wait", "push", "handoff", "syncJ", "fold_x", "B1", "syncB1", "E", "syncE", "B2+signal",
+                                  "host+absorb+sort", "" };
+inline void tp(mpic_sim* s, int k) { if (s->trace) cudaEventRecord(s->tev[k], s->st); }
+void trace_collect(mpic_sim* s) {                     // after the step's last event has been recorded
+    if (!s->trace) return;
+    cudaEventSynchronize(s->tev[11]);
+    for (int k = 0; k < 11; k++) { float ms = 0; if (cudaEventElapsedTime(&ms, s->tev[k], s->tev[k + 1]) == cudaSuccess) s->tacc[k] += ms; }
+    s->tsteps++;
+}
+void trace_report(mpic_sim* s) {
+    if (!s->trace || !s->tsteps) return;
+    fprintf(stderr, "[mpic peer trace] rank %d, %lld steps, mean us per phase:", s->prm.rank, s->tsteps);
+    double tot = 0;
+    for (int k = 0; k < 11; k++) { fprintf(stderr, " %s=%.1f", k_trace_names[k], 1e3 * s->tacc[k] / s->tsteps); tot += s->tacc[k]; }
+    fprintf(stderr, " total=%.1f\n", 1e3 * tot / s->tsteps);
 }
 
 int check_error_word(mpic_sim* s, unsigned long long w) {
@@ -177,6 +220,9 @@ void mpic_peer_release(mpic_sim* s) {
         if (p.ipc) { cudaIpcCloseMemHandle(p.planes); cudaIpcCloseMemHandle(p.jacc); if (p.arrive) cudaIpcCloseMemHandle(p.arrive); cudaIpcCloseMemHandle(p.ctl); }
         p = mpic_sim::PeerSide();
     }
+    trace_report(s);
+    for (int k = 0; k < 16; k++) if (s->tev[k]) { cudaEventDestroy(s->tev[k]); s->tev[k] = nullptr; }
+    s->trace = false;
     s->peer_on = false;
     if (s->h_counts) { cudaFreeHost(s->h_counts); s->h_counts = nullptr; }
     if (s->ev_counts) { cudaEventDestroy(s->ev_counts); s->ev_counts = nullptr; }
@@ -224,9 +270,12 @@ int mpic_peer_connect(mpic_sim* s, const mpic_peer_info* lo, const mpic_peer_inf
     TRY(particles_preload());
     {
         cudaFuncAttributes a;
-        const void* fs[] = { (const void*)peer_sync_kernel, (const void*)peer_jsend_kernel, (const void*)peer_ship_kernel,
-                             (const void*)peer_halo_push_kernel };
+        const void* fs[] = { (const void*)peer_sync_kernel, (const void*)peer_handoff_kernel, (const void*)peer_halo_push_kernel };
         for (const void* f : fs) CUDA_TRY(cudaFuncGetAttributes(&a, f));
+    }
+    if (const char* e = getenv("MPIC_PEER_TRACE")) if (atoi(e) > 0 && !s->trace) {
+        for (int k = 0; k < 12; k++) CUDA_TRY(cudaEventCreate(&s->tev[k]));
+        s->trace = true;
     }
     s->peer_on = true;
     return 0;
@@ -235,6 +284,7 @@ int mpic_peer_connect(mpic_sim* s, const mpic_peer_info* lo, const mpic_peer_inf
 int mpic_peer_refresh_begin(mpic_sim* s) {
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && s->peer_on, MPIC_ESTATE, "peer ring not connected");
+    TRY(b2_wait_if_pending(s));
     TRY(phase_sync(s, PH_R1));                           // both neighbours finished writing their own planes
     peer_halo_push_kernel<<<dim3(ceil_div(s->G.pitch, 256), 2 * 6 * s->G.g), 256, 0, s->st>>>(s->G, s->planes, 6, halo_of(s));
     LAUNCH_CHECK();
@@ -244,29 +294,46 @@ int mpic_peer_refresh_begin(mpic_sim* s) {
 int mpic_peer_refresh_end(mpic_sim* s) {
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && s->peer_on, MPIC_ESTATE, "peer ring not connected");
+    TRY(b2_wait_if_pending(s));
     unsigned long long w = 0;
     CUDA_TRY(cudaMemcpyAsync(&w, s->ctl + CTL_ERROR, 8, cudaMemcpyDeviceToHost, s->st));
     CUDA_TRY(cudaStreamSynchronize(s->st));
     return check_error_word(s, w);
 }
 
+// Phases A..F with the ordering fused into the sweeps: every sweep's edge CTAs await the flag of the phase that produced the
+// guard rows they read (and that last read the guard rows they overwrite at the neighbour), the last edge CTA raises the
+// sweep's own flag.  B1 awaits E of the previous step (a no-op after a B2, needed when scheme == 1 has no second half-B).
+static PeerSync sweep_sync(mpic_sim* s, int wait_ph, int sig_ph) {
+    PeerSync ps;
+    ps.wait_flags = s->ctl + wait_ph * 2; ps.want = s->epoch[wait_ph];
+    ps.sig = ++s->epoch[sig_ph];
+    ps.sig_lo = s->peer[0].ctl + sig_ph * 2 + 1; ps.sig_hi = s->peer[1].ctl + sig_ph * 2 + 0;
+    ps.done = (unsigned int*)(s->ctl + CTL_DONE);
+    ps.err = s->ctl + CTL_ERROR; ps.timeout_ns = timeout_ns(); ps.phase = wait_ph;
+    return ps;
+}
 static int yee_phases(mpic_sim* s, int with_j) {
     const PeerHalo h = halo_of(s);
-    TRY(launch_b_sweep(s->G, s->planes, s->cf, h, s->st));
-    TRY(phase_sync(s, PH_B1));
-    TRY(launch_e_sweep(s->G, s->planes, s->jacc, with_j, s->cf, h, s->st));
-    TRY(phase_sync(s, PH_E));
+    TRY(launch_b_sweep(s->G, s->planes, s->cf, h, sweep_sync(s, PH_E, PH_B1), s->st));
+    tp(s, 6); tp(s, 7);
+    TRY(launch_e_sweep(s->G, s->planes, s->jacc, with_j, s->cf, h, sweep_sync(s, PH_B1, PH_E), s->st));
+    tp(s, 8); tp(s, 9);
     s->launches += 2;
     if (s->prm.scheme == 0) {
-        TRY(launch_b_sweep(s->G, s->planes, s->cf, h, s->st));
+        TRY(launch_b_sweep(s->G, s->planes, s->cf, h, sweep_sync(s, PH_E, PH_B2), s->st));
         s->launches++;
     }
-    return phase_sync(s, PH_B2);
+    s->b2_pending = true;                                // the last sweep's flag is awaited before the next reader of the
+    s->pending_ph = s->prm.scheme == 0 ? PH_B2 : PH_E;   // guard rows it fills at this rank (push, dump, download)
+    tp(s, 10);
+    return 0;
 }
 
 int mpic_peer_field_step(mpic_sim* s) {
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && s->peer_on, MPIC_ESTATE, "peer ring not connected");
+    TRY(b2_wait_if_pending(s));
     return yee_phases(s, 0);
 }
 
@@ -276,25 +343,27 @@ int mpic_peer_step_begin(mpic_sim* s) {
     REQUIRE(s->cap > 0 && s->arrive_blk, MPIC_ESTATE, "no particle storage");
     const int par = (int)(++s->step_no & 1);
     const FieldGeom& G = s->G;
+    tp(s, 0);
+    TRY(b2_wait_if_pending(s));                          // the neighbours' B guards of the previous step
+    tp(s, 1);
     TRY(mpic_push_deposit(s));
+    tp(s, 2);
     const int64_t rec = MPIC_REC_DOUBLES;
     // my leavers going DOWN arrive at the lower neighbour "from above" (side 1); going UP: at the upper neighbour's side 0
-    peer_ship_kernel<<<dim3(32, 2), 256, 0, s->st>>>(s->lv,
+    const int gx = ceil_div(G.pitch, 256) > 16 ? ceil_div(G.pitch, 256) : 16;
+    peer_handoff_kernel<<<dim3(gx, 6 * G.g + 2), 256, 0, s->st>>>(G, (unsigned long long*)s->jacc, s->peer[0].jacc, s->peer[0].plane,
+        s->peer[0].nyl, s->peer[1].jacc, s->peer[1].plane, s->lv,
         s->peer[0].arrive + (int64_t)(par * 2 + 1) * s->peer[0].lcap * rec, s->peer[0].ctl + CTL_ARRIVE + par * 2 + 1, s->peer[0].lcap,
         s->peer[1].arrive + (int64_t)(par * 2 + 0) * s->peer[1].lcap * rec, s->peer[1].ctl + CTL_ARRIVE + par * 2 + 0, s->peer[1].lcap);
     LAUNCH_CHECK();
-    peer_jsend_kernel<<<dim3(ceil_div(G.pitch, 256), 6 * G.g), 256, 0, s->st>>>(G, (unsigned long long*)s->jacc, s->peer[0].jacc,
-        s->peer[0].plane, s->peer[0].nyl, s->peer[1].jacc, s->peer[1].plane);
-    LAUNCH_CHECK();
-    s->launches += 2;
-    TRY(phase_sync(s, PH_J));                            // neighbours pushed, shipped and added their current
-    // the one host wait of the step (taken in step_end, i.e. after the field phases have been enqueued)
-    CUDA_TRY(cudaMemcpyAsync(s->h_counts, s->lv.count, 2 * sizeof(int), cudaMemcpyDeviceToHost, s->st));
-    CUDA_TRY(cudaMemcpyAsync(s->h_counts + 4, s->ctl + CTL_ARRIVE + par * 2, 16, cudaMemcpyDeviceToHost, s->st));
-    CUDA_TRY(cudaMemcpyAsync(s->h_counts + 8, s->ctl + CTL_ERROR, 8, cudaMemcpyDeviceToHost, s->st));
-    CUDA_TRY(cudaEventRecord(s->ev_counts, s->st));
-    TRY(launch_fold_current(G, s->jacc, 3, 0, s->st));
     s->launches++;
+    tp(s, 3);
+    // neighbours pushed, shipped and added their current; the same kernel hands the counts to the host (the one host wait of
+    // the step is taken in step_end, i.e. after the field phases have been enqueued)
+    TRY(phase_launch(s, PH_J, true, true, true, par));
+    CUDA_TRY(cudaEventRecord(s->ev_counts, s->st));
+    tp(s, 4);
+    tp(s, 5);                                            // (the E sweep folds the x guards of J on the fly)
     return yee_phases(s, 1);
 }
 
@@ -304,10 +373,10 @@ int mpic_peer_step_end(mpic_sim* s) {
     REQUIRE(s->counts_valid, MPIC_ESTATE, "mpic_peer_step_end must follow mpic_peer_step_begin");
     CUDA_TRY(cudaEventSynchronize(s->ev_counts));
     const int par = (int)(s->step_no & 1);
-    unsigned long long arr[2], err;
-    memcpy(arr, s->h_counts + 4, 16); memcpy(&err, s->h_counts + 8, 8);
+    const long long* hc = (const long long*)s->h_counts;
+    const unsigned long long arr[2] = { (unsigned long long)hc[2], (unsigned long long)hc[3] }, err = (unsigned long long)hc[4];
     TRY(check_error_word(s, err));
-    const int leave[2] = { s->h_counts[0], s->h_counts[1] };
+    const int leave[2] = { (int)hc[0], (int)hc[1] };
     for (int d = 0; d < 2; d++)
         REQUIRE(leave[d] <= s->lv.cap && leave[d] <= s->peer[d].lcap && (int64_t)arr[d] <= s->lv.cap, MPIC_ENOMEM,
                 "migration buffer overflow: %d leavers / %lld arrivals > capacity %d", leave[d], (long long)arr[d], s->lv.cap);
@@ -320,7 +389,10 @@ int mpic_peer_step_end(mpic_sim* s) {
         s->arrived += n;
         s->launches += n > 0;
     }
-    return mpic_sort_after_push(s);
+    TRY(mpic_sort_after_push(s));
+    tp(s, 11);
+    trace_collect(s);
+    return 0;
 }
 
 }  // extern "C"

@@ -55,7 +55,14 @@ struct mpic_sim {
     unsigned long long* ctl = nullptr;     // own control block, written by the neighbours
     unsigned long long epoch[8] = {};      // per phase: last epoch signalled
     unsigned long long step_no = 0;        // PIC steps begun on the peer path (parity of the arrival buffers)
-    int* h_counts = nullptr;               // pinned: leave[2], arrive[2], error word
+    long long* h_counts = nullptr;         // pinned + mapped: leave[2], arrive[2], error word (written by peer_sync_kernel)
+    // MPIC_PEER_TRACE=1: per-phase device time of the peer step (events on the stream; adds one host wait per step)
+    bool trace = false;
+    cudaEvent_t tev[16] = {};
+    double tacc[16] = {};
+    long long tsteps = 0;
+    int pending_ph = 3;
+    bool b2_pending = false;               // B2 signalled, neighbours' B2 not awaited yet
     cudaEvent_t ev_counts = nullptr;
     std::vector<int> owner;        // global tiles
     void* ring_events = nullptr;   // ring.cu: per-handle events of the single-process peer-copy ring

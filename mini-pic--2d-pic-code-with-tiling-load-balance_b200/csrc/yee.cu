@@ -46,42 +46,90 @@ __device__ __forceinline__ void store_images(const FieldGeom& G, T* __restrict__
     }
 }
 
+__device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+// edge CTAs: wait for the neighbour(s) whose guard rows this CTA reads / writes (see PeerSync)
+__device__ __forceinline__ void edge_wait(const PeerSync& S, bool lo_edge, bool hi_edge) {
+    if (!(lo_edge || hi_edge)) return;
+    if (S.want && threadIdx.x == 0 && threadIdx.y == 0) {
+        unsigned long long t0;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+        for (int side = 0; side < 2; side++) {
+            if (!(side ? hi_edge : lo_edge)) continue;
+            while (ld_acquire_sys_u64(S.wait_flags + side) < S.want) {
+                unsigned long long t1;
+                asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+                if (t1 - t0 > S.timeout_ns) { atomicExch(S.err, 1ull + S.phase); break; }
+                __nanosleep(32);
+            }
+        }
+    }
+    __syncthreads();
+}
+// edge CTAs: after their (remote) stores, the last one of each side raises this sweep's flag at that neighbour
+__device__ __forceinline__ void edge_signal(const PeerSync& S, bool lo_edge, bool hi_edge) {
+    if (!(lo_edge || hi_edge)) return;
+    __syncthreads();
+    if (threadIdx.x == 0 && threadIdx.y == 0) {
+        __threadfence_system();
+        if (lo_edge && atomicAdd(&S.done[0], 1u) == S.n_lo - 1) {
+            S.done[0] = 0;
+            asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(S.sig_lo), "l"(S.sig) : "memory");
+        }
+        if (hi_edge && atomicAdd(&S.done[1], 1u) == S.n_hi - 1) {
+            S.done[1] = 0;
+            asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(S.sig_hi), "l"(S.sig) : "memory");
+        }
+    }
+}
+
 template <int FMA>
-__global__ void __launch_bounds__(256) b_sweep_kernel(FieldGeom G, double* __restrict__ f, double cx, double cy, PeerHalo H) {
+__global__ void __launch_bounds__(256) b_sweep_kernel(FieldGeom G, double* __restrict__ f, double cx, double cy, PeerHalo H, PeerSync S) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int j = blockIdx.y * blockDim.y + threadIdx.y;
-    if (i >= G.nx || j >= G.nyl) return;
-    const double* ex = f;
-    const double* ey = f + G.plane;
-    const double* ez = f + 2 * G.plane;
-    double* bx = f + 3 * G.plane;
-    double* by = f + 4 * G.plane;
-    double* bz = f + 5 * G.plane;
-    const int64_t k = fidx(G, i, j), kx = k + 1, ky = k + G.pitch;
-    const double ez0 = ez[k];
-    const double dEz_y = ez[ky] - ez0, dEz_x = ez[kx] - ez0;
-    const double dEy_x = ey[kx] - ey[k], dEx_y = ex[ky] - ex[k];
-    double nbx, nby, nbz;
-    if (FMA) {
-        nbx = fma(-cy, dEz_y, bx[k]);
-        nby = fma(cx, dEz_x, by[k]);
-        nbz = fma(cy, dEx_y, fma(-cx, dEy_x, bz[k]));
-    } else {
-        nbx = bx[k] - cy * dEz_y;
-        nby = by[k] + cx * dEz_x;
-        nbz = bz[k] - cx * dEy_x + cy * dEx_y;
+    const int j0 = blockIdx.y * blockDim.y;
+    const bool lo_edge = S.done && j0 < G.g, hi_edge = S.done && j0 + (int)blockDim.y > G.nyl - G.g;
+    edge_wait(S, lo_edge, hi_edge);
+    if (i < G.nx && j < G.nyl) {
+        const double* ex = f;
+        const double* ey = f + G.plane;
+        const double* ez = f + 2 * G.plane;
+        double* bx = f + 3 * G.plane;
+        double* by = f + 4 * G.plane;
+        double* bz = f + 5 * G.plane;
+        const int64_t k = fidx(G, i, j), kx = k + 1, ky = k + G.pitch;
+        const double ez0 = ez[k];
+        const double dEz_y = ez[ky] - ez0, dEz_x = ez[kx] - ez0;
+        const double dEy_x = ey[kx] - ey[k], dEx_y = ex[ky] - ex[k];
+        double nbx, nby, nbz;
+        if (FMA) {
+            nbx = fma(-cy, dEz_y, bx[k]);
+            nby = fma(cx, dEz_x, by[k]);
+            nbz = fma(cy, dEx_y, fma(-cx, dEy_x, bz[k]));
+        } else {
+            nbx = bx[k] - cy * dEz_y;
+            nby = by[k] + cx * dEz_x;
+            nbz = bz[k] - cx * dEy_x + cy * dEx_y;
+        }
+        store_images(G, bx, i, j, nbx, H.lo ? H.lo + 3 * H.lo_plane : nullptr, H.hi ? H.hi + 3 * H.hi_plane : nullptr, H.lo_row0);
+        store_images(G, by, i, j, nby, H.lo ? H.lo + 4 * H.lo_plane : nullptr, H.hi ? H.hi + 4 * H.hi_plane : nullptr, H.lo_row0);
+        store_images(G, bz, i, j, nbz, H.lo ? H.lo + 5 * H.lo_plane : nullptr, H.hi ? H.hi + 5 * H.hi_plane : nullptr, H.lo_row0);
     }
-    store_images(G, bx, i, j, nbx, H.lo ? H.lo + 3 * H.lo_plane : nullptr, H.hi ? H.hi + 3 * H.hi_plane : nullptr, H.lo_row0);
-    store_images(G, by, i, j, nby, H.lo ? H.lo + 4 * H.lo_plane : nullptr, H.hi ? H.hi + 4 * H.hi_plane : nullptr, H.lo_row0);
-    store_images(G, bz, i, j, nbz, H.lo ? H.lo + 5 * H.lo_plane : nullptr, H.hi ? H.hi + 5 * H.hi_plane : nullptr, H.lo_row0);
+    edge_signal(S, lo_edge, hi_edge);
 }
 
 template <int FMA, int WITH_J>
 __global__ void __launch_bounds__(256) e_sweep_kernel(FieldGeom G, double* __restrict__ f, int64_t* __restrict__ jacc,
-                                                      double cx, double cy, double dt, PeerHalo H) {
+                                                      double cx, double cy, double dt, PeerHalo H, PeerSync S) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int j = blockIdx.y * blockDim.y + threadIdx.y;
-    if (i >= G.nx || j >= G.nyl) return;
+    const int j0 = blockIdx.y * blockDim.y;
+    const bool lo_edge = S.done && j0 < G.g, hi_edge = S.done && j0 + (int)blockDim.y > G.nyl - G.g;
+    edge_wait(S, lo_edge, hi_edge);
+    if (i < G.nx && j < G.nyl) {
     double* ex = f;
     double* ey = f + G.plane;
     double* ez = f + 2 * G.plane;
@@ -102,18 +150,38 @@ __global__ void __launch_bounds__(256) e_sweep_kernel(FieldGeom G, double* __res
         ney = ey[k] - cx * dBz_x;
         nez = ez[k] + (cx * dBy_x - cy * dBx_y);
     }
-    if (WITH_J) {   // E <- E - dt*J, J = acc*2^-52; the accumulators are consumed (zeroed) here
-        int64_t* jx = jacc;
-        int64_t* jy = jacc + G.plane;
-        int64_t* jz = jacc + 2 * G.plane;
-        nex = fma(-dt, __ll2double_rn(jx[k]) * MPIC_INV_JSCALE, nex);
-        ney = fma(-dt, __ll2double_rn(jy[k]) * MPIC_INV_JSCALE, ney);
-        nez = fma(-dt, __ll2double_rn(jz[k]) * MPIC_INV_JSCALE, nez);
-        jx[k] = 0; jy[k] = 0; jz[k] = 0;
+    if (WITH_J) {   // E <- E - dt*J, J = acc*2^-52; the accumulators are consumed (zeroed) here.
+        // The guard-ring fold of SURVEY.md B.6 is done on the fly: deposits that landed in the periodic images of this cell
+        // (x guards; y guards too on a single slab -- between slabs the rows were added by the neighbour beforehand) are
+        // added here.  Integer adds: the same bits as a separate fold pass (mpic_fold_current), in any order.
+        const int g = G.g;
+        const int xs = i < g ? G.nx : (i >= G.nx - g ? -G.nx : 0);
+        const int64_t ys = G.ywrap ? (j < g ? (int64_t)G.nyl * G.pitch : (j >= G.nyl - g ? -(int64_t)G.nyl * G.pitch : 0)) : 0;
+        int64_t jv[3];
+#pragma unroll
+        for (int c = 0; c < 3; c++) jv[c] = jacc[c * G.plane + k];          // all loads first: independent, in flight together
+        if (xs | (ys != 0)) {                                                 // ring cells only (a thin frame of the slab)
+#pragma unroll
+            for (int c = 0; c < 3; c++) {
+                int64_t* a = jacc + c * G.plane;
+                if (xs) { jv[c] += a[k + xs]; a[k + xs] = 0; }
+                if (ys) {
+                    jv[c] += a[k + ys]; a[k + ys] = 0;
+                    if (xs) { jv[c] += a[k + ys + xs]; a[k + ys + xs] = 0; }
+                }
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < 3; c++) jacc[c * G.plane + k] = 0;
+        nex = fma(-dt, __ll2double_rn(jv[0]) * MPIC_INV_JSCALE, nex);
+        ney = fma(-dt, __ll2double_rn(jv[1]) * MPIC_INV_JSCALE, ney);
+        nez = fma(-dt, __ll2double_rn(jv[2]) * MPIC_INV_JSCALE, nez);
     }
     store_images(G, ex, i, j, nex, H.lo, H.hi, H.lo_row0);
     store_images(G, ey, i, j, ney, H.lo ? H.lo + H.lo_plane : nullptr, H.hi ? H.hi + H.hi_plane : nullptr, H.lo_row0);
     store_images(G, ez, i, j, nez, H.lo ? H.lo + 2 * H.lo_plane : nullptr, H.hi ? H.hi + 2 * H.hi_plane : nullptr, H.lo_row0);
+    }
+    edge_signal(S, lo_edge, hi_edge);
 }
 
 // ---- guard ring rebuild for `nplanes` planes starting at `first` (after uploads / halo receives)
@@ -287,21 +355,31 @@ __global__ void gauss_kernel(FieldGeom G, const double* __restrict__ f, const in
 
 #define LAUNCH_CHECK() do { cudaError_t _e = cudaGetLastError(); if (_e != cudaSuccess) { mpic_set_error("%s:%d: launch failed: %s", __FILE__, __LINE__, cudaGetErrorString(_e)); return MPIC_ECUDA; } } while (0)
 
-int launch_b_sweep(const FieldGeom& G, double* planes, const YeeCoef& c, const PeerHalo& ph, cudaStream_t st) {
+// edge CTAs per side for the fused phase ordering: CTA rows (of 4 cell rows) that contain a slab-edge row
+static void edge_ctas(const FieldGeom& G, dim3 grid, int by, PeerSync& ps) {
+    if (!ps.done) return;
+    unsigned lo = 0, hi = 0;
+    for (int j0 = 0; j0 < G.nyl; j0 += by) { lo += j0 < G.g; hi += j0 + by > G.nyl - G.g; }
+    ps.n_lo = lo * grid.x; ps.n_hi = hi * grid.x;
+}
+int launch_b_sweep(const FieldGeom& G, double* planes, const YeeCoef& c, const PeerHalo& ph, PeerSync ps, cudaStream_t st) {
     dim3 b(64, 4), g(ceil_div(G.nx, 64), ceil_div(G.nyl, 4));
-    if (c.fma) b_sweep_kernel<1><<<g, b, 0, st>>>(G, planes, c.bx, c.by, ph);
-    else b_sweep_kernel<0><<<g, b, 0, st>>>(G, planes, c.bx, c.by, ph);
+    edge_ctas(G, g, 4, ps);
+    if (c.fma) b_sweep_kernel<1><<<g, b, 0, st>>>(G, planes, c.bx, c.by, ph, ps);
+    else b_sweep_kernel<0><<<g, b, 0, st>>>(G, planes, c.bx, c.by, ph, ps);
     LAUNCH_CHECK();
     return 0;
 }
-int launch_e_sweep(const FieldGeom& G, double* planes, int64_t* jacc, int with_j, const YeeCoef& c, const PeerHalo& ph, cudaStream_t st) {
+int launch_e_sweep(const FieldGeom& G, double* planes, int64_t* jacc, int with_j, const YeeCoef& c, const PeerHalo& ph, PeerSync ps,
+                   cudaStream_t st) {
     dim3 b(64, 4), g(ceil_div(G.nx, 64), ceil_div(G.nyl, 4));
+    edge_ctas(G, g, 4, ps);
     if (c.fma) {
-        if (with_j) e_sweep_kernel<1, 1><<<g, b, 0, st>>>(G, planes, jacc, c.ex, c.ey, c.dt, ph);
-        else e_sweep_kernel<1, 0><<<g, b, 0, st>>>(G, planes, jacc, c.ex, c.ey, c.dt, ph);
+        if (with_j) e_sweep_kernel<1, 1><<<g, b, 0, st>>>(G, planes, jacc, c.ex, c.ey, c.dt, ph, ps);
+        else e_sweep_kernel<1, 0><<<g, b, 0, st>>>(G, planes, jacc, c.ex, c.ey, c.dt, ph, ps);
     } else {
-        if (with_j) e_sweep_kernel<0, 1><<<g, b, 0, st>>>(G, planes, jacc, c.ex, c.ey, c.dt, ph);
-        else e_sweep_kernel<0, 0><<<g, b, 0, st>>>(G, planes, jacc, c.ex, c.ey, c.dt, ph);
+        if (with_j) e_sweep_kernel<0, 1><<<g, b, 0, st>>>(G, planes, jacc, c.ex, c.ey, c.dt, ph, ps);
+        else e_sweep_kernel<0, 0><<<g, b, 0, st>>>(G, planes, jacc, c.ex, c.ey, c.dt, ph, ps);
     }
     LAUNCH_CHECK();
     return 0;

@@ -14,6 +14,7 @@ import contextlib
 import importlib
 import json
 import os
+import sys
 import time
 
 import numpy as np
@@ -213,10 +214,12 @@ def bench_main(args, w, rank, world, local, peak, peak_how):
             sim.sync()
             torch.cuda.synchronize()
         dist.barrier()
-        ms = torch.tensor([e0.elapsed_time(e1)], device=f"cuda:{local}", dtype=torch.float64)
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        npart = torch.tensor([sim.num_particles], device=f"cuda:{local}", dtype=torch.int64)
-        dist.all_reduce(npart)
+        # reductions of the two scalars through the object collective (host values; no stream-ordering subtleties between
+        # the library's non-blocking stream and the collective's own stream)
+        gathered = [None] * world
+        dist.all_gather_object(gathered, (float(e0.elapsed_time(e1)), int(sim.num_particles)))
+        ms_max = max(g[0] for g in gathered)
+        npart_total = sum(g[1] for g in gathered)
         launches = sim.kernel_launches - l0
 
         # end to end: every rank uploads its slab (fields + particles) from pinned host memory, steps once, reads it back
@@ -244,18 +247,19 @@ def bench_main(args, w, rank, world, local, peak, peak_how):
             for _ in range(ke):
                 host_step()
             torch.cuda.synchronize()
-            tw = torch.tensor([time.perf_counter() - t0], device=f"cuda:{local}", dtype=torch.float64)
-            dist.all_reduce(tw, op=dist.ReduceOp.MAX)
+            tws = [None] * world
+            dist.all_gather_object(tws, time.perf_counter() - t0)
+            tw_max = max(tws)
             nbytes = 6 * nx * w["ny"] * 8 + n_local * 52
-            e2e = {"value": float(npart.item()) * ke / tw.item(), "unit": "particles/s", "h2d_bytes_per_step": nbytes * world,
-                   "d2h_bytes_per_step": nbytes * world, "steps": ke, "ms_per_step": 1e3 * tw.item() / ke,
+            e2e = {"value": float(npart_total) * ke / tw_max, "unit": "particles/s", "h2d_bytes_per_step": nbytes * world,
+                   "d2h_bytes_per_step": nbytes * world, "steps": ke, "ms_per_step": 1e3 * tw_max / ke,
                    "api": "per rank: mpic_upload_planes + mpic_upload_particles, SlabStepper.step, mpic_download_*"}
     if rank == 0:
-        value = float(npart.item()) * K / (ms.item() * 1e-3)
+        value = float(npart_total) * K / (ms_max * 1e-3)
         out = {"metric": "particle-pushes/s (push+deposit+sort)", "value": value, "unit": "particles/s", "n_gpus": world,
-               "steps": K, "warmup": W, "ms_per_step": ms.item() / K, "higher_is_better": True, "scaling": "weak",
+               "steps": K, "warmup": W, "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "weak",
                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-               "config": {"workload": args.workload, **w, "ny_global": ny, "particles": int(npart.item()),
+               "config": {"workload": args.workload, **w, "ny_global": ny, "particles": int(npart_total),
                           "decomposition": f"{world} slabs of {w['ny']} cell rows, periodic ring, transport={transport}" + (" (CUDA-IPC peer memory: halos fused into the sweeps, remote atomics for J, flags for ordering)" if transport == "peer" else " (NCCL send/recv)"),
                           "l2": "per-rank particle state >> 126 MB L2 (no flush needed)"},
                "gpu_launches": int(launches), "clocks": clk.summary(), "migrated_records_rank0": int(stepper.moved),

@@ -52,7 +52,7 @@ def main():
     flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
 
     def rest():
-        sim.fold_current(); sim.step_b_half(); sim.step_e_full(); sim.step_b_half(); sim.sort_tiles()
+        sim.step_b_half(); sim.step_e_full(); sim.step_b_half(); sim.sort_tiles()
 
     def run(K, pre=None):
         evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
