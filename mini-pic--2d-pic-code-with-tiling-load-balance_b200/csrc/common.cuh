@@ -82,6 +82,13 @@ struct LeaveBufs {
     double* rec[2];       // AoS records of particles that left the slab downwards (0) / upwards (1)
     int* count;           // count[2]
     int cap;              // records per buffer
+    // peer-memory ring: the CTAs of the slab's first / last tile row await the neighbours' last field phase (their stores
+    // into this slab's guard rows) before staging their field patch -- no separate wait kernel in front of the push
+    const unsigned long long* wait_flags = nullptr;   // [0] lower, [1] upper neighbour
+    unsigned long long wait_want = 0;                 // 0: nothing to await
+    unsigned long long* wait_err = nullptr;
+    unsigned long long wait_timeout_ns = 0;
+    int wait_phase = 0;
 };
 
 void mpic_set_error(const char* fmt, ...);

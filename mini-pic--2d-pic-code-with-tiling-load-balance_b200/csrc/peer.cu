@@ -85,9 +85,22 @@ __global__ void peer_sync_kernel(unsigned long long* lo_flag, unsigned long long
 //                      (blockIdx.y = side*3g + plane*g + r)
 //   blockIdx.y >= 6g : leaver records (written by the push kernel) -> the neighbours' arrival buffers, plus the count
 //                      (blockIdx.y - 6g = direction)
+__device__ __forceinline__ void handoff_done(unsigned int* done, unsigned long long* sig_lo, unsigned long long* sig_hi,
+                                             unsigned long long sig) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        if (atomicAdd(done, 1u) == gridDim.x * gridDim.y - 1) {       // every CTA's remote stores are ordered before the flags
+            *done = 0;
+            st_release_sys(sig_lo, sig);
+            st_release_sys(sig_hi, sig);
+        }
+    }
+}
 __global__ void peer_handoff_kernel(FieldGeom G, unsigned long long* __restrict__ jacc, unsigned long long* lo_j, int64_t lo_plane,
                                     int lo_nyl, unsigned long long* hi_j, int64_t hi_plane, LeaveBufs lv, double* lo_dst,
-                                    unsigned long long* lo_cnt, int lo_cap, double* hi_dst, unsigned long long* hi_cnt, int hi_cap) {
+                                    unsigned long long* lo_cnt, int lo_cap, double* hi_dst, unsigned long long* hi_cnt, int hi_cap,
+                                    unsigned int* done, unsigned long long* sig_lo, unsigned long long* sig_hi, unsigned long long sig) {
     const int g = G.g;
     if ((int)blockIdx.y < 6 * g) {
         const int r = blockIdx.y % g, p = (blockIdx.y / g) % 3, side = blockIdx.y / (3 * g);
@@ -100,9 +113,9 @@ __global__ void peer_handoff_kernel(FieldGeom G, unsigned long long* __restrict_
             atomicAdd(dst, v);
             *mine = 0ull;
         }
+        handoff_done(done, sig_lo, sig_hi, sig);
         return;
     }
-    if (!lo_dst) return;                                 // no particle storage
     const int dir = blockIdx.y - 6 * g;
     const int raw = lv.count[dir];
     const int cap = dir ? hi_cap : lo_cap;
@@ -112,6 +125,16 @@ __global__ void peer_handoff_kernel(FieldGeom G, unsigned long long* __restrict_
     const int64_t total = (int64_t)n * MPIC_REC_DOUBLES;
     for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) dst[e] = src[e];
     if (blockIdx.x == 0 && threadIdx.x == 0) *(dir ? hi_cnt : lo_cnt) = (unsigned long long)raw;
+    handoff_done(done, sig_lo, sig_hi, sig);
+}
+
+// migration counts -> host (mapped pinned memory); launched behind the first half-B sweep, whose edge CTAs awaited both J flags
+__global__ void peer_counts_kernel(const int* leave_cnt, const unsigned long long* arrive_cnt, const unsigned long long* err,
+                                   volatile long long* host_out) {
+    const int t = threadIdx.x;
+    if (t < 2) { host_out[t] = leave_cnt[t]; host_out[2 + t] = (long long)ld_acquire_sys(arrive_cnt + t); }
+    if (t == 2) host_out[4] = (long long)ld_acquire_sys(err);
+    __threadfence_system();
 }
 
 // whole edge rows (x guards included) of `nplanes` planes -> neighbours' guard rows; used after uploads
@@ -270,7 +293,8 @@ int mpic_peer_connect(mpic_sim* s, const mpic_peer_info* lo, const mpic_peer_inf
     TRY(particles_preload());
     {
         cudaFuncAttributes a;
-        const void* fs[] = { (const void*)peer_sync_kernel, (const void*)peer_handoff_kernel, (const void*)peer_halo_push_kernel };
+        const void* fs[] = { (const void*)peer_sync_kernel, (const void*)peer_handoff_kernel, (const void*)peer_halo_push_kernel,
+                             (const void*)peer_counts_kernel };
         for (const void* f : fs) CUDA_TRY(cudaFuncGetAttributes(&a, f));
     }
     if (const char* e = getenv("MPIC_PEER_TRACE")) if (atoi(e) > 0 && !s->trace) {
@@ -313,9 +337,17 @@ static PeerSync sweep_sync(mpic_sim* s, int wait_ph, int sig_ph) {
     ps.err = s->ctl + CTL_ERROR; ps.timeout_ns = timeout_ns(); ps.phase = wait_ph;
     return ps;
 }
-static int yee_phases(mpic_sim* s, int with_j) {
+static int yee_phases(mpic_sim* s, int with_j, int par = -1) {
     const PeerHalo h = halo_of(s);
-    TRY(launch_b_sweep(s->G, s->planes, s->cf, h, sweep_sync(s, PH_E, PH_B1), s->st));
+    // in a PIC step the first half-B awaits the neighbours' J phase (they pushed, shipped, added their current -- and hence
+    // finished reading the guard rows this sweep overwrites); in a field-only step, their last E sweep
+    TRY(launch_b_sweep(s->G, s->planes, s->cf, h, sweep_sync(s, par >= 0 ? PH_J : PH_E, PH_B1), s->st));
+    if (par >= 0) {
+        peer_counts_kernel<<<1, 32, 0, s->st>>>(s->lv.count, s->ctl + CTL_ARRIVE + par * 2, s->ctl + CTL_ERROR, (volatile long long*)s->h_counts);
+        LAUNCH_CHECK();
+        CUDA_TRY(cudaEventRecord(s->ev_counts, s->st));    // the one host wait of the step is taken on this event in step_end
+        s->launches++;
+    }
     tp(s, 6); tp(s, 7);
     TRY(launch_e_sweep(s->G, s->planes, s->jacc, with_j, s->cf, h, sweep_sync(s, PH_B1, PH_E), s->st));
     tp(s, 8); tp(s, 9);
@@ -344,27 +376,30 @@ int mpic_peer_step_begin(mpic_sim* s) {
     const int par = (int)(++s->step_no & 1);
     const FieldGeom& G = s->G;
     tp(s, 0);
-    TRY(b2_wait_if_pending(s));                          // the neighbours' B guards of the previous step
+    if (s->b2_pending) {                                 // awaited by the push kernel's slab-edge CTAs themselves
+        s->b2_pending = false;
+        s->lv.wait_flags = s->ctl + s->pending_ph * 2; s->lv.wait_want = s->epoch[s->pending_ph];
+        s->lv.wait_err = s->ctl + CTL_ERROR; s->lv.wait_timeout_ns = timeout_ns(); s->lv.wait_phase = s->pending_ph;
+    }
     tp(s, 1);
-    TRY(mpic_push_deposit(s));
+    const int rc = mpic_push_deposit(s);
+    s->lv.wait_want = 0;
+    TRY(rc);
     tp(s, 2);
     const int64_t rec = MPIC_REC_DOUBLES;
-    // my leavers going DOWN arrive at the lower neighbour "from above" (side 1); going UP: at the upper neighbour's side 0
+    // ONE launch hands over the current guard rows (remote adds) and the leaver records, and its last CTA raises the J flag.
+    // My leavers going DOWN arrive at the lower neighbour "from above" (side 1); going UP: at the upper neighbour's side 0.
     const int gx = ceil_div(G.pitch, 256) > 16 ? ceil_div(G.pitch, 256) : 16;
+    const unsigned long long ej = ++s->epoch[PH_J];
     peer_handoff_kernel<<<dim3(gx, 6 * G.g + 2), 256, 0, s->st>>>(G, (unsigned long long*)s->jacc, s->peer[0].jacc, s->peer[0].plane,
         s->peer[0].nyl, s->peer[1].jacc, s->peer[1].plane, s->lv,
         s->peer[0].arrive + (int64_t)(par * 2 + 1) * s->peer[0].lcap * rec, s->peer[0].ctl + CTL_ARRIVE + par * 2 + 1, s->peer[0].lcap,
-        s->peer[1].arrive + (int64_t)(par * 2 + 0) * s->peer[1].lcap * rec, s->peer[1].ctl + CTL_ARRIVE + par * 2 + 0, s->peer[1].lcap);
+        s->peer[1].arrive + (int64_t)(par * 2 + 0) * s->peer[1].lcap * rec, s->peer[1].ctl + CTL_ARRIVE + par * 2 + 0, s->peer[1].lcap,
+        (unsigned int*)(s->ctl + CTL_DONE) + 2, s->peer[0].ctl + PH_J * 2 + 1, s->peer[1].ctl + PH_J * 2 + 0, ej);
     LAUNCH_CHECK();
     s->launches++;
-    tp(s, 3);
-    // neighbours pushed, shipped and added their current; the same kernel hands the counts to the host (the one host wait of
-    // the step is taken in step_end, i.e. after the field phases have been enqueued)
-    TRY(phase_launch(s, PH_J, true, true, true, par));
-    CUDA_TRY(cudaEventRecord(s->ev_counts, s->st));
-    tp(s, 4);
-    tp(s, 5);                                            // (the E sweep folds the x guards of J on the fly)
-    return yee_phases(s, 1);
+    tp(s, 3); tp(s, 4); tp(s, 5);
+    return yee_phases(s, 1, par);
 }
 
 int mpic_peer_step_end(mpic_sim* s) {

@@ -51,6 +51,14 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned 
     asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
+// With fused ordering the CTA rows that own the slab's UPPER edge are scheduled right after the lower-edge row (CTAs are
+// dispatched in blockIdx order): both edges' flag waits, remote stores and fences then overlap the interior of the sweep
+// instead of sitting in its tail.  Block row 0 -> 0, 1 -> last, 2 -> last-1, k>=3 -> k-2 (two top rows can hold edge rows).
+__device__ __forceinline__ int edge_first_row(const PeerSync& S) {
+    const int b = blockIdx.y, n = gridDim.y;
+    if (!S.done || n < 4) return b;
+    return b == 0 ? 0 : (b == 1 ? n - 1 : (b == 2 ? n - 2 : b - 2));
+}
 // edge CTAs: wait for the neighbour(s) whose guard rows this CTA reads / writes (see PeerSync)
 __device__ __forceinline__ void edge_wait(const PeerSync& S, bool lo_edge, bool hi_edge) {
     if (!(lo_edge || hi_edge)) return;
@@ -88,9 +96,10 @@ __device__ __forceinline__ void edge_signal(const PeerSync& S, bool lo_edge, boo
 
 template <int FMA>
 __global__ void __launch_bounds__(256) b_sweep_kernel(FieldGeom G, double* __restrict__ f, double cx, double cy, PeerHalo H, PeerSync S) {
+    const int brow = edge_first_row(S);
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const int j = blockIdx.y * blockDim.y + threadIdx.y;
-    const int j0 = blockIdx.y * blockDim.y;
+    const int j = brow * blockDim.y + threadIdx.y;
+    const int j0 = brow * blockDim.y;
     const bool lo_edge = S.done && j0 < G.g, hi_edge = S.done && j0 + (int)blockDim.y > G.nyl - G.g;
     edge_wait(S, lo_edge, hi_edge);
     if (i < G.nx && j < G.nyl) {
@@ -124,9 +133,10 @@ __global__ void __launch_bounds__(256) b_sweep_kernel(FieldGeom G, double* __res
 template <int FMA, int WITH_J>
 __global__ void __launch_bounds__(256) e_sweep_kernel(FieldGeom G, double* __restrict__ f, int64_t* __restrict__ jacc,
                                                       double cx, double cy, double dt, PeerHalo H, PeerSync S) {
+    const int brow = edge_first_row(S);
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const int j = blockIdx.y * blockDim.y + threadIdx.y;
-    const int j0 = blockIdx.y * blockDim.y;
+    const int j = brow * blockDim.y + threadIdx.y;
+    const int j0 = brow * blockDim.y;
     const bool lo_edge = S.done && j0 < G.g, hi_edge = S.done && j0 + (int)blockDim.y > G.nyl - G.g;
     edge_wait(S, lo_edge, hi_edge);
     if (i < G.nx && j < G.nyl) {
