@@ -34,6 +34,10 @@ WORKLOADS = {
     "thermal_128": dict(nx=128, ny=128, tn=16, ppc=16, u_th=0.05, two_stream=0.0, dx=0.1),
     # configs[3] per-GPU share at 8 GPUs
     "uniform_2048": dict(nx=2048, ny=2048, tn=16, ppc=64, u_th=0.05, two_stream=0.0, dx=0.1),
+    # configs[3] (4096^2, 64 ppc, 1.07 B particles) per-GPU slab at 8 GPUs: 4096 x 512 cells, 134 M particles per rank
+    "uniform_c4_slab": dict(nx=4096, ny=512, tn=16, ppc=64, u_th=0.05, two_stream=0.0, dx=0.1),
+    # configs[4] per-GPU slab: thermal background 8 ppc + drifting beam 80 ppc in the band y in [0.45,0.55) of the GLOBAL box
+    "beam_c5_slab": dict(nx=4096, ny=512, tn=16, ppc=8, u_th=0.05, two_stream=0.0, dx=0.1, beam_ppc=80, beam_band=(0.45, 0.55), beam_drift=0.5, beam_u_th=0.01),
 }
 # push_deposit_kernel is fused with the sort's data movement: it gathers every particle through the slot->storage
 # permutation and writes the other buffer in sorted order, so its algorithmic traffic is one full read + one full write

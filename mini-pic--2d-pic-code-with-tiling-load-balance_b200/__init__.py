@@ -151,15 +151,18 @@ class Sim:
     """Device-resident simulation (L1 API).  Mirrors the phases of the reference loop PIC_2D.cpp:171-420."""
 
     def __init__(self, nx, ny, tnx, tny, dx, dy, dt, guard=2, scheme=0, fma_mode=0, qm=-1.0, max_particles=0,
-                 rank=0, nranks=1, device=0):
+                 rank=0, nranks=1, device=0, rows=None):
+        """rows=(row0, nrows): this rank's tile rows (default: the even split of mpic_slab_rows; the rebalancer in slab.py
+        passes uneven ones)."""
         L = lib()
         gtr = ny // tny
-        row0, nrows = slab_rows(gtr, nranks, rank)
+        row0, nrows = rows if rows is not None else slab_rows(gtr, nranks, rank)
         self.p = Params(nx, ny, tnx, tny, guard, scheme, fma_mode, rank, nranks, row0, nrows, device, dx, dy, dt, qm,
                         max_particles)
         self.h = C.c_void_p()
         _chk(L.mpic_create(C.byref(self.p), C.byref(self.h)))
         self.nx, self.ny, self.tnx, self.tny, self.guard = nx, ny, tnx, tny, guard
+        self.dx, self.dy, self.dt = dx, dy, dt
         self.nyl = nrows * tny
         self.row0, self.nrows = row0, nrows
         self.gtc, self.gtr = nx // tnx, gtr

@@ -176,6 +176,104 @@ def balanced_slab_rows(row_costs, nranks):
     return parts
 
 
+def rebalance(sim, rank, world, make_sim, dist=None, group=None, w_cell=0.25, min_gain=0.05):
+    """Cost-driven re-partition of the tile rows over the ranks -- the load balancer the reference names as its purpose
+    but ships only as a hard-coded demo (PIC_2D.cpp:399-412 moves three tiles at step 5; removeTileFromRank /
+    addTileToRank, Auxiliar_functions.cpp:242-272, send the grid and DROP the particles).
+
+    Collective over all ranks.  (1) per-tile-row particle counts (the tile occupancy the sort maintains) are gathered;
+    (2) `balanced_slab_rows` minimises the most loaded slab under cost = particles + w_cell * cells; (3) unless the gain is
+    below `min_gain`, every rank ships the rows it loses -- field rows AND the particles inside them -- to their new owners
+    (point-to-point, sizes agreed through one small object all-gather) and builds its new handle with
+    `make_sim(row0, nrows, n_particles)`.  Results are partition-independent bit for bit (SURVEY.md F8 + fixed-point J), so a
+    rebalanced run equals the un-rebalanced one.  Returns (sim, [(row0, nrows)] per rank, changed); the caller reconnects
+    its stepper (guards are refreshed from the neighbours) and closes the old handle after a barrier."""
+    import torch
+    if dist is None:
+        import torch.distributed as dist
+    tny, gtc = sim.tny, sim.gtc
+    counts = np.asarray(sim.tile_counts(), dtype=np.int64).reshape(sim.nrows, gtc).sum(axis=1)
+    allr = [None] * world
+    dist.all_gather_object(allr, (int(sim.row0), int(sim.nrows), counts.tolist()), group=group)
+    old = [(a[0], a[1]) for a in allr]
+    gtr = sum(nr for _, nr in old)
+    rowp = np.zeros(gtr)
+    for r0, nr, c in allr:
+        rowp[r0:r0 + nr] = c
+    costs = tile_row_costs(rowp, 1, 1, w_cell=0.0) + w_cell * gtc * sim.tnx * tny
+    new = balanced_slab_rows(costs, world)
+    worst = lambda parts: max(costs[r0:r0 + nr].sum() for r0, nr in parts)
+    if new == old or worst(new) > (1.0 - min_gain) * worst(old):
+        return sim, old, False
+
+    planes = sim.download_planes()
+    parts = sim.download_particles()
+    prow = (np.floor(parts["y"] * (1.0 / sim.dy)).astype(np.int64)) // tny          # global tile row of every particle
+    my0, my1 = old[rank][0], old[rank][0] + old[rank][1]
+    overlap = lambda a, b: (max(a[0], b[0]), min(a[0] + a[1], b[0] + b[1]))
+
+    def piece(lo, hi):                       # rows [lo, hi) of my slab: field rows + the particles inside them
+        sel = (prow >= lo) & (prow < hi)
+        f = np.stack([a[(lo - my0) * tny:(hi - my0) * tny] for a in planes])
+        return f, {k: np.ascontiguousarray(v[sel]) for k, v in parts.items()}
+
+    outgoing = {}
+    for d in range(world):
+        lo, hi = overlap(old[rank], new[d])
+        if hi > lo:
+            outgoing[d] = (lo, hi) + piece(lo, hi)
+    meta = [None] * world
+    dist.all_gather_object(meta, {d: (lo, hi, int(pp["x"].shape[0])) for d, (lo, hi, _, pp) in outgoing.items()}, group=group)
+    on_gpu = dist.get_backend(group) == "nccl"
+    ship = (lambda t: t.cuda()) if on_gpu else (lambda t: t)
+    ops, keep, incoming = [], [], {}
+    for d, (lo, hi, f, pp) in outgoing.items():
+        if d == rank:
+            continue
+        body = torch.from_numpy(np.concatenate([f.ravel()] + [pp[k] for k in ("x", "y", "ux", "uy", "uz", "q")]))
+        tags = torch.from_numpy(pp["tag"].astype(np.int32))
+        for t in (body, tags):
+            if t.numel():
+                t = ship(t)
+                keep.append(t)
+                ops.append(dist.P2POp(dist.isend, t, d, group))
+    for src in range(world):
+        if src == rank or rank not in meta[src]:
+            continue
+        lo, hi, n = meta[src][rank]
+        body = torch.empty(6 * (hi - lo) * tny * sim.nx + 6 * n, dtype=torch.float64, device="cuda" if on_gpu else "cpu")
+        tags = torch.empty(n, dtype=torch.int32, device="cuda" if on_gpu else "cpu")
+        incoming[src] = (lo, hi, n, body, tags)
+        for t in (body, tags):
+            if t.numel():
+                ops.append(dist.P2POp(dist.irecv, t, src, group))
+    if ops:
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+    pieces = []
+    if rank in outgoing:
+        lo, hi, f, pp = outgoing[rank]
+        pieces.append((lo, f, pp))
+    for src, (lo, hi, n, body, tags) in incoming.items():
+        b = body.cpu().numpy()
+        nf = 6 * (hi - lo) * tny * sim.nx
+        pp = {k: b[nf + i * n: nf + (i + 1) * n].copy() for i, k in enumerate(("x", "y", "ux", "uy", "uz", "q"))}
+        pp["tag"] = tags.cpu().numpy().copy()
+        pieces.append((lo, b[:nf].reshape(6, (hi - lo) * tny, sim.nx), pp))
+    pieces.sort(key=lambda t: t[0])
+    new_planes = [np.ascontiguousarray(np.concatenate([f[k] for _, f, _ in pieces])) for k in range(6)]
+    new_parts = {k: np.concatenate([pp[k] for _, _, pp in pieces]) for k in ("x", "y", "ux", "uy", "uz", "q", "tag")}
+    out = make_sim(new[rank][0], new[rank][1], int(new_parts["x"].shape[0]))
+    out.upload_planes(new_planes)
+    out.upload_particles(new_parts)
+    if hasattr(out, "set_owner"):            # the replicated tile -> rank map of the reference (owner[], PIC_2D.cpp:55)
+        owner = np.empty(gtr * gtc, dtype=np.int32)
+        for r, (r0, nr) in enumerate(new):
+            owner[r0 * gtc:(r0 + nr) * gtc] = r
+        out.set_owner(owner)
+    return out, new, True
+
+
 # ------------------------------------------------------------------------------------------------ multi-GPU bench
 def bench_main(args, w, rank, world, local, peak, peak_how):
     """bench.py for N > 1 (torchrun, one rank per GPU): weak scaling -- every rank owns an (ny x nx) slab of an

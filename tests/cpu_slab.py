@@ -22,6 +22,7 @@ class CpuSlabSim:
     def __init__(self, nx, ny, tnx, tny, dx, dy, dt, rank, nranks, row0, nrows):
         self.lib = ob.load_oracle()
         self.nx, self.ny, self.tny, self.dx, self.dy, self.dt = nx, ny, tny, dx, dy, dt
+        self.tnx, self.gtc, self.row0, self.nrows = tnx, nx // tnx, row0, nrows
         self.P = ob.make_params(self.lib, nx, ny, tnx, tny, dx, dy, dt)
         self.cy0, self.nyl = row0 * tny, nrows * tny
         self.rows_int = np.arange(self.cy0, self.cy0 + self.nyl)
@@ -40,6 +41,25 @@ class CpuSlabSim:
         self.leave = [0, 0]
         self.left_mask = None
         self.arrivals = []
+
+    # ---- the Sim methods slab.rebalance() uses
+    def tile_counts(self):
+        cx = np.floor(self.parts["x"] * (1.0 / self.dx)).astype(np.int64) // self.tnx
+        cy = np.floor(self.parts["y"] * (1.0 / self.dy)).astype(np.int64) // self.tny - self.row0
+        return np.bincount(cy * self.gtc + cx, minlength=self.nrows * self.gtc).astype(np.int32)
+
+    def download_planes(self):
+        return [a[self.rows_int].copy() for a in self.planes]
+
+    def download_particles(self):
+        return {k: v.copy() for k, v in self.parts.items()}
+
+    def upload_planes(self, local_planes):
+        for a, b in zip(self.planes, local_planes):
+            a[self.rows_int] = b
+
+    def upload_particles(self, parts):
+        self.set_particles(parts)
 
     # ---- state in / out
     def set_interior(self, global_planes):

@@ -234,3 +234,80 @@ def test_nccl_slabs_two_processes():
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     assert "SLAB_NCCL_PARITY_OK" in r.stdout
+
+
+def _rebalance_gpu_worker(rank, world, port, steps, outdir):
+    import torch
+    import torch.distributed as dist
+    for p in (ROOT, os.path.join(ROOT, "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    from test_slab_gloo import _beam_problem
+    m = importlib.import_module(PKG)
+    slab = importlib.import_module(PKG + ".slab")
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    dev = rank % max(1, torch.cuda.device_count())
+    try:
+        g, parts, planes = _beam_problem()
+        cap = parts["x"].shape[0]
+        make = lambda r0, nr, n=0: m.Sim(g["nx"], g["ny"], g["tnx"], g["tny"], g["dx"], g["dy"], g["dt"], max_particles=cap,
+                                          rank=rank, nranks=world, device=dev, rows=(r0, nr))
+        sim = m.Sim(g["nx"], g["ny"], g["tnx"], g["tny"], g["dx"], g["dy"], g["dt"], max_particles=cap, rank=rank, nranks=world, device=dev)
+        r0, r1 = sim.row0 * g["tny"], (sim.row0 + sim.nrows) * g["tny"]
+        sim.upload_planes([a[r0:r1] for a in planes])
+        sim.upload_particles(parts)
+        st = slab.PeerStepper(sim, rank, world, dist)
+        st.refresh_guards()
+        for _ in range(steps):
+            st.step()
+        sim.sync()
+        before = sim.num_particles
+        new, rows, changed = slab.rebalance(sim, rank, world, make, dist)
+        dist.barrier()                     # nobody touches the old handles any more
+        if changed:
+            sim.close()
+        sim = new
+        st = slab.PeerStepper(sim, rank, world, dist)
+        st.refresh_guards()
+        for _ in range(steps):
+            st.step()
+        sim.sync()
+        dist.barrier()
+        pl = sim.download_planes()
+        np.savez(os.path.join(outdir, f"rank{rank}.npz"), row0=sim.row0 * g["tny"], changed=changed, before=before,
+                 after=sim.num_particles, counts=sim.tile_counts(), **{f"f{k}": pl[k] for k in range(6)}, **sim.download_particles())
+        dist.barrier()
+        sim.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_runtime_rebalance_over_the_peer_ring(world):
+    """One process per rank (CUDA IPC between them, all on one GPU when the box has one): peer-ring steps, cost-driven
+    re-partition of tile rows with their fields and particles (slab.rebalance), peer-ring steps on the new, uneven slabs.
+    Bit-exact versus the single-rank oracle; the most loaded rank gets lighter."""
+    import tempfile
+    import torch.multiprocessing as mp
+    from test_slab_gloo import _beam_problem, _free_port
+    steps = 3
+    with tempfile.TemporaryDirectory() as d:
+        mp.spawn(_rebalance_gpu_worker, args=(world, _free_port(), steps, d), nprocs=world, join=True)
+        outs = [np.load(os.path.join(d, f"rank{r}.npz")) for r in range(world)]
+    g, parts, planes = _beam_problem()
+    lib = ob.load_oracle()
+    P = ob.make_params(lib, g["nx"], g["ny"], g["tnx"], g["tny"], g["dx"], g["dy"], g["dt"])
+    want, wf = copy_parts(parts), [a.copy() for a in planes]
+    counts, _ = ob.pic_steps(lib, P, wf, want, 2 * steps)
+    got = by_tag({k: np.concatenate([o[k] for o in outs]) for k in ("x", "y", "ux", "uy", "uz", "q", "tag")})
+    want = by_tag(want)
+    assert np.array_equal(got["tag"], want["tag"])
+    for k in ("x", "y", "ux", "uy", "uz", "q"):
+        assert np.array_equal(got[k], want[k]), k
+    outs.sort(key=lambda o: int(o["row0"]))
+    for k in range(6):
+        assert np.array_equal(np.concatenate([o[f"f{k}"] for o in outs]), wf[k]), k
+    assert np.array_equal(np.concatenate([o["counts"] for o in outs]), counts)
+    assert all(bool(o["changed"]) for o in outs)
+    assert max(int(o["after"]) for o in outs) < 0.8 * max(int(o["before"]) for o in outs)

@@ -84,6 +84,78 @@ def test_slab_ring_matches_single_rank_oracle(world, rows):
             assert ((cy >= o["rows"][0]) & (cy <= o["rows"][-1])).all()
 
 
+def _beam_problem():
+    """thin dense band (6x the background) in the lowest tile rows: an even split is badly imbalanced"""
+    g, parts, planes = _problem(seed=9, ny=64, ppc=3)
+    extra = plasma().load_uniform(g["nx"], g["ny"], g["tnx"], g["tny"], g["dx"], g["dy"], 18, u_th=0.4, seed=10, drift=(0.3, 0.0, 0.0))
+    band = extra["y"] < 12 * g["dy"]
+    extra = {k: v[band] for k, v in extra.items()}
+    extra["tag"] = (extra["tag"].astype(np.int64) + 10 ** 6).astype(np.int32)
+    return g, {k: np.concatenate([parts[k], extra[k]]) for k in parts}, planes
+
+
+def _rebalance_worker(rank, world, port, steps, outdir):
+    for p in (ROOT, os.path.join(ROOT, "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import torch.distributed as dist
+    from cpu_slab import CpuSlabSim
+    slab = importlib.import_module(PKG + ".slab")
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        g, parts, planes = _beam_problem()
+        gtr = g["ny"] // g["tny"]
+        make = lambda r0, nr, n=0: CpuSlabSim(g["nx"], g["ny"], g["tnx"], g["tny"], g["dx"], g["dy"], g["dt"], rank, world, r0, nr)
+        base, rem = divmod(gtr, world)
+        sim = make(rank * base + min(rank, rem), base + (rank < rem))
+        sim.set_interior(planes)
+        sim.set_particles(parts)
+        st = slab.SlabStepper(sim, slab.Ring(rank, world))
+        st.refresh_guards()
+        for _ in range(steps):
+            st.step()
+        before = int(sim.parts["x"].shape[0])
+        sim, rows, changed = slab.rebalance(sim, rank, world, make, dist)
+        st = slab.SlabStepper(sim, slab.Ring(rank, world))
+        st.refresh_guards()
+        for _ in range(steps):
+            st.step()
+        np.savez(os.path.join(outdir, f"rank{rank}.npz"), rows=sim.rows_int, changed=changed, before=before,
+                 after=int(sim.parts["x"].shape[0]), new_rows=np.array(rows),
+                 **{f"f{k}": sim.planes[k][sim.rows_int] for k in range(6)}, **sim.parts)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_runtime_rebalance_is_bit_exact_and_evens_the_load(world):
+    """slab.rebalance (cost-driven re-partition of tile rows with their fields AND particles) in the
+    middle of a run: the result still equals the single-rank oracle bit for bit, and the most loaded rank gets lighter."""
+    from oracle import bindings as ob
+    steps = 3
+    with tempfile.TemporaryDirectory() as d:
+        mp.spawn(_rebalance_worker, args=(world, _free_port(), steps, d), nprocs=world, join=True)
+        outs = [np.load(os.path.join(d, f"rank{r}.npz")) for r in range(world)]
+        g, parts, planes = _beam_problem()
+        lib = ob.load_oracle()
+        P = ob.make_params(lib, g["nx"], g["ny"], g["tnx"], g["tny"], g["dx"], g["dy"], g["dt"])
+        want, wf = copy_parts(parts), [a.copy() for a in planes]
+        ob.pic_steps(lib, P, wf, want, 2 * steps)
+        got = by_tag({k: np.concatenate([o[k] for o in outs]) for k in ("x", "y", "ux", "uy", "uz", "q", "tag")})
+        want = by_tag(want)
+        assert np.array_equal(got["tag"], want["tag"])
+        for k in ("x", "y", "ux", "uy", "uz", "q"):
+            assert np.array_equal(got[k], want[k]), k
+        for o in outs:
+            for k in range(6):
+                assert np.array_equal(o[f"f{k}"], wf[k][o["rows"]]), k
+        assert all(bool(o["changed"]) for o in outs)
+        assert max(int(o["after"]) for o in outs) < 0.8 * max(int(o["before"]) for o in outs)
+        rows = outs[0]["new_rows"]
+        assert rows[0][0] == 0 and all(rows[i][0] + rows[i][1] == rows[i + 1][0] for i in range(world - 1))
+
+
 def test_balanced_slab_rows_policy():
     slab = importlib.import_module(PKG + ".slab")
     # uniform load -> even split
