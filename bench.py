@@ -51,6 +51,23 @@ YEE_BYTES_3SWEEP = 216.0           # reference-faithful half-B, E, half-B: 3 x 7
 YEE_BYTES_ALGO = 144.0             # SURVEY.md section 8(d) algorithmic figure (2 sweeps)
 
 
+def load_workload(sim, w):
+    """Populate `sim` with the workload's plasma (device loader, partition-independent: counter-based RNG keyed by tag)."""
+    sim.load_uniform(w["ppc"], u_th=w["u_th"], two_stream=w["two_stream"], seed=12345)
+    if "beam_ppc" in w:      # configs[4]: dense drifting beam confined to a band of the GLOBAL box (same macro-weight as the background)
+        sim.load_uniform(w["beam_ppc"], u_th=w["beam_u_th"], drift=(w["beam_drift"], 0.0, 0.0), band=tuple(w["beam_band"]),
+                         density=float(w["beam_ppc"]) / w["ppc"], seed=777, append=True)
+
+
+def expected_particles(w, ny_global, cy_lo, cy_hi):
+    """Particles the loader puts into global cell rows [cy_lo, cy_hi)."""
+    n = w["nx"] * (cy_hi - cy_lo) * w["ppc"]
+    if "beam_ppc" in w:
+        lo, hi = int(round(w["beam_band"][0] * ny_global)), int(round(w["beam_band"][1] * ny_global))
+        n += w["nx"] * max(0, min(hi, cy_hi) - max(lo, cy_lo)) * w["beam_ppc"]
+    return n
+
+
 def measured_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -201,9 +218,9 @@ def main():
     nx, ny, tn, ppc = w["nx"], w["ny"], w["tn"], w["ppc"]
     dx = dy = w["dx"]
     dt = m.courant_dt(dx, dy)
-    n = nx * ny * ppc
+    n = expected_particles(w, ny, 0, ny)
     sim = m.Sim(nx, ny, tn, tn, dx, dy, dt, max_particles=n + 1024, device=local)
-    sim.load_uniform(ppc, u_th=w["u_th"], two_stream=w["two_stream"], seed=12345)
+    load_workload(sim, w)
     sim.sync()
     assert sim.num_particles == n
     st = torch.cuda.ExternalStream(sim.stream)
@@ -251,7 +268,7 @@ def main():
         "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
         "config": {"workload": args.workload, **w, "particles": n, "tile": f"{tn}x{tn}", "dt": dt,
-                   "l2": "particle state 0.87 GB per pass >> 126 MB L2 (no flush needed)"},
+                   "l2": f"particle state {n * 52 / 1e9:.2f} GB per pass >> 126 MB L2 (no flush needed)"},
         "phases_ms": {"push_deposit": push_ms, "fields_and_fold": field_ms, "sort": sort_ms},
         "roofline": {"bound": "hbm", "kernel": "push_deposit_kernel", "achieved": push_gbs, "peak": peak, "unit": "GB/s",
                      "frac": push_gbs / peak, "traffic": NCU_TRAFFIC_BYTES_PER_PARTICLE * n, "bytes_per_particle": PUSH_BYTES_PER_PARTICLE,

@@ -286,40 +286,68 @@ def bench_main(args, w, rank, world, local, peak, peak_how):
     nx, ny, tn, ppc = w["nx"], w["ny"] * world, w["tn"], w["ppc"]
     dx = dy = w["dx"]
     dt = m.courant_dt(dx, dy)
-    n_local = nx * w["ny"] * ppc
-    sim = m.Sim(nx, ny, tn, tn, dx, dy, dt, max_particles=int(n_local * 1.05) + 4096, rank=rank, nranks=world, device=local)
-    sim.load_uniform(ppc, u_th=w["u_th"], two_stream=w["two_stream"], seed=12345)
+    gtr = ny // tn
+    row0, nrows = m.slab_rows(gtr, world, rank)
+    n_local = bench.expected_particles(w, ny, row0 * tn, (row0 + nrows) * tn)
+    make = lambda r0, nr, n=0: m.Sim(nx, ny, tn, tn, dx, dy, dt, max_particles=int(max(n, 1) * 1.05) + 4096, rank=rank,
+                                     nranks=world, device=local, rows=(r0, nr))
+    sim = make(row0, nrows, n_local)
+    bench.load_workload(sim, w)
     sim.sync()
     st = sim.torch_stream()
     K, W = args.steps, max(args.warmup, 3)
-    with torch.cuda.stream(st):
-        transport = os.environ.get("MPIC_TRANSPORT", "peer")
-        stepper = PeerStepper(sim, rank, world) if transport == "peer" else SlabStepper(sim, Ring(rank, world))
-        stepper.refresh_guards()
-        for _ in range(W):
-            stepper.step()
-        sim.sync()
-        dist.barrier()
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        l0 = sim.kernel_launches
-        clk = bench.ClockSampler(local) if rank == 0 else contextlib.nullcontext()
-        with clk:
-            e0.record(st)
-            for _ in range(K):
-                stepper.step()
-            e1.record(st)
-            sim.sync()
-            torch.cuda.synchronize()
-        dist.barrier()
-        # reductions of the two scalars through the object collective (host values; no stream-ordering subtleties between
-        # the library's non-blocking stream and the collective's own stream)
-        gathered = [None] * world
-        dist.all_gather_object(gathered, (float(e0.elapsed_time(e1)), int(sim.num_particles)))
-        ms_max = max(g[0] for g in gathered)
-        npart_total = sum(g[1] for g in gathered)
-        launches = sim.kernel_launches - l0
+    transport = os.environ.get("MPIC_TRANSPORT", "peer")
+    new_stepper = lambda s_: PeerStepper(s_, rank, world) if transport == "peer" else SlabStepper(s_, Ring(rank, world))
 
+    def timed(stepper, s_, stream, clocks=False):
+        """W warm-up + K timed steps; returns (max-over-ranks ms, total particles, launches, per-rank (ms, particles), clocks)."""
+        with torch.cuda.stream(stream):
+            stepper.refresh_guards()
+            for _ in range(W):
+                stepper.step()
+            s_.sync()
+            dist.barrier()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            l0 = s_.kernel_launches
+            clk = bench.ClockSampler(local) if (rank == 0 and clocks) else contextlib.nullcontext()
+            with clk:
+                e0.record(stream)
+                for _ in range(K):
+                    stepper.step()
+                e1.record(stream)
+                s_.sync()
+                torch.cuda.synchronize()
+            dist.barrier()
+            # the two scalars go through the object collective (host values; no stream-ordering subtleties between the
+            # library's non-blocking stream and the collective's own stream)
+            gathered = [None] * world
+            dist.all_gather_object(gathered, (float(e0.elapsed_time(e1)), int(s_.num_particles), int(s_.nrows)))
+        return (max(g[0] for g in gathered), sum(g[1] for g in gathered), s_.kernel_launches - l0, gathered,
+                clk.summary() if (rank == 0 and clocks) else None)
+
+    stepper = new_stepper(sim)
+    rebal = None
+    if "beam_ppc" in w and not os.environ.get("MPIC_NO_REBALANCE"):
+        # configs[4]: time the even split first, then let the cost-driven rebalancer move tile rows (fields + particles)
+        ms0, np0, _, per0, _ = timed(stepper, sim, st)
+        new, rows, changed = rebalance(sim, rank, world, make, dist)
+        dist.barrier()
+        if changed:
+            sim.close()
+            sim = new
+            st = sim.torch_stream()
+            stepper = new_stepper(sim)
+        rebal = {"changed": bool(changed), "even_split": {"ms_per_step": ms0 / K, "particles_per_rank": [g[1] for g in per0],
+                                                          "tile_rows_per_rank": [g[2] for g in per0],
+                                                          "pushes_per_s": float(np0) * K / (ms0 * 1e-3)},
+                 "policy": "slab.balanced_slab_rows on cost = particles + 0.25 * cells per tile row"}
+    ms_max, npart_total, launches, per, clocks = timed(stepper, sim, st, clocks=True)
+    if rebal is not None:
+        rebal["rebalanced"] = {"ms_per_step": ms_max / K, "particles_per_rank": [g[1] for g in per],
+                               "tile_rows_per_rank": [g[2] for g in per]}
+    n_local = int(sim.num_particles)
+    with torch.cuda.stream(st):
         # end to end: every rank uploads its slab (fields + particles) from pinned host memory, steps once, reads it back
         e2e = None
         if not args.no_e2e:
@@ -348,9 +376,9 @@ def bench_main(args, w, rank, world, local, peak, peak_how):
             tws = [None] * world
             dist.all_gather_object(tws, time.perf_counter() - t0)
             tw_max = max(tws)
-            nbytes = 6 * nx * w["ny"] * 8 + n_local * 52
-            e2e = {"value": float(npart_total) * ke / tw_max, "unit": "particles/s", "h2d_bytes_per_step": nbytes * world,
-                   "d2h_bytes_per_step": nbytes * world, "steps": ke, "ms_per_step": 1e3 * tw_max / ke,
+            nbytes = 6 * nx * ny * 8 + int(npart_total) * 52
+            e2e = {"value": float(npart_total) * ke / tw_max, "unit": "particles/s", "h2d_bytes_per_step": nbytes,
+                   "d2h_bytes_per_step": nbytes, "steps": ke, "ms_per_step": 1e3 * tw_max / ke,
                    "api": "per rank: mpic_upload_planes + mpic_upload_particles, SlabStepper.step, mpic_download_*"}
     if rank == 0:
         value = float(npart_total) * K / (ms_max * 1e-3)
@@ -360,12 +388,14 @@ def bench_main(args, w, rank, world, local, peak, peak_how):
                "config": {"workload": args.workload, **w, "ny_global": ny, "particles": int(npart_total),
                           "decomposition": f"{world} slabs of {w['ny']} cell rows, periodic ring, transport={transport}" + (" (CUDA-IPC peer memory: halos fused into the sweeps, remote atomics for J, flags for ordering)" if transport == "peer" else " (NCCL send/recv)"),
                           "l2": "per-rank particle state >> 126 MB L2 (no flush needed)"},
-               "gpu_launches": int(launches), "clocks": clk.summary(), "migrated_records_rank0": int(stepper.moved),
+               "gpu_launches": int(launches), "clocks": clocks, "migrated_records_rank0": int(stepper.moved),
                "roofline": {"bound": "hbm", "kernel": "whole step", "achieved": value * 112.0 / 1e9 / world, "peak": peak,
                             "unit": "GB/s", "frac": value * 112.0 / 1e9 / world / peak, "traffic": None,
                             "bytes_per_particle": 112.0, "peak_source": peak_how, "note": "per GPU: fused push+reorder 104 B + permutation sort 8 B per particle"}}
         if e2e:
             out["e2e"] = e2e
+        if rebal is not None:
+            out["rebalance"] = rebal
         print(json.dumps(out))
     sim.close()
     dist.destroy_process_group()

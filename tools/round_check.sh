@@ -6,5 +6,5 @@ timeout 300 python __graft_entry__.py smoke 2>&1 | tail -3
 timeout 600 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; tail -c 3000 gpurun_out/bench.json
 timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.json 2>&1; cat gpurun_out/bench_ref.json
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv python bench.py --steps 3 --warmup 3 --no-yee --no-cpu --no-e2e > gpurun_out/ncu_l.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:"push_deposit|scatter_kernel" -s 8 -c 2 -o gpurun_out/push_full -f python bench.py --steps 3 --warmup 3 --no-yee --no-cpu --no-e2e > gpurun_out/ncu_f.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:"push_deposit|scatter_kernel" -s 3 -c 2 -o gpurun_out/push_full -f python bench.py --steps 3 --warmup 3 --no-yee --no-cpu --no-e2e > gpurun_out/ncu_f.log 2>&1
 ls -la gpurun_out
