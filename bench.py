@@ -45,7 +45,7 @@ WORKLOADS = {
 # PLUS 116 B for a separate reorder; the fused kernel replaces both.  `frac_88B` reports the stricter push-only figure.)
 PUSH_BYTES_PER_PARTICLE = 104.0
 PUSH_ONLY_BYTES = 88.0
-NCU_TRAFFIC_BYTES_PER_PARTICLE = 117.0   # measured: (1.041 GB read + 0.923 GB written) / 16.8 M particles
+NCU_TRAFFIC_BYTES_PER_PARTICLE = 113.7   # measured: (0.968 GB read + 0.940 GB written) / 16.8 M particles, profiles/r01d_ncu_full_push_two_stream.csv
 SORT_BYTES_PER_PARTICLE = 8.0      # what is left of the sort: keys read (4) + permutation written (4); scan is per cell
 YEE_BYTES_3SWEEP = 216.0           # reference-faithful half-B, E, half-B: 3 x 72 B per cell
 YEE_BYTES_ALGO = 144.0             # SURVEY.md section 8(d) algorithmic figure (2 sweeps)
@@ -273,7 +273,7 @@ def main():
         "roofline": {"bound": "hbm", "kernel": "push_deposit_kernel", "achieved": push_gbs, "peak": peak, "unit": "GB/s",
                      "frac": push_gbs / peak, "traffic": NCU_TRAFFIC_BYTES_PER_PARTICLE * n, "bytes_per_particle": PUSH_BYTES_PER_PARTICLE,
                      "frac_88B": push_gbs / peak * PUSH_ONLY_BYTES / PUSH_BYTES_PER_PARTICLE,
-                     "traffic_source": "ncu --set full dram__bytes_read+write of one launch, profiles/r01c_ncu_push_thermal.csv (117 B/particle)",
+                     "traffic_source": "ncu --set full dram__bytes_read+write of one launch, profiles/r01d_ncu_full_push_two_stream.csv (113.7 B/particle)",
                      "pushes_per_s_kernel_only": n / (push_ms * 1e-3), "peak_source": peak_how,
                      "sort_gbs": n * SORT_BYTES_PER_PARTICLE / (sort_ms * 1e-3) / 1e9,
                      "note": "fused gather+push+deposit+reorder: 52 B read + 52 B written per particle; the sort that remains (scan + permutation build) moves 8 B/particle"},

@@ -186,8 +186,11 @@ class Sim:
         ptrs = (c_dp * 6)(*[_dp(a) for a in arr])
         _chk(lib().mpic_upload_planes(self.h, ptrs))
 
-    def download_planes(self):
-        out = [np.empty((self.nyl, self.nx)) for _ in range(6)]
+    def download_planes(self, out=None):
+        """out: optional six preallocated (nyl, nx) float64 arrays (e.g. views of pinned host memory) filled in place."""
+        if out is None:
+            out = [np.empty((self.nyl, self.nx)) for _ in range(6)]
+        assert all(a.shape == (self.nyl, self.nx) and a.dtype == np.float64 and a.flags.c_contiguous for a in out)
         ptrs = (c_dp * 6)(*[_dp(a) for a in out])
         _chk(lib().mpic_download_planes(self.h, ptrs))
         return out
@@ -281,10 +284,16 @@ class Sim:
         _chk(lib().mpic_upload_particles(self.h, n, *[_dp(a) for a in arr], _ip(tag)))
         self.sync()
 
-    def download_particles(self):
+    def download_particles(self, out=None):
+        """out: optional dict of preallocated arrays with capacity >= num_particles (e.g. pinned host memory); the returned
+        dict holds views of their first num_particles entries."""
         n = self.num_particles
-        out = {k: np.empty(n) for k in PART_KEYS}
-        out["tag"] = np.empty(n, dtype=np.int32)
+        if out is None:
+            out = {k: np.empty(n) for k in PART_KEYS}
+            out["tag"] = np.empty(n, dtype=np.int32)
+        else:
+            assert all(out[k].shape[0] >= n and out[k].flags.c_contiguous for k in out)
+            out = {k: v[:n] for k, v in out.items()}
         nout = C.c_int64()
         _chk(lib().mpic_download_particles(self.h, n, *[_dp(out[k]) for k in PART_KEYS], _ip(out["tag"]), C.byref(nout)))
         assert nout.value == n

@@ -267,6 +267,12 @@ int mpic_destroy(mpic_sim* s) {
     cudaFree(s->halo_send); cudaFree(s->halo_recv); cudaFree(s->lv.count);
     for (int d = 0; d < 2; d++) cudaFree(s->lv.rec[d]);
     cudaFree(s->arrive_blk);
+    if (s->pipe_up) {
+        cudaStreamDestroy(s->pipe_up); cudaStreamDestroy(s->pipe_down);
+        for (int c = 0; c < MPIC_PIPE_MAX; c++) { cudaEventDestroy(s->pipe_ev_up[c]); cudaEventDestroy(s->pipe_ev_done[c]); }
+        cudaEventDestroy(s->pipe_ev_free);
+        cudaFree(s->pipe_count); cudaFree(s->pipe_start);
+    }
     if (s->st) cudaStreamDestroy(s->st);
     delete s;
     return 0;
@@ -568,7 +574,7 @@ int mpic_push_deposit(mpic_sim* s) {
     if (s->prm.nranks > 1) CUDA_TRY(cudaMemsetAsync(s->lv.count, 0, 2 * sizeof(int), s->st));
     s->left = s->prm.nranks > 1 ? -1 : 0;
     TRY(launch_push_deposit(s->P, s->G, &s->tmap, s->jacc, s->pa[s->cur], s->pa[s->cur ^ 1], s->perm,
-                            s->cell_start, s->cell_count, s->keys, s->push_split, s->lv, s->st));
+                            s->cell_start, s->cell_count, s->keys, s->push_split, s->lv, s->st, s->n));
     s->launches++;
     s->cur ^= 1;                    // the push wrote the other buffer in slot order
     s->perm_valid = false;
@@ -600,10 +606,101 @@ int mpic_pic_steps(mpic_sim* s, int nsteps) {
     }
     return 0;
 }
+static Particles offset_particles(const Particles& p, int64_t o) {
+    Particles r = { p.x + o, p.y + o, p.ux + o, p.uy + o, p.uz + o, p.q + o, p.tag + o };
+    return r;
+}
+static int pipe_setup(mpic_sim* s) {
+    if (s->pipe_up) return 0;
+    CUDA_TRY(cudaStreamCreateWithFlags(&s->pipe_up, cudaStreamNonBlocking));
+    CUDA_TRY(cudaStreamCreateWithFlags(&s->pipe_down, cudaStreamNonBlocking));
+    for (int c = 0; c < MPIC_PIPE_MAX; c++) {
+        CUDA_TRY(cudaEventCreateWithFlags(&s->pipe_ev_up[c], cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&s->pipe_ev_done[c], cudaEventDisableTiming));
+    }
+    CUDA_TRY(cudaEventCreateWithFlags(&s->pipe_ev_free, cudaEventDisableTiming));
+    CUDA_TRY(cudaMalloc(&s->pipe_count, (size_t)s->n_entries * 4));
+    CUDA_TRY(cudaMalloc(&s->pipe_start, (size_t)(s->n_entries + 1) * 4));
+    return 0;
+}
+
+// One PIC step on HOST buffers with the PCIe transfers overlapped with the compute (single slab, one step): the particles
+// cross the bus in chunks; while chunk c+1 is still uploading, chunk c is sorted (count / scan / scatter inside its own
+// index range), pushed (the tile CTAs of tiles without particles in this chunk exit at once) and its results are already
+// on their way back on a second copy stream -- the two directions of the link run concurrently.  The current of all chunks
+// accumulates in the same int64 planes (integer adds: any order, same bits), the Yee sweeps follow the last chunk, and the
+// tile sort of the resident state is the usual scan + permutation build over the keys every push wrote.  Same results as
+// upload -> mpic_pic_steps(1) -> download; the particles come back in a different ORDER (chunk by chunk, tile-sorted
+// inside each chunk), which the API never promised.
+static int pic_step_host_pipelined(mpic_sim* s, double* const planes[6], int64_t n, double* x, double* y, double* ux,
+                                   double* uy, double* uz, double* q, int* tag, int64_t* n_out) {
+    TRY(pipe_setup(s));
+    const FieldGeom& G = s->G;
+    int nchunk = (int)((n + (2 << 20) - 1) / (2 << 20));           // ~2 M particles (104 MB) per chunk
+    if (nchunk < 2) nchunk = 2;
+    if (nchunk > MPIC_PIPE_MAX) nchunk = MPIC_PIPE_MAX;
+    s->perm_valid = false; s->counts_valid = false; s->arrived = 0;
+    Particles& A = s->pa[s->cur];
+    Particles& B = s->pa[s->cur ^ 1];
+    // everything enqueued earlier on the main stream (it may still read A/B) precedes the first upload
+    CUDA_TRY(cudaEventRecord(s->pipe_ev_free, s->st));
+    CUDA_TRY(cudaStreamWaitEvent(s->pipe_up, s->pipe_ev_free, 0));
+    CUDA_TRY(cudaStreamWaitEvent(s->pipe_down, s->pipe_ev_free, 0));
+    for (int p = 0; p < 6; p++)
+        CUDA_TRY(cudaMemcpy2DAsync(s->planes + p * G.plane + (int64_t)G.g * G.pitch + MPIC_X0, (size_t)G.pitch * 8, planes[p],
+                                   (size_t)G.nx * 8, (size_t)G.nx * 8, G.nyl, cudaMemcpyHostToDevice, s->st));
+    TRY(refresh_all_guards(s));
+    CUDA_TRY(cudaMemsetAsync(s->cell_count, 0, (size_t)s->n_entries * 4, s->st));
+    const double* src[6] = { x, y, ux, uy, uz, q };
+    double* hdst[6] = { x, y, ux, uy, uz, q };
+    for (int c = 0; c < nchunk; c++) {
+        const int64_t lo = n * c / nchunk, hi = n * (c + 1) / nchunk, m = hi - lo;
+        if (m <= 0) continue;
+        double* dA[6] = { A.x, A.y, A.ux, A.uy, A.uz, A.q };
+        for (int k = 0; k < 6; k++) CUDA_TRY(cudaMemcpyAsync(dA[k] + lo, src[k] + lo, (size_t)m * 8, cudaMemcpyHostToDevice, s->pipe_up));
+        CUDA_TRY(cudaMemcpyAsync(A.tag + lo, tag + lo, (size_t)m * 4, cudaMemcpyHostToDevice, s->pipe_up));
+        CUDA_TRY(cudaEventRecord(s->pipe_ev_up[c], s->pipe_up));
+        // sort the chunk inside [lo, hi): A -> B, then push B -> A
+        CUDA_TRY(cudaStreamWaitEvent(s->st, s->pipe_ev_up[c], 0));
+        CUDA_TRY(cudaMemsetAsync(s->pipe_count, 0, (size_t)s->n_entries * 4, s->st));
+        const Particles Ac = offset_particles(A, lo), Bc = offset_particles(B, lo);
+        TRY(launch_count_keys(s->P, Ac, 0, m, s->pipe_count, nullptr, s->st));
+        TRY(launch_scan_cells(s->pipe_count, s->pipe_start, s->n_entries, s->scan_tmp, s->st));
+        TRY(launch_scatter(s->P, Ac, Bc, m, s->perm + lo, s->pipe_count, s->st));
+        TRY(launch_push_deposit(s->P, s->G, &s->tmap, s->jacc, Bc, Ac, s->perm + lo, s->pipe_start, s->cell_count, s->keys + lo,
+                                s->push_split, s->lv, s->st, 0));      // chunk occupancy unknown: adaptive lane groups
+        s->launches += 6;
+        CUDA_TRY(cudaEventRecord(s->pipe_ev_done[c], s->st));
+        // results of the chunk go home while the next one is still arriving
+        CUDA_TRY(cudaStreamWaitEvent(s->pipe_down, s->pipe_ev_done[c], 0));
+        for (int k = 0; k < 6; k++) CUDA_TRY(cudaMemcpyAsync(hdst[k] + lo, dA[k] + lo, (size_t)m * 8, cudaMemcpyDeviceToHost, s->pipe_down));
+        CUDA_TRY(cudaMemcpyAsync(tag + lo, A.tag + lo, (size_t)m * 4, cudaMemcpyDeviceToHost, s->pipe_down));
+    }
+    s->n = n;
+    s->left = 0;
+    s->counts_valid = true;            // cell_count = destination histogram of all chunks, keys[] = destination keys
+    TRY(mpic_step_b_half(s));
+    TRY(e_sweep(s, 1));
+    TRY(mpic_step_b_half(s));
+    for (int p = 0; p < 6; p++)
+        CUDA_TRY(cudaMemcpy2DAsync(planes[p], (size_t)G.nx * 8, s->planes + p * G.plane + (int64_t)G.g * G.pitch + MPIC_X0,
+                                   (size_t)G.pitch * 8, (size_t)G.nx * 8, G.nyl, cudaMemcpyDeviceToHost, s->st));
+    TRY(sort_all(s, true));            // resident state stays usable: A read through perm
+    CUDA_TRY(cudaStreamSynchronize(s->pipe_down));
+    CUDA_TRY(cudaStreamSynchronize(s->st));
+    if (n_out) *n_out = n;
+    return 0;
+}
+
 int mpic_pic_steps_host(mpic_sim* s, int nsteps, double* const planes[6], int64_t n, double* x, double* y, double* ux,
                         double* uy, double* uz, double* q, int* tag, int64_t* n_out) {
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && planes, MPIC_EINVAL, "bad argument");
+    REQUIRE(n >= 0 && n <= s->cap, MPIC_ENOMEM, "particle capacity %lld exceeded (%lld)", (long long)s->cap, (long long)n);
+    int64_t pipe_min = 1 << 20;        // below this the transfers are too short to be worth chunking
+    if (const char* e = getenv("MPIC_PIPELINE_MIN")) pipe_min = atoll(e);
+    if (nsteps == 1 && s->prm.nranks == 1 && n >= pipe_min && n >= 2 && !getenv("MPIC_NO_PIPELINE"))
+        return pic_step_host_pipelined(s, planes, n, x, y, ux, uy, uz, q, tag, n_out);
     const FieldGeom& G = s->G;
     for (int p = 0; p < 6; p++)
         CUDA_TRY(cudaMemcpy2DAsync(s->planes + p * G.plane + (int64_t)G.g * G.pitch + MPIC_X0, (size_t)G.pitch * 8, planes[p],

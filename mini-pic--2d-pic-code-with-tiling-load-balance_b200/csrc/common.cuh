@@ -129,7 +129,7 @@ int launch_gauss_residual(const FieldGeom& G, const double* planes, const int64_
 // ---- kernel launchers implemented in particles.cu
 int launch_push_deposit(const PicConst& P, const FieldGeom& G, const CUtensorMap* tmap, int64_t* jacc, Particles src,
                         Particles dst, const int* perm, const int* cell_start, int* cell_count_new, int* keys, int split,
-                        LeaveBufs lv, cudaStream_t st);
+                        LeaveBufs lv, cudaStream_t st, int64_t n_hint);   // n_hint: particles in the slab (picks the sparse-cell variant)
 int launch_perm_build(const PicConst& P, const int* keys, int64_t n, int* cursor, int* perm, cudaStream_t st);
 int launch_gather(Particles src, Particles dst, int* perm, int64_t n, cudaStream_t st);
 int launch_absorb(const PicConst& P, Particles p, int64_t first, const double* rec, int n, int* cell_count, int* keys,

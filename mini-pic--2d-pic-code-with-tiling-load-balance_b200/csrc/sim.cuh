@@ -3,6 +3,7 @@
 #include "common.cuh"
 #include <vector>
 
+#define MPIC_PIPE_MAX 32
 struct mpic_sim {
     mpic_params prm;
     FieldGeom G;
@@ -64,6 +65,11 @@ struct mpic_sim {
     int pending_ph = 3;
     bool b2_pending = false;               // B2 signalled, neighbours' B2 not awaited yet
     cudaEvent_t ev_counts = nullptr;
+    // ---- pipelined host-buffer step (api.cu: pic_step_host_pipelined)
+    cudaStream_t pipe_up = nullptr, pipe_down = nullptr;
+    cudaEvent_t pipe_ev_up[MPIC_PIPE_MAX] = {}, pipe_ev_done[MPIC_PIPE_MAX] = {}, pipe_ev_free = nullptr;
+    int* pipe_count = nullptr;     // per-chunk cell histogram / scatter cursor
+    int* pipe_start = nullptr;     // per-chunk cell offsets (relative to the chunk's first slot)
     std::vector<int> owner;        // global tiles
     void* ring_events = nullptr;   // ring.cu: per-handle events of the single-process peer-copy ring
 };

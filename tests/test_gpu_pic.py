@@ -156,6 +156,55 @@ def test_host_buffer_entry_point_matches_resident_path():
         assert np.array_equal(hf[k], wf[k])
 
 
+def test_pipelined_host_step_matches_oracle_and_resident_path(monkeypatch):
+    """mpic_pic_steps_host with one step overlaps the PCIe transfers with the compute chunk by chunk (api.cu:
+    pic_step_host_pipelined).  Same bits as the oracle on a small case (forced through the pipeline), and on a 2 M-particle
+    case in shuffled host order the same bits as upload -> pic_steps(1) -> download; the resident state it leaves behind
+    continues identically."""
+    monkeypatch.setenv("MPIC_PIPELINE_MIN", "2")
+    s, P, parts, pl = _setup(48, 32, 16, 16, 7, 0.4)
+    hp, hf = copy_parts(parts), [a.copy() for a in pl]
+    for _ in range(3):                                   # three calls: the resident leftovers of one call never leak into the next
+        s.pic_steps_host(1, hf, hp)
+    want, wf = copy_parts(parts), [a.copy() for a in pl]
+    counts, _ = ob.pic_steps(lib, P, wf, want, 3)
+    hp, want = by_tag(hp), by_tag(want)
+    for k in ("x", "y", "ux", "uy", "uz", "q"):
+        assert np.array_equal(hp[k], want[k]), k
+    for k in range(6):
+        assert np.array_equal(hf[k], wf[k])
+    assert np.array_equal(s.tile_counts(), counts)
+    s.close()
+    monkeypatch.delenv("MPIC_PIPELINE_MIN")
+    nx = ny = 256
+    dx = 0.1
+    dt = pkg().courant_dt(dx, dx)
+    parts = plasma().load_uniform(nx, ny, 16, 16, dx, dx, 32, u_th=0.2, seed=9)
+    rng = np.random.default_rng(4)
+    order = rng.permutation(parts["x"].shape[0])
+    parts = {k: np.ascontiguousarray(v[order]) for k, v in parts.items()}
+    pl = [0.02 * rng.standard_normal((ny, nx)) for _ in range(6)]
+    n = parts["x"].shape[0]
+    a = pkg().Sim(nx, ny, 16, 16, dx, dx, dt, max_particles=n + 64)
+    b = pkg().Sim(nx, ny, 16, 16, dx, dx, dt, max_particles=n + 64)
+    hp, hf = copy_parts(parts), [x.copy() for x in pl]
+    a.pic_steps_host(1, hf, hp)
+    b.upload_planes(pl)
+    b.upload_particles(parts)
+    b.pic_steps(1)
+    got, want = by_tag(hp), by_tag(b.download_particles())
+    for k in ("x", "y", "ux", "uy", "uz", "q"):
+        assert np.array_equal(got[k], want[k]), k
+    for u, v in zip(hf, b.download_planes()):
+        assert np.array_equal(u, v)
+    a.pic_steps(2)
+    b.pic_steps(2)
+    got, want = by_tag(a.download_particles()), by_tag(b.download_particles())
+    for k in ("x", "y", "ux", "uy", "uz"):
+        assert np.array_equal(got[k], want[k]), k
+    assert np.array_equal(a.tile_counts(), b.tile_counts())
+
+
 @pytest.mark.gpu
 def test_branch_free_division_and_sqrt_are_ieee():
     """The push kernel's transcribed fast-path sequences (1/sqrt(x), 2/x for x >= 1) must be bit-identical to the
