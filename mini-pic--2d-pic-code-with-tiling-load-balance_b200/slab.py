@@ -131,10 +131,18 @@ class PeerStepper:
         self.sim.peer_step_end()
 
 
-def tile_row_costs(counts, gtc, cells_per_tile, w_particle=1.0, w_cell=0.25):
+# Cost of one grid cell in particle-equivalents, fitted on B200 from two N=1 bench lines of the 4096 x 512 slab (2.1 M cells):
+# 134.2 M particles -> 4.45 ms, 33.8 M particles -> 1.57 ms  =>  0.0287 ms per M particles, 0.286 ms per M cells  =>  ~10.
+# (the per-cell work of the push -- reduction + 8 atomics per occupied cell, patch staging, J flush -- and the Yee sweeps do
+# not shrink with the occupancy); 8 is used: the sparse sample also carries the beam's cell crossers.
+W_CELL = float(os.environ.get("MPIC_REBALANCE_W_CELL", "8.0"))
+
+
+def tile_row_costs(counts, gtc, cells_per_tile, w_particle=1.0, w_cell=None):
     """Cost model of the rebalancer: cost of a tile row = particles + w_cell * cells (the Yee sweeps and
     the per-tile patch staging do not vanish in empty tiles)."""
     counts = np.asarray(counts, dtype=np.float64).reshape(-1, gtc)
+    w_cell = W_CELL if w_cell is None else w_cell
     return w_particle * counts.sum(axis=1) + w_cell * gtc * cells_per_tile
 
 
@@ -176,7 +184,7 @@ def balanced_slab_rows(row_costs, nranks):
     return parts
 
 
-def rebalance(sim, rank, world, make_sim, dist=None, group=None, w_cell=0.25, min_gain=0.05):
+def rebalance(sim, rank, world, make_sim, dist=None, group=None, w_cell=None, min_gain=0.05):
     """Cost-driven re-partition of the tile rows over the ranks -- the load balancer the reference names as its purpose
     but ships only as a hard-coded demo (PIC_2D.cpp:399-412 moves three tiles at step 5; removeTileFromRank /
     addTileToRank, Auxiliar_functions.cpp:242-272, send the grid and DROP the particles).
@@ -200,6 +208,7 @@ def rebalance(sim, rank, world, make_sim, dist=None, group=None, w_cell=0.25, mi
     rowp = np.zeros(gtr)
     for r0, nr, c in allr:
         rowp[r0:r0 + nr] = c
+    w_cell = W_CELL if w_cell is None else w_cell
     costs = tile_row_costs(rowp, 1, 1, w_cell=0.0) + w_cell * gtc * sim.tnx * tny
     new = balanced_slab_rows(costs, world)
     worst = lambda parts: max(costs[r0:r0 + nr].sum() for r0, nr in parts)
@@ -341,7 +350,7 @@ def bench_main(args, w, rank, world, local, peak, peak_how):
         rebal = {"changed": bool(changed), "even_split": {"ms_per_step": ms0 / K, "particles_per_rank": [g[1] for g in per0],
                                                           "tile_rows_per_rank": [g[2] for g in per0],
                                                           "pushes_per_s": float(np0) * K / (ms0 * 1e-3)},
-                 "policy": "slab.balanced_slab_rows on cost = particles + 0.25 * cells per tile row"}
+                 "policy": f"slab.balanced_slab_rows on cost = particles + {W_CELL:g} * cells per tile row"}
     ms_max, npart_total, launches, per, clocks = timed(stepper, sim, st, clocks=True)
     if rebal is not None:
         rebal["rebalanced"] = {"ms_per_step": ms_max / K, "particles_per_rank": [g[1] for g in per],

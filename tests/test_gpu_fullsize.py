@@ -194,6 +194,6 @@ def test_c5_beam_plasma_occupancy_and_policy():
     rowc = slab.tile_row_costs(counts, nx // tn, tn * tn)
     even = [rowc[r * 32:(r + 1) * 32].sum() for r in range(8)]
     bal = [rowc[r0:r0 + nr].sum() for r0, nr in slab.balanced_slab_rows(rowc, 8)]
-    assert max(even) / np.mean(even) > 2.0
+    assert max(even) / np.mean(even) > 1.7
     assert max(bal) / np.mean(bal) < 1.25
     s.close()

@@ -263,7 +263,7 @@ def _rebalance_gpu_worker(rank, world, port, steps, outdir):
             st.step()
         sim.sync()
         before = sim.num_particles
-        new, rows, changed = slab.rebalance(sim, rank, world, make, dist)
+        new, rows, changed = slab.rebalance(sim, rank, world, make, dist, w_cell=0.25)
         dist.barrier()                     # nobody touches the old handles any more
         if changed:
             sim.close()

@@ -116,7 +116,7 @@ def _rebalance_worker(rank, world, port, steps, outdir):
         for _ in range(steps):
             st.step()
         before = int(sim.parts["x"].shape[0])
-        sim, rows, changed = slab.rebalance(sim, rank, world, make, dist)
+        sim, rows, changed = slab.rebalance(sim, rank, world, make, dist, w_cell=0.25)
         st = slab.SlabStepper(sim, slab.Ring(rank, world))
         st.refresh_guards()
         for _ in range(steps):
