@@ -36,6 +36,8 @@ WORKLOADS = {
     "uniform_2048": dict(nx=2048, ny=2048, tn=16, ppc=64, u_th=0.05, two_stream=0.0, dx=0.1),
     # configs[3] (4096^2, 64 ppc, 1.07 B particles) per-GPU slab at 8 GPUs: 4096 x 512 cells, 134 M particles per rank
     "uniform_c4_slab": dict(nx=4096, ny=512, tn=16, ppc=64, u_th=0.05, two_stream=0.0, dx=0.1),
+    # configs[3] whole: 4096^2 x 64 ppc = 1.07 B particles, STRONG scaling (the domain is fixed, every rank owns 4096/N rows)
+    "uniform_c4": dict(nx=4096, ny=4096, tn=16, ppc=64, u_th=0.05, two_stream=0.0, dx=0.1, strong=True),
     # configs[4] per-GPU slab: thermal background 8 ppc + drifting beam 80 ppc in the band y in [0.45,0.55) of the GLOBAL box
     "beam_c5_slab": dict(nx=4096, ny=512, tn=16, ppc=8, u_th=0.05, two_stream=0.0, dx=0.1, beam_ppc=80, beam_band=(0.45, 0.55), beam_drift=0.5, beam_u_th=0.01),
 }
@@ -154,6 +156,32 @@ def run_reference(args):
         "gpu_launches": 0}))
 
 
+def yee_cpu_reference(n=1800, tile=25, steps=10):
+    """The reference's OWN field path on the host: unmodified Field_update.cpp + Auxiliar_functions.cpp pack/unpack driven
+    by the reference loop structure (phases A-F with its Grid<->split copies; oracle/ref_wrap.cpp only calls reference
+    functions), single rank through the mpi.h shim, on a bounded n x n sample.  -O2 build and the documented -O0 build."""
+    from oracle import bindings as ob
+    out = {}
+    dx = 10.0 / n
+    dt = 0.5 * dx / np.sqrt(2.0)
+    x = (np.arange(n) + 0.5) * dx
+    prof = 0.1 * np.sin(np.pi * x) * np.cos((x - 3.5) / 3.0 * np.pi / 2) ** 2 * (np.abs(x - 3.5) < 3.0)
+    g6 = np.zeros((n, n, 6))
+    g6[:, :, 1] = prof
+    g6[:, :, 5] = prof
+    for name, k in (("libref.so", steps), ("libref_O0.so", max(1, steps // 5))):
+        if not ob.have_ref(name):
+            continue
+        ref = ob.load_ref(name)
+        r = ob.ref_run_loop(ref, g6, 1, 1, n // tile, n // tile, 2, dt, dx, dx, k, want_tiles=False)
+        out[name] = float(n) * n * k / r["seconds"]
+    if not out:
+        return None
+    return {"value": out.get("libref.so"), "unit": "cells/s", "cores": 1, "kind": "reference",
+            "sample": f"{n}x{n} cells in {tile}x{tile} tiles (the reference's tile size), {steps} steps, 1 MPI rank (shim), g++ -O2",
+            "value_O0_documented_build": out.get("libref_O0.so")}
+
+
 def yee_bench(m, torch, steps, warmup, n=8192):
     """Field-only sub-benchmark (BASELINE.json configs[2]): n x n vacuum pulse, reference-faithful 3-sweep loop."""
     dx = dy = 10.0 / n
@@ -265,7 +293,7 @@ def main():
 
     out = {
         "metric": "particle-pushes/s (push+deposit+sort)", "value": value, "unit": "particles/s", "n_gpus": 1, "steps": K,
-        "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong" if w.get("strong") else "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
         "config": {"workload": args.workload, **w, "particles": n, "tile": f"{tn}x{tn}", "dt": dt,
                    "l2": f"particle state {n * 52 / 1e9:.2f} GB per pass >> 126 MB L2 (no flush needed)"},
@@ -281,6 +309,9 @@ def main():
         "diagnostics_after": {k: float(v) for k, v in diag.items()},
     }
 
+    if n * 52 > 16e9 and not args.no_e2e:
+        args.no_e2e = True                 # the host image of a billion-particle state does not belong in a default bench run
+        out["e2e_skipped"] = "host image > 16 GB"
     if not args.no_e2e:
         # end to end through the host-buffer C-ABI call: pinned host state in, 1 PIC step, full state out, every step
         host = {k: torch.empty(n, dtype=torch.float64).pin_memory() for k in m.PART_KEYS}
@@ -309,6 +340,13 @@ def main():
     if not args.no_yee:
         out["yee"] = yee_bench(m, torch, max(K, 10), W)
     if not args.no_cpu:
+        if "yee" in out:
+            try:
+                cb = yee_cpu_reference()
+            except Exception as e:      # oracle/_ref is built where /root/reference exists and travels with the snapshot
+                cb = {"unavailable": repr(e)}
+            if cb:
+                out["yee"]["cpu_baseline"] = cb
         v, cores, sample = cpu_port_pushes_per_s(w, steps=2)
         out["cpu_baseline"] = {"value": v, "unit": "particles/s", "cores": cores, "kind": "port", "sample": sample,
                                "note": "reference has no particle code (SURVEY.md F1); this is the repo's scalar FP64 oracle with OpenMP"}

@@ -292,7 +292,8 @@ def bench_main(args, w, rank, world, local, peak, peak_how):
     m = importlib.import_module(__package__)
     bench = importlib.import_module("bench")
     dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
-    nx, ny, tn, ppc = w["nx"], w["ny"] * world, w["tn"], w["ppc"]
+    strong = bool(w.get("strong"))                      # strong scaling: the global domain is the workload's, split N ways
+    nx, ny, tn, ppc = w["nx"], (w["ny"] if strong else w["ny"] * world), w["tn"], w["ppc"]
     dx = dy = w["dx"]
     dt = m.courant_dt(dx, dy)
     gtr = ny // tn
@@ -394,10 +395,10 @@ def bench_main(args, w, rank, world, local, peak, peak_how):
     if rank == 0:
         value = float(npart_total) * K / (ms_max * 1e-3)
         out = {"metric": "particle-pushes/s (push+deposit+sort)", "value": value, "unit": "particles/s", "n_gpus": world,
-               "steps": K, "warmup": W, "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "weak",
+               "steps": K, "warmup": W, "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "strong" if strong else "weak",
                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                "config": {"workload": args.workload, **w, "ny_global": ny, "particles": int(npart_total),
-                          "decomposition": f"{world} slabs of {w['ny']} cell rows, periodic ring, transport={transport}" + (" (CUDA-IPC peer memory: halos fused into the sweeps, remote atomics for J, flags for ordering)" if transport == "peer" else " (NCCL send/recv)"),
+                          "decomposition": f"{world} slabs of {ny // world} cell rows, periodic ring, transport={transport}" + (" (CUDA-IPC peer memory: halos fused into the sweeps, remote atomics for J, flags for ordering)" if transport == "peer" else " (NCCL send/recv)"),
                           "l2": "per-rank particle state >> 126 MB L2 (no flush needed)"},
                "gpu_launches": int(launches), "clocks": clocks, "migrated_records_rank0": int(stepper.moved),
                "roofline": {"bound": "hbm", "kernel": "whole step", "achieved": value * 112.0 / 1e9 / world, "peak": peak,
