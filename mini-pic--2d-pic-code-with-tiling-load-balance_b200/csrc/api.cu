@@ -218,7 +218,7 @@ int mpic_create(const mpic_params* p, mpic_sim** out) {
         // enough CTAs per tile that the grid covers >= 4 waves of 2 CTAs/SM even for few tiles
         int ntiles = P.ltr * P.gtc;
         s->push_split = 1;
-        while (ntiles * s->push_split < 16 * s->nsm && s->push_split < 64) s->push_split *= 2;
+        while (ntiles * s->push_split < 12 * s->nsm && s->push_split < 64) s->push_split *= 2;   // >= 4 waves of 3 CTAs/SM
         if (const char* e = getenv("MPIC_PUSH_SPLIT")) { int v = atoi(e); if (v >= 1 && v <= 256) s->push_split = v; }   // tuning knob
     }
     if (p->nranks > 1) {
@@ -636,7 +636,9 @@ static int pic_step_host_pipelined(mpic_sim* s, double* const planes[6], int64_t
                                    double* uy, double* uz, double* q, int* tag, int64_t* n_out) {
     TRY(pipe_setup(s));
     const FieldGeom& G = s->G;
-    int nchunk = (int)((n + (2 << 20) - 1) / (2 << 20));           // ~2 M particles (104 MB) per chunk
+    int64_t chunk = 1 << 20;                                       // ~1 M particles (52 MB) per chunk (B200: 21.0 ms; 2 M: 22.3; 4 M: 23.2)
+    if (const char* e = getenv("MPIC_PIPE_CHUNK")) { const long long v = atoll(e); if (v >= 1024) chunk = v; }   // tuning knob
+    int nchunk = (int)((n + chunk - 1) / chunk);
     if (nchunk < 2) nchunk = 2;
     if (nchunk > MPIC_PIPE_MAX) nchunk = MPIC_PIPE_MAX;
     s->perm_valid = false; s->counts_valid = false; s->arrived = 0;
