@@ -38,6 +38,8 @@ WORKLOADS = {
     "uniform_c4_slab": dict(nx=4096, ny=512, tn=16, ppc=64, u_th=0.05, two_stream=0.0, dx=0.1),
     # configs[3] whole: 4096^2 x 64 ppc = 1.07 B particles, STRONG scaling (the domain is fixed, every rank owns 4096/N rows)
     "uniform_c4": dict(nx=4096, ny=4096, tn=16, ppc=64, u_th=0.05, two_stream=0.0, dx=0.1, strong=True),
+    # configs[2]: vacuum pulse, no particles; STRONG scaling over N slabs (halo rows stored into the neighbours by the sweeps)
+    "yee_8192": dict(nx=8192, ny=8192, tn=32, ppc=0, u_th=0.0, two_stream=0.0, dx=10.0 / 8192, fields_only=True, strong=True),
     # configs[4] per-GPU slab: thermal background 8 ppc + drifting beam 80 ppc in the band y in [0.45,0.55) of the GLOBAL box
     "beam_c5_slab": dict(nx=4096, ny=512, tn=16, ppc=8, u_th=0.05, two_stream=0.0, dx=0.1, beam_ppc=80, beam_band=(0.45, 0.55), beam_drift=0.5, beam_u_th=0.01),
 }
@@ -47,7 +49,7 @@ WORKLOADS = {
 # PLUS 116 B for a separate reorder; the fused kernel replaces both.  `frac_88B` reports the stricter push-only figure.)
 PUSH_BYTES_PER_PARTICLE = 104.0
 PUSH_ONLY_BYTES = 88.0
-NCU_TRAFFIC_BYTES_PER_PARTICLE = 113.7   # measured: (0.968 GB read + 0.940 GB written) / 16.8 M particles, profiles/r01d_ncu_full_push_two_stream.csv
+NCU_TRAFFIC_BYTES_PER_PARTICLE = 113.5   # measured: (0.964 GB read + 0.940 GB written) / 16.8 M particles, profiles/r01e_ncu_full_push_two_stream.csv
 SORT_BYTES_PER_PARTICLE = 8.0      # what is left of the sort: keys read (4) + permutation written (4); scan is per cell
 YEE_BYTES_3SWEEP = 216.0           # reference-faithful half-B, E, half-B: 3 x 72 B per cell
 YEE_BYTES_ALGO = 144.0             # SURVEY.md section 8(d) algorithmic figure (2 sweeps)
@@ -206,7 +208,9 @@ def yee_bench(m, torch, steps, warmup, n=8192):
            "config": {"workload": f"vacuum pulse {n}x{n}, half-B/E/half-B per step", "fields_bytes": 48 * n * n},
            "gpu_launches": sim.kernel_launches - l0,
            "roofline": {"bound": "hbm", "achieved": cells * YEE_BYTES_3SWEEP / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
-                        "frac": cells * YEE_BYTES_3SWEEP / (ms * 1e-3) / 1e9 / peak, "traffic": None,
+                        "frac": cells * YEE_BYTES_3SWEEP / (ms * 1e-3) / 1e9 / peak,
+                        "traffic": (3.225 + 1.568 + 3.225 + 1.572 + 3.225 + 1.568) * 1e9 * (float(n) * n / 8192.0 ** 2),
+                        "traffic_source": "ncu --set full dram__bytes_read+write of b_sweep / e_sweep at 8192^2 (profiles/r01e_ncu_full_yee_8192.csv), three sweeps per step: 14.38 GB vs 14.50 GB algorithmic",
                         "bytes_per_cell_update": YEE_BYTES_3SWEEP,
                         "frac_of_144B_figure": cells * YEE_BYTES_ALGO / (ms * 1e-3) / 1e9 / peak, "peak_source": how}}
     sim.close()
@@ -241,7 +245,20 @@ def main():
 
     if world > 1:
         dist = importlib.import_module(PKG + ".slab")
+        if w.get("fields_only"):
+            return dist.bench_fields(args, w, rank, world, local, peak, peak_how)
         return dist.bench_main(args, w, rank, world, local, peak, peak_how)
+    if w.get("fields_only"):
+        with ClockSampler(local) as clk:
+            y = yee_bench(m, torch, K, W, n=w["nx"])
+        out = {"metric": y["metric"], "value": y["value"], "unit": y["unit"], "n_gpus": 1, "steps": K, "warmup": W,
+               "ms_per_step": y["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+               "data": "synthetic", "config": {"workload": args.workload, **y["config"], "l2": "48 B/cell x 67 M cells = 3.2 GB >> 126 MB L2"},
+               "roofline": y["roofline"], "gpu_launches": y["gpu_launches"], "clocks": clk.summary()}
+        if not args.no_cpu:
+            out["cpu_baseline"] = yee_cpu_reference()
+        print(json.dumps(out))
+        return
 
     nx, ny, tn, ppc = w["nx"], w["ny"], w["tn"], w["ppc"]
     dx = dy = w["dx"]
@@ -301,7 +318,7 @@ def main():
         "roofline": {"bound": "hbm", "kernel": "push_deposit_kernel", "achieved": push_gbs, "peak": peak, "unit": "GB/s",
                      "frac": push_gbs / peak, "traffic": NCU_TRAFFIC_BYTES_PER_PARTICLE * n, "bytes_per_particle": PUSH_BYTES_PER_PARTICLE,
                      "frac_88B": push_gbs / peak * PUSH_ONLY_BYTES / PUSH_BYTES_PER_PARTICLE,
-                     "traffic_source": "ncu --set full dram__bytes_read+write of one launch, profiles/r01d_ncu_full_push_two_stream.csv (113.7 B/particle)",
+                     "traffic_source": "ncu --set full dram__bytes_read+write of one launch, profiles/r01e_ncu_full_push_two_stream.csv (113.5 B/particle)",
                      "pushes_per_s_kernel_only": n / (push_ms * 1e-3), "peak_source": peak_how,
                      "sort_gbs": n * SORT_BYTES_PER_PARTICLE / (sort_ms * 1e-3) / 1e9,
                      "note": "fused gather+push+deposit+reorder: 52 B read + 52 B written per particle; the sort that remains (scan + permutation build) moves 8 B/particle"},

@@ -284,6 +284,65 @@ def rebalance(sim, rank, world, make_sim, dist=None, group=None, w_cell=None, mi
 
 
 # ------------------------------------------------------------------------------------------------ multi-GPU bench
+def bench_fields(args, w, rank, world, local, peak, peak_how):
+    """Field-only workload (BASELINE.json configs[2]) on N slabs: half-B / E / half-B per step over the peer ring (the
+    sweeps store their slab-edge rows straight into the neighbours' guard rows; flags order the phases) or, with
+    MPIC_TRANSPORT=nccl, pack -> send/recv -> unpack.  Strong scaling: the n x n domain is split into N slabs."""
+    import torch
+    import torch.distributed as dist
+    m = importlib.import_module(__package__)
+    bench = importlib.import_module("bench")
+    dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    nx, ny, tn = w["nx"], w["ny"], w["tn"]
+    dx = dy = w["dx"]
+    dt = m.courant_dt(dx, dy)
+    sim = m.Sim(nx, ny, tn, tn, dx, dy, dt, rank=rank, nranks=world, device=local)
+    x = (np.arange(nx) + 0.5) * dx
+    prof = 0.1 * np.sin(np.pi * x) * np.cos((x - 3.5) / 3.0 * np.pi / 2) ** 2 * (np.abs(x - 3.5) < 3.0)
+    z = np.zeros((sim.nyl, nx))
+    row = np.tile(prof, (sim.nyl, 1))
+    sim.upload_planes([z, row, z, z, z, row])
+    st = sim.torch_stream()
+    K, W = args.steps, max(args.warmup, 3)
+    transport = os.environ.get("MPIC_TRANSPORT", "peer")
+    stepper = PeerStepper(sim, rank, world) if transport == "peer" else SlabStepper(sim, Ring(rank, world))
+    with torch.cuda.stream(st):
+        stepper.refresh_guards()
+        for _ in range(W):
+            stepper.field_step()
+        sim.sync()
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = sim.kernel_launches
+        clk = bench.ClockSampler(local) if rank == 0 else contextlib.nullcontext()
+        with clk:
+            e0.record(st)
+            for _ in range(K):
+                stepper.field_step()
+            e1.record(st)
+            sim.sync()
+            torch.cuda.synchronize()
+        dist.barrier()
+        gathered = [None] * world
+        dist.all_gather_object(gathered, (float(e0.elapsed_time(e1)), float(sim.diagnostics()["field_energy"])))
+    if rank == 0:
+        ms = max(g[0] for g in gathered)
+        cells = float(nx) * ny * K
+        gbs = cells * bench.YEE_BYTES_3SWEEP / (ms * 1e-3) / 1e9 / world
+        print(json.dumps({
+            "metric": "Yee cell-updates/s", "value": cells / (ms * 1e-3), "unit": "cells/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": args.workload, "nx": nx, "ny": ny, "decomposition": f"{world} slabs of {ny // world} rows, transport={transport}",
+                       "l2": "48 B/cell x 67 M cells = 3.2 GB >> 126 MB L2 x N"},
+            "roofline": {"bound": "hbm", "kernel": "b_sweep/e_sweep/b_sweep", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
+                         "traffic": None, "bytes_per_cell_update": bench.YEE_BYTES_3SWEEP, "peak_source": peak_how, "note": "per GPU"},
+            "gpu_launches": int(sim.kernel_launches - l0), "clocks": clk.summary(),
+            "field_energy_total": sum(g[1] for g in gathered)}))
+    sim.close()
+    dist.destroy_process_group()
+
+
 def bench_main(args, w, rank, world, local, peak, peak_how):
     """bench.py for N > 1 (torchrun, one rank per GPU): weak scaling -- every rank owns an (ny x nx) slab of an
     (N*ny x nx) domain.  Timed on the device (CUDA events on the library stream), max over ranks."""
