@@ -141,6 +141,19 @@ def run_reference(args):
     if rank != 0:
         return
     w = WORKLOADS[args.workload]
+    if w.get("fields_only"):
+        # the reference's OWN field path (unmodified Field_update.cpp + pack/unpack under its loop structure), one rank
+        vals = [yee_cpu_reference(steps=10) for _ in range(max(1, min(args.steps, 3)))]
+        cb = sorted(vals, key=lambda c: c["value"])[len(vals) // 2]
+        v = cb["value"]
+        print(json.dumps({
+            "impl": "reference", "metric": "Yee cell-updates/s", "value": v, "unit": "cells/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * 1800.0 * 1800.0 / v, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": args.workload, "note": "bounded sample of the same pulse: " + cb["sample"]},
+            "cpu_baseline": cb, "e2e": {"value": v, "unit": "cells/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}))
+        return
     vals = []
     sample = cores = None
     for _ in range(max(1, min(args.steps, 3))):
