@@ -64,6 +64,49 @@ def test_ten_pic_steps_bit_exact(cfg):
     assert np.array_equal(gidx[np.argsort(raw["tag"], kind="stable")], wkey[order])
 
 
+@pytest.mark.parametrize("ppc", [12, 16, 20, 24])
+def test_lane_group_walks_bit_exact(ppc):
+    """The sparse-slab push variant splits its warps into lane groups of 32 / 16 / 8 per CTA (mean occupancy > 20 / > 10 /
+    else): 12-20 ppc runs the 16-lane walk, 24 ppc the 32-lane walk of the ADAPT... and of the dense kernel; same bits."""
+    s, P, parts, pl = _setup(48, 32, 16, 16, ppc, 0.5, fields=0.02)
+    s.upload_planes(pl)
+    s.upload_particles(parts)
+    s.pic_steps(6)
+    want, wf = copy_parts(parts), [a.copy() for a in pl]
+    counts, _ = ob.pic_steps(lib, P, wf, want, 6)
+    got, want = by_tag(s.download_particles()), by_tag(want)
+    for k in ("x", "y", "ux", "uy", "uz"):
+        assert np.array_equal(got[k], want[k]), k
+    for a, b in zip(s.download_planes(), wf):
+        assert np.array_equal(a, b)
+    assert np.array_equal(s.tile_counts(), counts)
+
+
+def test_mixed_density_tiles_bit_exact():
+    """Sparse background + dense drifting band in one launch: CTAs of the same kernel take different lane-group walks."""
+    nx, ny, tn, dx = 64, 64, 16, 0.1
+    dt = pkg().courant_dt(dx, dx)
+    bg = plasma().load_uniform(nx, ny, tn, tn, dx, dx, 4, u_th=0.3, seed=21)
+    beam = plasma().load_uniform(nx, ny, tn, tn, dx, dx, 48, u_th=0.05, seed=22, drift=(0.5, 0.0, 0.0), band=(0.25, 0.5))
+    beam["tag"] = (beam["tag"].astype(np.int64) + 10 ** 6).astype(np.int32)
+    parts = {k: np.concatenate([bg[k], beam[k]]) for k in bg}
+    rng = np.random.default_rng(5)
+    pl = [0.02 * rng.standard_normal((ny, nx)) for _ in range(6)]
+    P = ob.make_params(lib, nx, ny, tn, tn, dx, dx, dt)
+    s = pkg().Sim(nx, ny, tn, tn, dx, dx, dt, max_particles=parts["x"].shape[0] + 64)
+    s.upload_planes(pl)
+    s.upload_particles(parts)
+    s.pic_steps(8)
+    want, wf = copy_parts(parts), [a.copy() for a in pl]
+    counts, _ = ob.pic_steps(lib, P, wf, want, 8)
+    got, want = by_tag(s.download_particles()), by_tag(want)
+    for k in ("x", "y", "ux", "uy", "uz"):
+        assert np.array_equal(got[k], want[k]), k
+    for a, b in zip(s.download_planes(), wf):
+        assert np.array_equal(a, b)
+    assert np.array_equal(s.tile_counts(), counts)
+
+
 def test_device_loader_matches_host_loader():
     nx, ny, tnx, tny, dx, dy = 64, 32, 16, 16, 0.1, 0.1
     m = pkg()
