@@ -1,4 +1,3 @@
-for sp in 1 2 3 4 6 8; do
-  echo "== split=$sp"
-  MPIC_PUSH_SPLIT=$sp GAP_SHORT=1 timeout 200 python tools/push_gap.py 2>&1 | sed 's/"push_ms_first10.*total_ms/ total_ms/' | cut -c1-170
-done | tee gpurun_out/split_push.log
+for sp in 2 3 5 6 7 13; do MPIC_PUSH_SPLIT=$sp timeout 300 python bench.py --steps 20 --warmup 5 --no-yee --no-cpu --no-e2e 2>/dev/null | python -c "
+import json,sys
+d=json.loads(sys.stdin.read());print('split $sp', round(d['ms_per_step'],4), round(d['phases_ms']['push_deposit'],4))"; done
