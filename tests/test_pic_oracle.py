@@ -129,3 +129,33 @@ def test_cold_plasma_oscillation_at_omega_p():
     t_cross = [t[i] - amp[i] * dt / (amp[i + 1] - amp[i]) for i in zc[:2]]
     assert len(t_cross) == 2
     assert abs((t_cross[1] - t_cross[0]) - np.pi) < 0.03 * np.pi      # half period = pi/omega_p
+
+
+def test_two_stream_growth_rate_of_a_seeded_mode():
+    """Two cold counter-streaming electron beams (u0 = +-0.2, each half the density): the seeded mode m = 3 of a 6.4 c/omega_p
+    box grows at the rate of the cold-beam dispersion relation 1 = omega_b^2 [1/(w - kv)^2 + 1/(w + kv)^2] with
+    omega_b^2 = omega_p^2 / (2 gamma0^3):  gamma^2 = omega_b^2 (sqrt(4x + 1) - (x + 1)),  x = (k v0)^2 / omega_b^2  ->  0.343."""
+    nx, ny, tn, ppc, dx = 64, 8, 8, 64, 0.1
+    dt = 0.5 / np.sqrt(2) * dx
+    P = ob.make_params(lib, nx, ny, tn, tn, dx, dx, dt)
+    parts = plasma.load_uniform(nx, ny, tn, tn, dx, dx, ppc, u_th=0.0, two_stream=0.2)
+    m = 3
+    k = 2 * np.pi * m / P.box_x
+    parts["ux"] = parts["ux"] + 1e-5 * np.sin(k * parts["x"])
+    pl = _zero_planes(nx, ny)
+    mode = np.exp(-1j * k * (np.arange(nx) + 0.5) * dx)
+    A, T = [], []
+    for s in range(850):
+        ob.pic_steps(lib, P, pl, parts, 1)
+        A.append(abs((pl[0].mean(axis=0) * mode).sum()))
+        T.append((s + 1) * dt)
+    A, T = np.array(A), np.array(T)
+    sel = (T > 12.0) & (A < 0.1 * A.max()) & (T < T[np.argmax(A)])
+    assert sel.sum() > 100
+    rate = np.polyfit(T[sel], np.log(A[sel]), 1)[0]
+    g0 = np.sqrt(1.0 + 0.2 ** 2)
+    wb2 = 0.5 / g0 ** 3
+    x = (k * 0.2 / g0) ** 2 / wb2
+    theory = np.sqrt(wb2 * (np.sqrt(4 * x + 1) - (x + 1)))
+    assert abs(theory - 0.343) < 2e-3
+    assert abs(rate - theory) < 0.05 * theory, (rate, theory)
