@@ -192,9 +192,17 @@ def yee_cpu_reference(n=1800, tile=25, steps=10):
         out[name] = float(n) * n * k / r["seconds"]
     if not out:
         return None
-    return {"value": out.get("libref.so"), "unit": "cells/s", "cores": 1, "kind": "reference",
-            "sample": f"{n}x{n} cells in {tile}x{tile} tiles (the reference's tile size), {steps} steps, 1 MPI rank (shim), g++ -O2",
-            "value_O0_documented_build": out.get("libref_O0.so")}
+    res = {"value": out.get("libref.so"), "unit": "cells/s", "cores": 1, "kind": "reference",
+           "sample": f"{n}x{n} cells in {tile}x{tile} tiles (the reference's tile size), {steps} steps, 1 MPI rank (shim), g++ -O2",
+           "value_O0_documented_build": out.get("libref_O0.so")}
+    if ob.have_ref("libref_omp.so"):
+        # all host cores: the same reference functions, the loops over tiles run with OpenMP (oracle/ref_wrap.cpp).  NOT the
+        # reference's own parallelisation (MPI ranks, unavailable here: no mpirun in the image) -- labelled as such.
+        ref = ob.load_ref("libref_omp.so")
+        r = ob.ref_run_loop(ref, g6, 1, 1, n // tile, n // tile, 2, dt, dx, dx, steps, want_tiles=False)
+        res["omp_over_tiles"] = {"value": float(n) * n * steps / r["seconds"], "cores": int(ref.ref_num_threads()),
+                                 "note": "reference functions, OpenMP over tiles (not the reference's MPI decomposition)"}
+    return res
 
 
 def yee_bench(m, torch, steps, warmup, n=8192):

@@ -16,6 +16,9 @@
 #include <map>
 #include <vector>
 #include <chrono>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 #include "Auxiliar_functions.h"   // reference header (needs shim mpi.h on the include path)
 #include "Field_update.h"         // reference header
 
@@ -45,6 +48,11 @@ static_assert(sizeof(Grid) == 48 && sizeof(GridE) == 24 && sizeof(GridB) == 24, 
 extern "C" {
 
 int ref_sizeof_particle() { return (int)sizeof(Particle); }
+#ifdef _OPENMP
+int ref_num_threads() { return omp_get_max_threads(); }
+#else
+int ref_num_threads() { return 1; }
+#endif
 
 // ---- Field_update.h:36,54 on raw pointers (AoS triplets, tile incl. guards, row-major j*TX+i)
 void ref_update_b_half(const double* E3, const double* Bold3, double* Bnew3,
@@ -148,8 +156,15 @@ double ref_run_loop(double* global6, int nx, int ny, int R, int C, int tileRows,
     };
     rebuild();
 
+    // Flat list of every tile of every emulated rank.  The loops below are `omp parallel for` over it: ignored in libref.so
+    // (built without -fopenmp: the reference's own single-threaded rank), active in libref_omp.so -- an all-cores variant of
+    // the same loop, NOT the reference's parallelisation (that is MPI ranks), reported beside it as such.
+    auto all_tiles = [&]() { std::vector<Tile*> v; for (auto& info : ranks) for (auto& t : info.tiles) v.push_back(&t); return v; };
     auto b_phase = [&]() {                                       // PIC_2D.cpp:174-196 / 322-344
-        for (auto& info : ranks) for (auto& tile : info.tiles) {
+        std::vector<Tile*> tl = all_tiles();
+#pragma omp parallel for schedule(static)
+        for (long ti = 0; ti < (long)tl.size(); ti++) {
+            Tile& tile = *tl[ti];
             size_t n = tile.grid.size();
             std::vector<GridE> E(n); std::vector<GridB> Bo(n);
             for (size_t k = 0; k < n; k++) {
@@ -162,7 +177,10 @@ double ref_run_loop(double* global6, int nx, int ny, int R, int C, int tileRows,
         }
     };
     auto e_phase = [&]() {                                       // PIC_2D.cpp:251-272
-        for (auto& info : ranks) for (auto& tile : info.tiles) {
+        std::vector<Tile*> tl = all_tiles();
+#pragma omp parallel for schedule(static)
+        for (long ti = 0; ti < (long)tl.size(); ti++) {
+            Tile& tile = *tl[ti];
             size_t n = tile.grid.size();
             std::vector<GridE> E(n); std::vector<GridB> B(n);
             for (size_t k = 0; k < n; k++) {
@@ -175,7 +193,10 @@ double ref_run_loop(double* global6, int nx, int ny, int R, int C, int tileRows,
     };
     auto exchange = [&]() {                                      // PIC_2D.cpp:200-248: all sends packed first, then unpacked
         std::vector<std::vector<std::vector<Grid>>> rbuf(total, std::vector<std::vector<Grid>>(8));
-        for (auto& info : ranks) for (auto& tile : info.tiles) {
+        std::vector<Tile*> tl = all_tiles();
+#pragma omp parallel for schedule(static)
+        for (long ti = 0; ti < (long)tl.size(); ti++) {          // every (gid, d) writes its own mailbox slot
+            Tile& tile = *tl[ti];
             int gid = tile.info.globalID;
             for (int d = 0; d < 8; d++) {
                 int nbr = getNeighborGID(gid, d, gtr, gtc);
@@ -184,8 +205,9 @@ double ref_run_loop(double* global6, int nx, int ny, int R, int C, int tileRows,
                 rbuf[nbr][opposite[d]] = packSendBuffer(tile, d, guard);
             }
         }
-        for (auto& info : ranks) for (auto& tile : info.tiles)
-            for (int d = 0; d < 8; d++) updateGuardRegion(tile, d, guard, rbuf[tile.info.globalID][d]);
+#pragma omp parallel for schedule(static)
+        for (long ti = 0; ti < (long)tl.size(); ti++)
+            for (int d = 0; d < 8; d++) updateGuardRegion(*tl[ti], d, guard, rbuf[tl[ti]->info.globalID][d]);
     };
 
     auto t0 = std::chrono::steady_clock::now();
