@@ -156,3 +156,13 @@ def test_tile_functions_vs_reference_fixture(golden_dir):
     lib.orc_update_e_full_tile(ob._dp(En), ob._dp(B), tnx, tny, g, 0.013, 0.11, 0.07, 0)
     assert np.array_equal(En, f["Enew"])
     assert lib.orc_compute_tag(17, 5) == 17 * 8 + 5
+
+
+@pytest.mark.skipif(not (ob.have_ref() and ob.have_ref("libref_omp.so")), reason="oracle/_ref not built")
+def test_openmp_variant_of_the_reference_loop_is_bit_identical():
+    """libref_omp.so (the all-cores CPU baseline: same reference functions, loops over tiles under OpenMP) == libref.so."""
+    rng = np.random.default_rng(11)
+    g6 = rng.standard_normal((60, 90, 6))
+    a = ob.ref_run_loop(ob.load_ref("libref.so"), g6, 1, 1, 4, 6, 2, 0.004, 0.1, 0.07, 7)
+    b = ob.ref_run_loop(ob.load_ref("libref_omp.so"), g6, 1, 1, 4, 6, 2, 0.004, 0.1, 0.07, 7)
+    assert np.array_equal(a["global"], b["global"]) and np.array_equal(a["tiles"], b["tiles"])
