@@ -116,12 +116,13 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def cpu_port_pushes_per_s(w, steps=2, sample_cells=256):
-    """The oracle port (OpenMP over particles) on a bounded sample: a (sample_cells x sample_cells) piece of the workload."""
+def cpu_port_pushes_per_s(w, steps=2, sample_cells=256, omp=True):
+    """The oracle port (OpenMP over particles, or the scalar build with omp=False) on a bounded sample: a (sample_cells x
+    sample_cells) piece of the workload."""
     from oracle import bindings as ob
     plasma = importlib.import_module(PKG + ".plasma")
     m = importlib.import_module(PKG)
-    lib = ob.load_oracle(omp=True)
+    lib = ob.load_oracle(omp=omp)
     nx = ny = min(sample_cells, w["nx"])
     dx = dy = w["dx"]
     dt = m.courant_dt(dx, dy)
@@ -133,7 +134,7 @@ def cpu_port_pushes_per_s(w, steps=2, sample_cells=256):
     ob.pic_steps(lib, P, planes, parts, steps)
     dtw = time.perf_counter() - t0
     n = parts["x"].shape[0]
-    return n * steps / dtw, lib.orc_num_threads(), f"{nx}x{ny} cells x {w['ppc']} ppc = {n} particles, {steps} full PIC steps (push+deposit+Yee+sort)"
+    return n * steps / dtw, (lib.orc_num_threads() if omp else 1), f"{nx}x{ny} cells x {w['ppc']} ppc = {n} particles, {steps} full PIC steps (push+deposit+Yee+sort)"
 
 
 def run_reference(args):
@@ -386,7 +387,9 @@ def main():
             if cb:
                 out["yee"]["cpu_baseline"] = cb
         v, cores, sample = cpu_port_pushes_per_s(w, steps=2)
+        v1, _, sample1 = cpu_port_pushes_per_s(w, steps=1, sample_cells=128, omp=False)
         out["cpu_baseline"] = {"value": v, "unit": "particles/s", "cores": cores, "kind": "port", "sample": sample,
+                               "value_single_core": v1, "sample_single_core": sample1,
                                "note": "reference has no particle code (SURVEY.md F1); this is the repo's scalar FP64 oracle with OpenMP"}
     print(json.dumps(out))
 
