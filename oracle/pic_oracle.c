@@ -171,11 +171,43 @@ void orc_apply_current(const orc_pic_params* P, double* ex, double* ey, double* 
 }
 
 void orc_tile_keys(const orc_pic_params* P, const double* x, const double* y, long n, int* key) {
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static)
+#endif
     for (long p = 0; p < n; p++) key[p] = tile_key(P, x[p], y[p]);
 }
 
 /* Stable counting sort by tile key.  counts has ntiles entries; perm[new_slot] = old_slot. */
 void orc_sort_perm(const int* key, long n, int ntiles, int* counts, long* perm) {
+#ifdef _OPENMP
+    /* all-cores build (the timed CPU baseline): the same stable counting sort with one histogram per thread over a
+       contiguous chunk of slots; offsets are laid out tile-major, thread-minor, so the permutation is the serial one. */
+    if (n > (1L << 16)) {
+        const int T = omp_get_max_threads();
+        long* hist = (long*)calloc((size_t)T * ntiles, sizeof(long));
+#pragma omp parallel num_threads(T)
+        {
+            const int t = omp_get_thread_num();
+            const long lo = n * t / T, hi = n * (t + 1) / T;
+            long* h = hist + (size_t)t * ntiles;
+            for (long p = lo; p < hi; p++) h[key[p]]++;
+#pragma omp barrier
+#pragma omp single
+            {
+                long run = 0;
+                for (int k = 0; k < ntiles; k++) {
+                    long c = 0;
+                    for (int u = 0; u < T; u++) { long v = hist[(size_t)u * ntiles + k]; hist[(size_t)u * ntiles + k] = run + c; c += v; }
+                    counts[k] = (int)c;
+                    run += c;
+                }
+            }
+            for (long p = lo; p < hi; p++) perm[h[key[p]]++] = p;
+        }
+        free(hist);
+        return;
+    }
+#endif
     long* off = (long*)calloc((size_t)ntiles + 1, sizeof(long));
     memset(counts, 0, (size_t)ntiles * sizeof(int));
     for (long p = 0; p < n; p++) counts[key[p]]++;
@@ -237,12 +269,25 @@ void orc_pic_steps(const orc_pic_params* P, double* ex, double* ey, double* ez, 
             orc_sort_perm(key, n, ntiles, counts, perm);
             double* arrs[6] = { x, y, ux, uy, uz, q };
             for (int a = 0; a < 6; a++) {
-                for (long p = 0; p < n; p++) tmp[p] = arrs[a][perm[p]];
-                memcpy(arrs[a], tmp, (size_t)n * sizeof(double));
+                double* src = arrs[a];
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static)
+#endif
+                for (long p = 0; p < n; p++) tmp[p] = src[perm[p]];
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static)
+#endif
+                for (long p = 0; p < n; p++) src[p] = tmp[p];
             }
             int* ti = (int*)tmp;
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static)
+#endif
             for (long p = 0; p < n; p++) ti[p] = tag[perm[p]];
-            memcpy(tag, ti, (size_t)n * sizeof(int));
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static)
+#endif
+            for (long p = 0; p < n; p++) tag[p] = ti[p];
         }
     }
     if (counts_out) {
