@@ -174,3 +174,21 @@ def test_balanced_slab_rows_policy():
     assert all(nr >= 1 for _, nr in slab.balanced_slab_rows(np.array([100.0, 1, 1, 1]), 4))
     costs = slab.tile_row_costs(np.arange(12), 3, 64)
     assert costs.shape == (4,) and costs[1] > costs[0]
+
+
+def test_policy_reproduces_the_measured_beam_partition():
+    """configs[4] at 8 ranks (4096^2 cells, 8 ppc background + 80 ppc beam in rows [0.45, 0.55) of the box): with the cost
+    model calibrated on B200 (slab.W_CELL = 8 particle-equivalents per cell) the exact bottleneck partition is the one the
+    N=8 bench line reports (profiles/r01e_bench_n8_beam2.json: 48,48,24,8,8,24,48,48 tile rows; 3.44 -> 2.12 ms/step)."""
+    slab = importlib.import_module(PKG + ".slab")
+    ny = nx = 4096
+    tn = 16
+    lo, hi = int(round(0.45 * ny)), int(round(0.55 * ny))
+    rows = np.arange(ny)
+    per_tile_row = ((8 + 80 * ((rows >= lo) & (rows < hi))) * nx).reshape(-1, tn).sum(axis=1)
+    costs = per_tile_row + 8.0 * (nx // tn) * tn * tn
+    parts = slab.balanced_slab_rows(costs, 8)
+    assert [nr for _, nr in parts] == [48, 48, 24, 8, 8, 24, 48, 48]
+    load = [costs[r0:r0 + nr].sum() for r0, nr in parts]
+    even = [costs[r * 32:(r + 1) * 32].sum() for r in range(8)]
+    assert max(load) / np.mean(load) < 1.01 and max(even) / np.mean(even) > 1.9
