@@ -60,14 +60,21 @@ static inline double bilerp(const double* F, int nx, int ny, int i, int j, doubl
     return fma(wy, hi - lo, lo);
 }
 
-static inline void jadd(int64_t* J, int nx, int ny, int i, int j, double c) {
+/* `shared`: the plane is written by several threads at once (all-cores build without private planes) */
+static inline void jadd_impl(int64_t* J, int nx, int ny, int i, int j, double c, int shared) {
     int64_t v = (int64_t)llrint(c * ORC_JSCALE);          /* round-to-nearest-even (default rounding mode) */
     int64_t* p = &J[(size_t)wrapi(j, ny) * nx + wrapi(i, nx)];
 #ifdef _OPENMP
+    if (shared) {
 #pragma omp atomic
+        *p += v;
+        return;
+    }
 #endif
+    (void)shared;
     *p += v;
 }
+#define jadd(J, nx, ny, i, j, c) jadd_impl(J, nx, ny, i, j, c, jshared)
 
 /* tile key of a stored (wrapped) position: SURVEY.md B.2 with reciprocal multiply */
 static inline int tile_key(const orc_pic_params* P, double x, double y) {
@@ -90,8 +97,26 @@ void orc_push_deposit(const orc_pic_params* P, const double* ex, const double* e
                       double* x, double* y, double* ux, double* uy, double* uz, const double* q, long n) {
     const int nx = P->nx, ny = P->ny;
     const double h = P->h, dt = P->dt;
+    int jshared = 0;
 #ifdef _OPENMP
-#pragma omp parallel for schedule(static)
+    /* all-cores build: every thread deposits into its own three planes (no atomics) and the planes are summed afterwards --
+       integer adds, so the bits equal the scalar build's; falls back to atomic adds on the shared planes when the private
+       copies would not fit in 1 GB */
+    const size_t nc_ = (size_t)nx * ny;
+    const int T_ = omp_get_max_threads();
+    int64_t* priv = NULL;
+    if (T_ > 1 && n > (1L << 16) && (size_t)T_ * 3 * nc_ * sizeof(int64_t) <= ((size_t)1 << 30)) priv = (int64_t*)malloc((size_t)T_ * 3 * nc_ * sizeof(int64_t));
+    jshared = priv == NULL && T_ > 1;
+    int64_t* const gjx = jx; int64_t* const gjy = jy; int64_t* const gjz = jz;
+#pragma omp parallel
+    {
+    int64_t *jx = gjx, *jy = gjy, *jz = gjz;
+    if (priv) {
+        int64_t* mine = priv + (size_t)omp_get_thread_num() * 3 * nc_;
+        memset(mine, 0, 3 * nc_ * sizeof(int64_t));
+        jx = mine; jy = mine + nc_; jz = mine + 2 * nc_;
+    }
+#pragma omp for schedule(static)
 #endif
     for (long p = 0; p < n; p++) {
         /* ---- gather */
@@ -157,6 +182,21 @@ void orc_push_deposit(const orc_pic_params* P, const double* ex, const double* e
         x[p] = wrap_pos(xn, P->box_x, P->inv_dx, nx);
         y[p] = wrap_pos(yn, P->box_y, P->inv_dy, ny);
     }
+#ifdef _OPENMP
+    }   /* omp parallel */
+    if (priv) {
+        int64_t* const out[3] = { gjx, gjy, gjz };
+        const int used = T_;
+#pragma omp parallel for schedule(static)
+        for (long k = 0; k < (long)nc_; k++)
+            for (int c = 0; c < 3; c++) {
+                int64_t s = 0;
+                for (int t = 0; t < used; t++) s += priv[((size_t)t * 3 + c) * nc_ + k];
+                out[c][k] += s;
+            }
+        free(priv);
+    }
+#endif
 }
 
 /* E <- E - dt*J with J = acc * 2^-52 (applied after the reference E sweep; exact no-op when acc == 0) */
@@ -218,6 +258,7 @@ void orc_sort_perm(const int* key, long n, int ntiles, int* counts, long* perm) 
 
 /* rho (charge density at nodes, Ez lattice) by CIC in fixed point: diagnostic only */
 void orc_deposit_rho(const orc_pic_params* P, const double* x, const double* y, const double* q, long n, int64_t* rho) {
+    const int jshared = 0;
     for (long p = 0; p < n; p++) {
         double X = x[p] * P->inv_dx, Y = y[p] * P->inv_dy;
         double fi = floor(X), fj = floor(Y);
