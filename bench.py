@@ -335,6 +335,7 @@ def main():
         "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong" if w.get("strong") else "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
         "config": {"workload": args.workload, **w, "particles": n, "tile": f"{tn}x{tn}", "dt": dt,
+                   "regime": f"steps {W + 1}..{W + K} after the loader's quiet start (the whole 2000-step run of configs[1] averages 0.649 ms/step: DESIGN.md section 7.0)",
                    "l2": f"particle state {n * 52 / 1e9:.2f} GB per pass >> 126 MB L2 (no flush needed)"},
         "phases_ms": {"push_deposit": push_ms, "fields_and_fold": field_ms, "sort": sort_ms},
         "roofline": {"bound": "hbm", "kernel": "push_deposit_kernel", "achieved": push_gbs, "peak": peak, "unit": "GB/s",
