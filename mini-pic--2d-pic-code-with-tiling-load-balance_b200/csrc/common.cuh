@@ -17,6 +17,7 @@
 #include "../../include/minipic_b200.h"
 
 #define MPIC_X0 16
+#define MPIC_MAX_DEVICES 64                             /* per-device caches of function attributes */
 #define MPIC_JSCALE 4503599627370496.0               /* 2^52: fixed-point scale of the current accumulators */
 #define MPIC_INV_JSCALE (1.0 / 4503599627370496.0)
 
