@@ -105,8 +105,13 @@ int mpic_step_b_half(mpic_sim* s);
 int mpic_step_e_full(mpic_sim* s);
 /* nsteps field-only iterations of the loop PIC_2D.cpp:171-396 (A..F, or A..D for scheme 1). */
 int mpic_field_steps(mpic_sim* s, int nsteps);
-/* Same result (bit-identical) from one fused kernel per step (overlapped-tile B/2,E,B/2; 96 B/cell instead of 216). */
+/* Same result (bit-identical) from ONE kernel per step (csrc/yee.cu fused_yee_kernel: tile + ring of all six planes staged
+ * by one TMA box load, half-B -> E -> half-B in shared memory, out of place between two plane blocks): 96 B/cell of HBM
+ * traffic instead of 216.  scheme 1 (two sweeps) falls back to mpic_field_steps. */
 int mpic_field_steps_fused(mpic_sim* s, int nsteps);
+/* Phases A..F of ONE step fused as above, with the -dt*J term (guard ring of J folded on the fly, accumulators zeroed)
+ * when the handle holds particles.  Single slab, scheme 0.  mpic_pic_steps uses it. */
+int mpic_step_fields_fused(mpic_sim* s);
 
 /* ---- slab halos (nranks > 1): replace the inter-rank part of the exchange phases B/D/F (PIC_2D.cpp:200-248,276-319,
  * 348-396; MPI_Isend/Irecv of packSendBuffer strips) for a 1-D slab decomposition over tile rows.
@@ -160,6 +165,9 @@ int mpic_peer_connect(mpic_sim* s, const mpic_peer_info* lo, const mpic_peer_inf
 int mpic_peer_refresh_begin(mpic_sim* s);   /* after uploads: y guards of E and B from the neighbours */
 int mpic_peer_refresh_end(mpic_sim* s);
 int mpic_peer_field_step(mpic_sim* s);      /* phases A..F of one step; no host synchronisation at all */
+/* The same step (bit-identical) from the fused kernel of mpic_field_steps_fused: ONE launch and ONE flag exchange per
+ * step; edge rows go straight into the neighbours' other plane block.  All ranks must call the same sequence. */
+int mpic_peer_field_step_fused(mpic_sim* s);
 int mpic_peer_step_begin(mpic_sim* s);      /* push+deposit, hand-off, J add, Yee phases: everything enqueued, no host wait */
 int mpic_peer_step_end(mpic_sim* s);        /* migration counts (the one host wait), arrivals absorbed, tile sort */
 

@@ -61,7 +61,7 @@ def lib():
     L.mpic_num_particles.argtypes = [C.c_void_p]
     L.mpic_create.argtypes = [C.POINTER(Params), C.POINTER(C.c_void_p)]
     for name in ("mpic_destroy", "mpic_sync", "mpic_step_b_half", "mpic_step_e_full", "mpic_push_deposit",
-                 "mpic_sort_tiles", "mpic_fold_current"):
+                 "mpic_sort_tiles", "mpic_fold_current", "mpic_step_fields_fused", "mpic_peer_field_step_fused"):
         getattr(L, name).argtypes = [C.c_void_p]
     for name in ("mpic_field_steps", "mpic_field_steps_fused", "mpic_pic_steps", "mpic_halo_pack", "mpic_halo_unpack"):
         getattr(L, name).argtypes = [C.c_void_p, C.c_int]
@@ -214,7 +214,12 @@ class Sim:
         _chk(lib().mpic_step_e_full(self.h))
 
     def field_steps(self, n, fused=False):
+        """n iterations of half-B / E / half-B (PIC_2D.cpp:171-396).  fused=True: one kernel per step (bit-identical)."""
         _chk((lib().mpic_field_steps_fused if fused else lib().mpic_field_steps)(self.h, n))
+
+    def step_fields_fused(self):
+        """Phases A..F of one step in ONE kernel, with the -dt*J term when particles are present (single slab)."""
+        _chk(lib().mpic_step_fields_fused(self.h))
 
     # ---- slab plumbing (nranks > 1); the torch tensors are zero-copy views of the library's device staging buffers
     def halo_tensors(self):
@@ -263,8 +268,8 @@ class Sim:
     def peer_refresh_end(self):
         _chk(lib().mpic_peer_refresh_end(self.h))
 
-    def peer_field_step(self):
-        _chk(lib().mpic_peer_field_step(self.h))
+    def peer_field_step(self, fused=False):
+        _chk((lib().mpic_peer_field_step_fused if fused else lib().mpic_peer_field_step)(self.h))
 
     def peer_step_begin(self):
         _chk(lib().mpic_peer_step_begin(self.h))

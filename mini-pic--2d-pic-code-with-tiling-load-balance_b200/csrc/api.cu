@@ -9,6 +9,7 @@
 #include <math.h>
 #include <vector>
 #include <string>
+#include <utility>
 
 static thread_local char g_err[512] = "";
 void mpic_set_error(const char* fmt, ...) {
@@ -129,7 +130,7 @@ int mpic_update_guard_region(double* grid6, int tnx, int tny, int g, int d, cons
 }
 
 // ------------------------------------------------------------------------------------------ handle
-static int make_tensor_map(mpic_sim* s) {
+static int encode_box_map(mpic_sim* s, double* planes, int pw, int ph, CUtensorMap* out) {
     typedef CUresult (*encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -137,17 +138,21 @@ static int make_tensor_map(mpic_sim* s) {
     cudaDriverEntryPointQueryResult qres;
     CUDA_TRY(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
     REQUIRE(fn && qres == cudaDriverEntryPointSuccess, MPIC_ECUDA, "cuTensorMapEncodeTiled not available");
-    int pw, ph;
-    push_box_dims(s->P.tnx, s->P.tny, &pw, &ph);
     REQUIRE(pw <= 256 && ph <= 256, MPIC_EINVAL, "tile too large for one TMA box (max 254 cells per side)");
     cuuint64_t gdim[3] = { (cuuint64_t)s->G.pitch, (cuuint64_t)s->G.rows, 6 };
     cuuint64_t gstr[2] = { (cuuint64_t)s->G.pitch * 8, (cuuint64_t)s->G.plane * 8 };
     cuuint32_t box[3] = { (cuuint32_t)pw, (cuuint32_t)ph, 6 };
     cuuint32_t estr[3] = { 1, 1, 1 };
-    CUresult r = ((encode_fn)fn)(&s->tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, s->planes, gdim, gstr, box, estr,
+    CUresult r = ((encode_fn)fn)(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, planes, gdim, gstr, box, estr,
                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     REQUIRE(r == CUDA_SUCCESS, MPIC_ECUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return 0;
+}
+static int make_tensor_map(mpic_sim* s) {
+    int pw, ph;
+    push_box_dims(s->P.tnx, s->P.tny, &pw, &ph);
+    TRY(encode_box_map(s, s->planes, pw, ph, &s->tmap));
     s->has_tmap = true;
     return 0;
 }
@@ -261,7 +266,7 @@ int mpic_destroy(mpic_sim* s) {
     if (s->st) cudaStreamSynchronize(s->st);
     mpic_ring_release(s);
     mpic_peer_release(s);
-    cudaFree(s->planes); cudaFree(s->jacc); cudaFree(s->rho); cudaFree(s->d_scratch);
+    cudaFree(s->planes); cudaFree(s->planes_alt); cudaFree(s->jacc); cudaFree(s->rho); cudaFree(s->d_scratch);
     for (int k = 0; k < 2; k++) { cudaFree(s->pa[k].x); cudaFree(s->pa[k].tag); }
     cudaFree(s->cell_start); cudaFree(s->cell_count); cudaFree(s->scan_tmp); cudaFree(s->keys); cudaFree(s->perm);
     cudaFree(s->halo_send); cudaFree(s->halo_recv); cudaFree(s->lv.count);
@@ -389,8 +394,55 @@ int mpic_field_steps(mpic_sim* s, int nsteps) {
     }
     return 0;
 }
+}  // extern "C"
+int mpic_fused_setup(mpic_sim* s) {
+    if (s->fused_ready) return 0;
+    const size_t bytes = (size_t)6 * s->G.plane * 8;
+    if (!s->planes_alt) {
+        CUDA_TRY(cudaMalloc(&s->planes_alt, bytes));
+        CUDA_TRY(cudaMemsetAsync(s->planes_alt, 0, bytes, s->st));
+    }
+    int pw, ph;
+    fused_box_dims(&pw, &ph);
+    TRY(encode_box_map(s, s->planes, pw, ph, &s->ftmap));
+    TRY(encode_box_map(s, s->planes_alt, pw, ph, &s->ftmap_alt));
+    if (s->has_tmap) {
+        push_box_dims(s->P.tnx, s->P.tny, &pw, &ph);
+        TRY(encode_box_map(s, s->planes_alt, pw, ph, &s->tmap_alt));
+    }
+    s->fused_ready = true;
+    return 0;
+}
+void mpic_fused_swap(mpic_sim* s) {
+    std::swap(s->planes, s->planes_alt);
+    std::swap(s->ftmap, s->ftmap_alt);
+    if (s->has_tmap) std::swap(s->tmap, s->tmap_alt);
+    for (int side = 0; side < 2; side++) std::swap(s->peer[side].planes, s->peer[side].planes_alt);
+}
+// one fused half-B / E / half-B step of a single slab (periodic in y inside the kernel's images)
+static int fused_step_local(mpic_sim* s, int with_j) {
+    TRY(mpic_fused_setup(s));
+    TRY(launch_fused_step(s->G, &s->ftmap, s->planes_alt, s->jacc, with_j, s->cf, PeerHalo(), PeerSync(), s->st));
+    s->launches++;
+    if (with_j) CUDA_TRY(cudaMemsetAsync(s->jacc, 0, (size_t)3 * s->G.plane * 8, s->st));   // the accumulators are consumed
+    mpic_fused_swap(s);
+    return 0;
+}
+extern "C" {
+int mpic_step_fields_fused(mpic_sim* s) {
+    if (s) cudaSetDevice(s->prm.device);
+    REQUIRE(s, MPIC_EINVAL, "null handle");
+    REQUIRE(s->prm.nranks == 1 && s->prm.scheme == 0, MPIC_ESTATE, "mpic_step_fields_fused: single slab, scheme 0 only");
+    return fused_step_local(s, s->cap > 0);
+}
 int mpic_field_steps_fused(mpic_sim* s, int nsteps) {
-    if (s) cudaSetDevice(s->prm.device); return mpic_field_steps(s, nsteps); }   // fused kernel: see round notes
+    if (s) cudaSetDevice(s->prm.device);
+    REQUIRE(s && nsteps >= 0, MPIC_EINVAL, "bad argument");
+    REQUIRE(s->prm.nranks == 1, MPIC_ESTATE, "mpic_field_steps_fused needs a single slab (slabs: mpic_peer_field_step_fused)");
+    if (s->prm.scheme != 0) return mpic_field_steps(s, nsteps);      // v1 scheme (B full dt, E): two sweeps, nothing to fuse across
+    for (int k = 0; k < nsteps; k++) TRY(fused_step_local(s, 0));
+    return 0;
+}
 
 // ------------------------------------------------------------------------------------------ halos
 static double* halo_base(mpic_sim* s, int which) {
@@ -597,11 +649,15 @@ int mpic_pic_steps(mpic_sim* s, int nsteps) {
     REQUIRE(s && nsteps >= 0, MPIC_EINVAL, "bad argument");
     REQUIRE(s->cap > 0, MPIC_ESTATE, "no particle storage");
     REQUIRE(s->prm.nranks == 1, MPIC_ESTATE, "mpic_pic_steps needs a single slab; drive phases + halos from the host for nranks>1");
+    static const bool fuse = !getenv("MPIC_NO_FUSED_YEE");
     for (int k = 0; k < nsteps; k++) {
         TRY(mpic_push_deposit(s));
-        TRY(mpic_step_b_half(s));                       // the E sweep folds the J guard ring on the fly (yee.cu)
-        TRY(e_sweep(s, 1));
-        TRY(mpic_step_b_half(s));
+        if (fuse && s->prm.scheme == 0) TRY(fused_step_local(s, 1));   // half-B, E - dt*J (guard ring folded on the fly), half-B: one kernel
+        else {
+            TRY(mpic_step_b_half(s));                   // the E sweep folds the J guard ring on the fly (yee.cu)
+            TRY(e_sweep(s, 1));
+            TRY(mpic_step_b_half(s));
+        }
         TRY(sort_all(s, true));
     }
     return 0;

@@ -109,8 +109,9 @@ static inline int ceil_div(int64_t a, int64_t b) { return (int)((a + b - 1) / b)
 struct YeeCoef { double bx, by, ex, ey, dt; int fma; };   // bx = dt/(2dx) or dt/dx ; ex = dt/dx
 int launch_b_sweep(const FieldGeom& G, double* planes, const YeeCoef& c, const PeerHalo& ph, PeerSync ps, cudaStream_t st);
 int launch_e_sweep(const FieldGeom& G, double* planes, int64_t* jacc, int with_j, const YeeCoef& c, const PeerHalo& ph, PeerSync ps, cudaStream_t st);
-int launch_fused_step(const FieldGeom& G, const double* src, double* dst, int64_t* jacc, int with_j,
-                      const YeeCoef& c, int scheme, cudaStream_t st);
+int launch_fused_step(const FieldGeom& G, const CUtensorMap* src_map, double* dst, const int64_t* jacc, int with_j, const YeeCoef& c,
+                      const PeerHalo& dst_halo, PeerSync ps, cudaStream_t st);
+void fused_box_dims(int* pw, int* ph);
 int launch_wrap_guards(const FieldGeom& G, double* planes, int first_plane, int nplanes, int do_y, cudaStream_t st);
 int launch_fold_current(const FieldGeom& G, int64_t* jacc, int nplanes, int do_y, cudaStream_t st);
 // slab halos: staging layout [side][3 planes][g rows][pitch] (+ header), side 0 = lower neighbour, 1 = upper neighbour

@@ -20,7 +20,7 @@
 
 namespace {
 
-enum Phase { PH_J = 0, PH_B1 = 1, PH_E = 2, PH_B2 = 3, PH_R1 = 4, PH_R2 = 5, PH_COUNT = 6 };
+enum Phase { PH_J = 0, PH_B1 = 1, PH_E = 2, PH_B2 = 3, PH_R1 = 4, PH_R2 = 5, PH_F = 6, PH_COUNT = 7 };   // PH_F: fused field step
 constexpr int CTL_WORDS = 64;
 constexpr int CTL_ARRIVE = 16;        // + parity*2 + from_side : record count written by that neighbour
 constexpr int CTL_ERROR = 24;         // non-zero: a wait timed out (value = 1 + phase)
@@ -31,9 +31,9 @@ struct PeerBlob {                     // what travels inside mpic_peer_info
     unsigned long long magic;
     int pid, device, rank, nyl, lcap, pad;
     int64_t plane;
-    void* raw[4];                     // planes, jacc, arrive block, control block (valid inside the exporting process)
-    cudaIpcMemHandle_t h[4];
-    unsigned long long has[4];
+    void* raw[5];                     // planes, jacc, arrive block, control block, planes_alt (valid inside the exporting process)
+    cudaIpcMemHandle_t h[5];
+    unsigned long long has[5];
 };
 static_assert(sizeof(PeerBlob) <= sizeof(mpic_peer_info), "peer blob does not fit");
 
@@ -213,8 +213,8 @@ int check_error_word(mpic_sim* s, unsigned long long w) {
 int open_side(mpic_sim* s, int side, const PeerBlob& b, const mpic_sim::PeerSide* same) {
     mpic_sim::PeerSide& p = s->peer[side];
     p.plane = b.plane; p.nyl = b.nyl; p.lcap = b.lcap;
-    if (same) { p.planes = same->planes; p.jacc = same->jacc; p.arrive = same->arrive; p.ctl = same->ctl; p.ipc = false; return 0; }
-    void* ptr[4] = { nullptr, nullptr, nullptr, nullptr };
+    if (same) { p.planes = same->planes; p.planes_alt = same->planes_alt; p.jacc = same->jacc; p.arrive = same->arrive; p.ctl = same->ctl; p.ipc = false; return 0; }
+    void* ptr[5] = { nullptr, nullptr, nullptr, nullptr, nullptr };
     if (b.pid == (int)getpid()) {                       // same process: plain pointers (+ peer access across devices)
         if (b.device != s->prm.device) {
             int can = 0;
@@ -224,13 +224,13 @@ int open_side(mpic_sim* s, int side, const PeerBlob& b, const mpic_sim::PeerSide
             if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) CUDA_TRY(e);
             cudaGetLastError();
         }
-        for (int k = 0; k < 4; k++) ptr[k] = b.raw[k];
+        for (int k = 0; k < 5; k++) ptr[k] = b.raw[k];
     } else {
-        for (int k = 0; k < 4; k++)
+        for (int k = 0; k < 5; k++)
             if (b.has[k]) CUDA_TRY(cudaIpcOpenMemHandle(&ptr[k], b.h[k], cudaIpcMemLazyEnablePeerAccess));
         p.ipc = true;
     }
-    p.planes = (double*)ptr[0]; p.jacc = (unsigned long long*)ptr[1]; p.arrive = (double*)ptr[2]; p.ctl = (unsigned long long*)ptr[3];
+    p.planes = (double*)ptr[0]; p.planes_alt = (double*)ptr[4]; p.jacc = (unsigned long long*)ptr[1]; p.arrive = (double*)ptr[2]; p.ctl = (unsigned long long*)ptr[3];
     return 0;
 }
 
@@ -240,7 +240,7 @@ void mpic_peer_release(mpic_sim* s) {
     if (!s) return;
     for (int side = 0; side < 2; side++) {
         mpic_sim::PeerSide& p = s->peer[side];
-        if (p.ipc) { cudaIpcCloseMemHandle(p.planes); cudaIpcCloseMemHandle(p.jacc); if (p.arrive) cudaIpcCloseMemHandle(p.arrive); cudaIpcCloseMemHandle(p.ctl); }
+        if (p.ipc) { cudaIpcCloseMemHandle(p.planes); if (p.planes_alt) cudaIpcCloseMemHandle(p.planes_alt); cudaIpcCloseMemHandle(p.jacc); if (p.arrive) cudaIpcCloseMemHandle(p.arrive); cudaIpcCloseMemHandle(p.ctl); }
         p = mpic_sim::PeerSide();
     }
     trace_report(s);
@@ -269,8 +269,9 @@ int mpic_peer_export(mpic_sim* s, mpic_peer_info* out) {
     memset(&b, 0, sizeof b);
     b.magic = PEER_MAGIC; b.pid = (int)getpid(); b.device = s->prm.device; b.rank = s->prm.rank; b.nyl = s->G.nyl;
     b.lcap = s->lv.cap; b.plane = s->G.plane;
-    b.raw[0] = s->planes; b.raw[1] = s->jacc; b.raw[2] = s->arrive_blk; b.raw[3] = s->ctl;
-    for (int k = 0; k < 4; k++)
+    TRY(mpic_fused_setup(s));                            // the second plane block of the fused step is peer-visible too
+    b.raw[0] = s->planes; b.raw[1] = s->jacc; b.raw[2] = s->arrive_blk; b.raw[3] = s->ctl; b.raw[4] = s->planes_alt;
+    for (int k = 0; k < 5; k++)
         if (b.raw[k]) { CUDA_TRY(cudaIpcGetMemHandle(&b.h[k], b.raw[k])); b.has[k] = 1; }
     memcpy(out->bytes, &b, sizeof b);
     return 0;
@@ -367,6 +368,29 @@ int mpic_peer_field_step(mpic_sim* s) {
     REQUIRE(s && s->peer_on, MPIC_ESTATE, "peer ring not connected");
     TRY(b2_wait_if_pending(s));
     return yee_phases(s, 0);
+}
+
+// One fused kernel per field step over the ring: the slab-edge CTAs await the neighbours' PREVIOUS fused step (its stores
+// filled the guard rows this step reads, and it was the last reader of the guard rows this step overwrites in the
+// neighbours' other plane block), every other CTA starts at once; the last edge CTA of each side raises this step's flag.
+// One flag exchange per step instead of three.  Every rank must take the same sequence of fused / unfused steps (the plane
+// blocks swap in lockstep).
+int mpic_peer_field_step_fused(mpic_sim* s) {
+    if (s) cudaSetDevice(s->prm.device);
+    REQUIRE(s && s->peer_on, MPIC_ESTATE, "peer ring not connected");
+    REQUIRE(s->prm.scheme == 0, MPIC_ESTATE, "fused step: scheme 0 only");
+    REQUIRE(s->peer[0].planes_alt && s->peer[1].planes_alt, MPIC_ESTATE, "neighbours exported no second plane block");
+    TRY(b2_wait_if_pending(s));                          // a preceding unfused phase: await it with its own flag
+    PeerHalo h;                                          // images go into the neighbours' OTHER block (their dst of this step)
+    h.lo = s->peer[0].planes_alt; h.hi = s->peer[1].planes_alt;
+    h.lo_plane = s->peer[0].plane; h.hi_plane = s->peer[1].plane;
+    h.lo_row0 = s->G.g + s->peer[0].nyl;
+    TRY(launch_fused_step(s->G, &s->ftmap, s->planes_alt, s->jacc, 0, s->cf, h, sweep_sync(s, PH_F, PH_F), s->st));
+    s->launches++;
+    mpic_fused_swap(s);
+    s->b2_pending = true;                                // the flag just raised by the neighbours is awaited by the next reader
+    s->pending_ph = PH_F;
+    return 0;
 }
 
 int mpic_peer_step_begin(mpic_sim* s) {

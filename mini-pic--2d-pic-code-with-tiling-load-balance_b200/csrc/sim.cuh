@@ -20,8 +20,13 @@ struct mpic_sim {
     int* cell_count = nullptr;     // n_entries (doubles as scatter cursor)
     int* scan_tmp = nullptr;
     int n_entries = 0;             // ncells + 2 (leave-down, leave-up bins)
-    CUtensorMap tmap;
+    CUtensorMap tmap;               // push kernel: tile + 1-cell ring box on `planes`
     bool has_tmap = false;
+    // fused Yee step (yee.cu: fused_yee_kernel) ping-pongs between `planes` and `planes_alt`; after every fused step the two
+    // blocks (and every map / peer pointer bound to them) are swapped, so `planes` always names the current fields
+    double* planes_alt = nullptr;
+    CUtensorMap tmap_alt, ftmap, ftmap_alt;   // push box on planes_alt; fused-step box on planes / planes_alt
+    bool fused_ready = false;
     double* d_scratch = nullptr;   // 8 doubles
     int64_t tag_base = 0;
     int64_t launches = 0;
@@ -43,6 +48,7 @@ struct mpic_sim {
     // ---- peer-memory ring (peer.cu)
     struct PeerSide {
         double* planes = nullptr;          // neighbour's 6 field planes
+        double* planes_alt = nullptr;      // neighbour's other plane block (fused step ping-pong; swapped in lockstep)
         unsigned long long* jacc = nullptr; // neighbour's 3 current accumulators
         double* arrive = nullptr;          // neighbour's arrival block: [parity][from side][cap records]
         unsigned long long* ctl = nullptr; // neighbour's control block (flags + arrival counts)
@@ -75,6 +81,8 @@ struct mpic_sim {
 };
 
 void mpic_ring_release(mpic_sim* s);
+int mpic_fused_setup(mpic_sim* s);                   // api.cu: second plane block + tensor maps (idempotent)
+void mpic_fused_swap(mpic_sim* s);                   // api.cu: planes <-> planes_alt (+ maps, + peer pointers)
 void mpic_peer_release(mpic_sim* s);
 extern "C" int mpic_sort_after_push(mpic_sim* s);   // api.cu: sort_all(counted)
 #define HALO_HDR 16                /* values (128 B) of header in front of each halo message; [0] = leaver count to that side */

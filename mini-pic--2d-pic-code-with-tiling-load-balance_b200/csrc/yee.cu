@@ -8,8 +8,10 @@
 // Arithmetic contract: this file is compiled with -fmad=false, so every expression below is evaluated in exactly the
 // written order with one rounding per operation == the reference built without contraction.  fma_mode==1 uses explicit
 // fma() in the pattern a per-statement contracting compiler (the build that produced the shipped dumps) generates.
-// Roofline: HBM-bound; algorithmic bytes 72 B/cell per sweep (read 3+3 planes, write 3), 216 B per 3-sweep step.
+// Roofline: HBM-bound; algorithmic bytes 72 B/cell per sweep (read 3+3 planes, write 3), 216 B per 3-sweep step;
+// the fused step (fused_yee_kernel) moves 96 B/cell (+ halo ring re-reads served by L2).
 #include "common.cuh"
+#include <mutex>
 
 namespace {
 
@@ -190,6 +192,172 @@ __global__ void __launch_bounds__(256) e_sweep_kernel(FieldGeom G, double* __res
     store_images(G, ex, i, j, nex, H.lo, H.hi, H.lo_row0);
     store_images(G, ey, i, j, ney, H.lo ? H.lo + H.lo_plane : nullptr, H.hi ? H.hi + H.hi_plane : nullptr, H.lo_row0);
     store_images(G, ez, i, j, nez, H.lo ? H.lo + 2 * H.lo_plane : nullptr, H.hi ? H.hi + 2 * H.hi_plane : nullptr, H.lo_row0);
+    }
+    edge_signal(S, lo_edge, hi_edge);
+}
+
+// ------------------------------------------------------------------------------------------------ fused step
+// One kernel per time step: half-B -> E (-dt*J) -> half-B on an overlapped tile, all three in shared memory.
+// Replaces, per step, the three sweeps above (= phases A..F of PIC_2D.cpp:171-396 around Field_update.cpp:14-59) with ONE
+// pass over HBM: every plane is read once (plus a halo ring: 1 cell below/left, 2 above/right) and written once --
+// 96 B/cell algorithmic + ~20 % halo re-reads that hit L2, instead of 216 B.  Out of place (src planes -> dst planes, the
+// handle ping-pongs): other CTAs read this tile's ring from src while this CTA writes dst.
+// Dependencies: B'(i,j) needs E(i..i+1, j..j+1); E'(i,j) needs B'(i-1..i, j-1..j); B''(i,j) needs E'(i..i+1, j..j+1).  For a tile
+// [x0,x0+TX) x [y0,y0+TY): B' on [x0-1, x0+TX] x [y0-1, y0+TY], E' on [x0, x0+TX] x [y0, y0+TY], B'' on the tile.  Ring cells
+// are recomputed by the neighbouring CTAs from the same inputs with the same operations -> every value is bit-identical
+// to the three-sweep result.  The guard ring of src holds the periodic images (or the neighbour slab's rows), exactly as
+// after the reference's exchange phases, so tiles at the box edge need no special case; dst gets its images from
+// store_images like the sweeps.
+// The tile + ring of all six planes is ONE 3-D TMA box load (x start 2 cells early: the box must begin on 16 bytes).
+constexpr int FY_TX = 64;
+#ifndef FY_TY_T
+#define FY_TY_T 16
+#endif
+constexpr int FY_TY = FY_TY_T;
+constexpr int FY_PW = FY_TX + 4, FY_PH = FY_TY + 3, FY_PP = FY_PW * FY_PH;
+constexpr int FY_THREADS = 256;
+constexpr size_t FY_SMEM = (size_t)6 * FY_PP * 8 + 16;
+
+__device__ __forceinline__ uint32_t fy_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+template <int FMA>
+__device__ __forceinline__ void fy_b_update(double* __restrict__ F, int k, double cx, double cy, double& nbx, double& nby, double& nbz) {
+    const double* ex = F;
+    const double* ey = F + FY_PP;
+    const double* ez = F + 2 * FY_PP;
+    const int kx = k + 1, ky = k + FY_PW;
+    const double ez0 = ez[k];
+    const double dEz_y = ez[ky] - ez0, dEz_x = ez[kx] - ez0;
+    const double dEy_x = ey[kx] - ey[k], dEx_y = ex[ky] - ex[k];
+    const double bx = F[3 * FY_PP + k], by = F[4 * FY_PP + k], bz = F[5 * FY_PP + k];
+    if (FMA) {
+        nbx = fma(-cy, dEz_y, bx);
+        nby = fma(cx, dEz_x, by);
+        nbz = fma(cy, dEx_y, fma(-cx, dEy_x, bz));
+    } else {
+        nbx = bx - cy * dEz_y;
+        nby = by + cx * dEz_x;
+        nbz = bz - cx * dEy_x + cy * dEx_y;
+    }
+}
+
+// current of cell (i,j) with every periodic image folded in (the same sum the E sweep forms; integer adds, any order)
+__device__ __forceinline__ void fy_folded_j(const FieldGeom& G, const int64_t* __restrict__ jacc, int i, int j, int64_t (&jv)[3]) {
+    const int g = G.g;
+    const int ic = i >= G.nx ? i - G.nx : i, jc = j >= G.nyl ? j - G.nyl : j;       // ring cell beyond the edge -> its interior image
+    const int64_t k = fidx(G, ic, jc);
+    const int xs = ic < g ? G.nx : (ic >= G.nx - g ? -G.nx : 0);
+    const int64_t ys = jc < g ? (int64_t)G.nyl * G.pitch : (jc >= G.nyl - g ? -(int64_t)G.nyl * G.pitch : 0);
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        const int64_t* a = jacc + c * G.plane;
+        int64_t v = a[k];
+        if (xs) v += a[k + xs];
+        if (ys) { v += a[k + ys]; if (xs) v += a[k + ys + xs]; }
+        jv[c] = v;
+    }
+}
+
+template <int FMA, int WITH_J>
+__global__ void __launch_bounds__(FY_THREADS) fused_yee_kernel(FieldGeom G, const __grid_constant__ CUtensorMap tmap, double* __restrict__ dst,
+                                                               const int64_t* __restrict__ jacc, double bcx, double bcy, double ecx,
+                                                               double ecy, double dt, PeerHalo H, PeerSync S) {
+    extern __shared__ __align__(128) unsigned char fy_raw[];
+    double* F = reinterpret_cast<double*>(fy_raw);
+    uint64_t* bar = reinterpret_cast<uint64_t*>(fy_raw + (size_t)6 * FY_PP * 8);
+    const int brow = edge_first_row(S);
+    const int x0 = blockIdx.x * FY_TX, y0 = brow * FY_TY;
+    // slab-edge CTAs read guard rows filled by a neighbour and store into the neighbour's guard rows
+    const bool lo_edge = S.done && y0 == 0, hi_edge = S.done && y0 + FY_TY + 2 > G.nyl;
+    if (threadIdx.x == 0) {
+        if (S.want && (lo_edge || hi_edge)) {
+            unsigned long long t0;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+            for (int side = 0; side < 2; side++) {
+                if (!(side ? hi_edge : lo_edge)) continue;
+                while (ld_acquire_sys_u64(S.wait_flags + side) < S.want) {
+                    unsigned long long t1;
+                    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+                    if (t1 - t0 > S.timeout_ns) { atomicExch(S.err, 1ull + S.phase); break; }
+                    __nanosleep(32);
+                }
+            }
+            asm volatile("fence.proxy.async;" ::: "memory");          // the TMA (async proxy) must see the neighbours' stores
+        }
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(fy_smem_u32(bar)), "r"(1) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fy_smem_u32(bar)), "r"((uint32_t)(6 * FY_PP * 8)) : "memory");
+        asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                     ::"r"(fy_smem_u32(F)), "l"(&tmap), "r"(MPIC_X0 + x0 - 2), "r"(G.g + y0 - 1), "r"(0), "r"(fy_smem_u32(bar)) : "memory");
+    }
+    __syncthreads();
+    asm volatile(
+        "{\n.reg .pred p;\nFY_WAIT:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n@p bra FY_DONE;\nbra FY_WAIT;\nFY_DONE:\n}\n"
+        ::"r"(fy_smem_u32(bar)), "r"(0) : "memory");
+
+    // smem element (lx, ly) <-> slab cell (x0 - 2 + lx, y0 - 1 + ly)
+    // ---- phase A: B' = B - (dt/2) curl E on [x0-1, x0+TX] x [y0-1, y0+TY], in place
+    for (int e = threadIdx.x; e < (FY_TX + 2) * (FY_TY + 2); e += FY_THREADS) {
+        const int ly = e / (FY_TX + 2), lx = e - ly * (FY_TX + 2) + 1;
+        const int k = ly * FY_PW + lx;
+        double nbx, nby, nbz;
+        fy_b_update<FMA>(F, k, bcx, bcy, nbx, nby, nbz);
+        F[3 * FY_PP + k] = nbx; F[4 * FY_PP + k] = nby; F[5 * FY_PP + k] = nbz;
+    }
+    __syncthreads();
+    // ---- phase C: E' = E + dt curl B' (- dt J) on [x0, x0+TX] x [y0, y0+TY], in place
+    for (int e = threadIdx.x; e < (FY_TX + 1) * (FY_TY + 1); e += FY_THREADS) {
+        const int ly = e / (FY_TX + 1) + 1, lx = e - (ly - 1) * (FY_TX + 1) + 2;
+        const int k = ly * FY_PW + lx, kx = k - 1, ky = k - FY_PW;
+        const double* bx = F + 3 * FY_PP;
+        const double* by = F + 4 * FY_PP;
+        const double* bz = F + 5 * FY_PP;
+        const double bz0 = bz[k];
+        const double dBz_y = bz0 - bz[ky], dBz_x = bz0 - bz[kx];
+        const double dBy_x = by[k] - by[kx], dBx_y = bx[k] - bx[ky];
+        double nex, ney, nez;
+        if (FMA) {
+            nex = fma(ecy, dBz_y, F[k]);
+            ney = fma(-ecx, dBz_x, F[FY_PP + k]);
+            nez = F[2 * FY_PP + k] + fma(ecx, dBy_x, -(ecy * dBx_y));
+        } else {
+            nex = F[k] + ecy * dBz_y;
+            ney = F[FY_PP + k] - ecx * dBz_x;
+            nez = F[2 * FY_PP + k] + (ecx * dBy_x - ecy * dBx_y);
+        }
+        if (WITH_J) {
+            const int i = x0 - 2 + lx, j = y0 - 1 + ly;
+            if (i <= G.nx && j <= G.nyl) {
+                int64_t jv[3];
+                fy_folded_j(G, jacc, i, j, jv);
+                nex = fma(-dt, __ll2double_rn(jv[0]) * MPIC_INV_JSCALE, nex);
+                ney = fma(-dt, __ll2double_rn(jv[1]) * MPIC_INV_JSCALE, ney);
+                nez = fma(-dt, __ll2double_rn(jv[2]) * MPIC_INV_JSCALE, nez);
+            }
+        }
+        F[k] = nex; F[FY_PP + k] = ney; F[2 * FY_PP + k] = nez;
+    }
+    __syncthreads();
+    // ---- phase E: B'' = B' - (dt/2) curl E' on the tile; E' and B'' go to dst with their periodic / neighbour-slab images
+    {
+        const int tx = threadIdx.x & (FY_TX - 1), ty0 = threadIdx.x / FY_TX;
+        const int i = x0 + tx;
+        for (int ty = ty0; ty < FY_TY; ty += FY_THREADS / FY_TX) {
+            const int j = y0 + ty;
+            if (i < G.nx && j < G.nyl) {
+                const int k = (ty + 1) * FY_PW + tx + 2;
+                double nbx, nby, nbz;
+                fy_b_update<FMA>(F, k, bcx, bcy, nbx, nby, nbz);
+                double* d = dst;
+                store_images(G, d, i, j, F[k], H.lo, H.hi, H.lo_row0);
+                store_images(G, d + G.plane, i, j, F[FY_PP + k], H.lo ? H.lo + H.lo_plane : nullptr, H.hi ? H.hi + H.hi_plane : nullptr, H.lo_row0);
+                store_images(G, d + 2 * G.plane, i, j, F[2 * FY_PP + k], H.lo ? H.lo + 2 * H.lo_plane : nullptr, H.hi ? H.hi + 2 * H.hi_plane : nullptr, H.lo_row0);
+                store_images(G, d + 3 * G.plane, i, j, nbx, H.lo ? H.lo + 3 * H.lo_plane : nullptr, H.hi ? H.hi + 3 * H.hi_plane : nullptr, H.lo_row0);
+                store_images(G, d + 4 * G.plane, i, j, nby, H.lo ? H.lo + 4 * H.lo_plane : nullptr, H.hi ? H.hi + 4 * H.hi_plane : nullptr, H.lo_row0);
+                store_images(G, d + 5 * G.plane, i, j, nbz, H.lo ? H.lo + 5 * H.lo_plane : nullptr, H.hi ? H.hi + 5 * H.hi_plane : nullptr, H.lo_row0);
+            }
+        }
     }
     edge_signal(S, lo_edge, hi_edge);
 }
@@ -394,6 +562,40 @@ int launch_e_sweep(const FieldGeom& G, double* planes, int64_t* jacc, int with_j
     LAUNCH_CHECK();
     return 0;
 }
+// fused step: src planes are read through `tmap` (box FY_PW x FY_PH x 6 on the src block), dst is the other plane block
+void fused_box_dims(int* pw, int* ph) { *pw = FY_PW; *ph = FY_PH; }
+int launch_fused_step(const FieldGeom& G, const CUtensorMap* tmap, double* dst, const int64_t* jacc, int with_j, const YeeCoef& c,
+                      const PeerHalo& ph, PeerSync ps, cudaStream_t st) {
+    static std::mutex mu;
+    static bool configured[MPIC_MAX_DEVICES] = {};
+    {
+        int dev = 0;
+        CUDA_TRY(cudaGetDevice(&dev));
+        std::lock_guard<std::mutex> lock(mu);
+        if (dev < 0 || dev >= MPIC_MAX_DEVICES || !configured[dev]) {
+            CUDA_TRY(cudaFuncSetAttribute(fused_yee_kernel<0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FY_SMEM));
+            CUDA_TRY(cudaFuncSetAttribute(fused_yee_kernel<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FY_SMEM));
+            CUDA_TRY(cudaFuncSetAttribute(fused_yee_kernel<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FY_SMEM));
+            CUDA_TRY(cudaFuncSetAttribute(fused_yee_kernel<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FY_SMEM));
+            if (dev >= 0 && dev < MPIC_MAX_DEVICES) configured[dev] = true;
+        }
+    }
+    dim3 g(ceil_div(G.nx, FY_TX), ceil_div(G.nyl, FY_TY));
+    if (ps.done) {                      // edge CTAs per side: CTA rows that read / fill slab-edge rows (see the kernel)
+        unsigned lo = 0, hi = 0;
+        for (int y0 = 0; y0 < G.nyl; y0 += FY_TY) { lo += y0 == 0; hi += y0 + FY_TY + 2 > G.nyl; }
+        ps.n_lo = lo * g.x; ps.n_hi = hi * g.x;
+    }
+    if (c.fma) {
+        if (with_j) fused_yee_kernel<1, 1><<<g, FY_THREADS, FY_SMEM, st>>>(G, *tmap, dst, jacc, c.bx, c.by, c.ex, c.ey, c.dt, ph, ps);
+        else fused_yee_kernel<1, 0><<<g, FY_THREADS, FY_SMEM, st>>>(G, *tmap, dst, jacc, c.bx, c.by, c.ex, c.ey, c.dt, ph, ps);
+    } else {
+        if (with_j) fused_yee_kernel<0, 1><<<g, FY_THREADS, FY_SMEM, st>>>(G, *tmap, dst, jacc, c.bx, c.by, c.ex, c.ey, c.dt, ph, ps);
+        else fused_yee_kernel<0, 0><<<g, FY_THREADS, FY_SMEM, st>>>(G, *tmap, dst, jacc, c.bx, c.by, c.ex, c.ey, c.dt, ph, ps);
+    }
+    LAUNCH_CHECK();
+    return 0;
+}
 int launch_wrap_guards(const FieldGeom& G, double* planes, int first, int nplanes, int do_y, cudaStream_t st) {
     if (do_y) { wrap_y_kernel<<<dim3(ceil_div(G.nx, 256), 2 * G.g), 256, 0, st>>>(G, planes, first, nplanes); LAUNCH_CHECK(); }
     wrap_x_kernel<<<ceil_div(G.rows, 128), 128, 0, st>>>(G, planes, first, nplanes);
@@ -470,7 +672,9 @@ int yee_preload() {
                          (const void*)e_sweep_kernel<0, 1>, (const void*)e_sweep_kernel<1, 0>, (const void*)e_sweep_kernel<1, 1>,
                          (const void*)wrap_y_kernel, (const void*)wrap_x_kernel, (const void*)fold_y_kernel, (const void*)fold_x_kernel,
                          (const void*)halo_pack_kernel, (const void*)halo_unpack_kernel, (const void*)tiles_kernel<0>,
-                         (const void*)tiles_kernel<1>, (const void*)field_energy_kernel, (const void*)gauss_kernel };
+                         (const void*)tiles_kernel<1>, (const void*)field_energy_kernel, (const void*)gauss_kernel,
+                         (const void*)fused_yee_kernel<0, 0>, (const void*)fused_yee_kernel<0, 1>, (const void*)fused_yee_kernel<1, 0>,
+                         (const void*)fused_yee_kernel<1, 1> };
     for (const void* f : fs) CUDA_TRY(cudaFuncGetAttributes(&a, f));
     return 0;
 }

@@ -59,6 +59,15 @@ def test_resident_loop_bit_exact_vs_reference_loop_fixture():
     for k in range(6):
         assert np.array_equal(out[k], f["out"][..., k]), k
     gids = np.arange(R * tr * C * tc, dtype=np.int32)
+    # the fused one-kernel-per-step path against the same reference fixture, guards included
+    sf = m.Sim(nx, ny, tnx, tny, float(f["dx"]), float(f["dy"]), float(f["dt"]))
+    sf.upload_planes([f["ic"][..., k] for k in range(6)])
+    sf.field_steps(steps, fused=True)
+    outf = sf.download_planes()
+    for k in range(6):
+        assert np.array_equal(outf[k], f["out"][..., k]), ("fused", k)
+    assert np.array_equal(sf.download_tiles(gids), f["tiles"])
+    sf.close()
     tiles = s.download_tiles(gids)
     assert np.array_equal(tiles, f["tiles"])
     # tile-layout upload round trip (interiors in, guards rebuilt)
@@ -99,7 +108,7 @@ def test_replay_of_shipped_dumps_bit_exact():
             assert np.array_equal(t[0], g["tile3_25"]) and np.array_equal(t[1], g["tile200_25"])
 
 
-@pytest.mark.parametrize("shape", [(64, 48, 16, 16), (50, 75, 25, 25), (36, 20, 12, 4)])
+@pytest.mark.parametrize("shape", [(64, 48, 16, 16), (50, 75, 25, 25), (36, 20, 12, 4), (200, 136, 8, 8)])
 def test_random_fields_vs_oracle(shape):
     nx, ny, tnx, tny = shape
     m = pkg(); lib = ob.load_oracle()
@@ -115,6 +124,19 @@ def test_random_fields_vs_oracle(shape):
         got = s.download_planes()
         for k in range(6):
             assert np.array_equal(got[k], want[k]), (scheme, mode, k)
+        # fused kernel (scheme 1 falls back to the sweeps); odd and even step counts exercise both plane blocks
+        for nst in (5, 6):
+            sf = m.Sim(nx, ny, tnx, tny, dx, dy, dt, scheme=scheme, fma_mode=mode)
+            sf.upload_planes(pl)
+            sf.field_steps(nst - 2, fused=True)
+            sf.field_steps(1)                      # mixing the two paths must be seamless
+            sf.field_steps(1, fused=True)
+            want = [a.copy() for a in pl]
+            ob.yee_steps(lib, want, dt, dx, dy, nst, scheme=scheme, mode=mode)
+            got = sf.download_planes()
+            for k in range(6):
+                assert np.array_equal(got[k], want[k]), ("fused", scheme, mode, nst, k)
+            sf.close()
 
 
 def test_large_grid_energy_and_linearity():
@@ -141,3 +163,27 @@ def test_large_grid_energy_and_linearity():
         s.close()
     for k in range(6):
         assert np.abs(outs[2][k] - (outs[0][k] + outs[1][k])).max() < 1e-15
+
+
+def test_fused_step_equals_three_sweeps_at_8192():
+    """configs[2] at full size: the fused kernel and the reference-faithful three sweeps agree bit for bit after 7 steps
+    (size-independent check: no oracle run needed), and the pulse energy is conserved."""
+    m = pkg()
+    n = 8192
+    dx = dy = 10.0 / n
+    dt = m.courant_dt(dx, dy)
+    x = (np.arange(n) + 0.5) * dx
+    prof = 0.1 * np.sin(np.pi * x) * np.cos((x - 3.5) / 3.0 * np.pi / 2) ** 2 * (np.abs(x - 3.5) < 3.0)
+    z = np.zeros((n, n))
+    pl = [np.tile(prof[:, None], (1, n)), np.tile(prof, (n, 1)), z, z, z, np.tile(prof, (n, 1)) - np.tile(prof[:, None], (1, n))]
+    outs = []
+    for fused in (False, True):
+        s = m.Sim(n, n, 32, 32, dx, dy, dt)
+        s.upload_planes(pl)
+        e0 = s.diagnostics()["field_energy"]
+        s.field_steps(7, fused=fused)
+        assert abs(s.diagnostics()["field_energy"] - e0) / e0 < 1e-6
+        outs.append(s.download_planes())
+        s.close()
+    for k in range(6):
+        assert np.array_equal(outs[0][k], outs[1][k]), k
