@@ -3,16 +3,21 @@
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl native|reference] [--workload NAME]
 
-Native arm: one "step" = one full PIC iteration (gather+Boris push+deposit fused with the reorder, J fold, half-B, E with
--dt*J, half-B, per-cell count/scan/permutation sort) over the synthetic workload, state resident in HBM.  N=1 workload = BASELINE.json
-configs[1] (two-stream, 512x512 cells, 64 ppc = 16.8 M particles, 0.87 GB of particle state >> 126 MB L2).  N>1: weak
-scaling, every rank owns a 512-row slab of a (512N x 512) domain (halo exchange, J reduce and particle migration over
-NCCL).  Prints ONE JSON line on rank 0.
+Native arm: one "step" = one full PIC iteration (gather+Boris push+deposit fused with the sort's reorder; half-B, E with
+-dt*J, half-B in ONE fused kernel; per-cell count/scan/permutation sort) over the synthetic workload, state resident in HBM.
+N=1 workload = BASELINE.json configs[1] (two-stream, 512x512 cells, 64 ppc = 16.8 M particles, 0.87 GB of particle state
+>> 126 MB L2), timed in the regime the 2000-step run lives in: the plasma is first advanced, untimed, into saturation.
+N>1: weak scaling, every rank owns a 512-row slab of a (512N x 512) domain (halos, J reduce and particle migration over
+NVLink peer memory).  Every line also carries the sub-records `c4_slab` (configs[3]: 4096x512 cells, 134 M particles per
+GPU -- at N=8 this IS the 1.07 B-particle config) and `yee` / `yee_8192` (configs[2], 8192^2 field-only, strong scaling).
+Prints ONE JSON line on rank 0.
 
 Reference arm (--impl reference): the reference has no particle code, so the timed CPU implementation is
-the repo's scalar FP64 oracle port with OpenMP over particles ("kind": "port"), on a bounded sample of the same workload.
+the repo's scalar FP64 oracle port with OpenMP over particles ("kind": "port") on the SAME configuration, all host cores,
+for exactly the --warmup/--steps it is given (bounded sample only when the state would not fit the host; stated).
 """
 import argparse
+import contextlib
 import importlib
 import json
 import os
@@ -29,7 +34,7 @@ PKG = "mini-pic--2d-pic-code-with-tiling-load-balance_b200"
 
 WORKLOADS = {
     # BASELINE.json configs[1]; loader parameters from SURVEY.md section 8(d) C2
-    "two_stream_512": dict(nx=512, ny=512, tn=16, ppc=64, u_th=0.001, two_stream=0.2, dx=0.1),
+    "two_stream_512": dict(nx=512, ny=512, tn=16, ppc=64, u_th=0.001, two_stream=0.2, dx=0.1, saturate_steps=1500),
     # configs[0] (the "reference default" that exists only in BASELINE.json): thermal 128^2, 16 ppc
     "thermal_128": dict(nx=128, ny=128, tn=16, ppc=16, u_th=0.05, two_stream=0.0, dx=0.1),
     # configs[3] per-GPU share at 8 GPUs
@@ -43,16 +48,19 @@ WORKLOADS = {
     # configs[4] per-GPU slab: thermal background 8 ppc + drifting beam 80 ppc in the band y in [0.45,0.55) of the GLOBAL box
     "beam_c5_slab": dict(nx=4096, ny=512, tn=16, ppc=8, u_th=0.05, two_stream=0.0, dx=0.1, beam_ppc=80, beam_band=(0.45, 0.55), beam_drift=0.5, beam_u_th=0.01),
 }
-# push_deposit_kernel is fused with the sort's data movement: it gathers every particle through the slot->storage
-# permutation and writes the other buffer in sorted order, so its algorithmic traffic is one full read + one full write
-# of the particle state: x,y,ux,uy,uz,q,tag = 52 B each way.  (SURVEY.md section 8(d) counts 88 B for an in-place push
-# PLUS 116 B for a separate reorder; the fused kernel replaces both.  `frac_88B` reports the stricter push-only figure.)
-PUSH_BYTES_PER_PARTICLE = 104.0
-PUSH_ONLY_BYTES = 88.0
-NCU_TRAFFIC_BYTES_PER_PARTICLE = 113.5   # measured: (0.964 GB read + 0.940 GB written) / 16.8 M particles, profiles/r01e_ncu_full_push_two_stream.csv
+# Algorithmic bytes.  SURVEY.md 8(d): fused gather+push+deposit reads x,y,ux,uy,uz,q (48 B) and
+# writes x,y,ux,uy,uz (40 B) = 88 B, + the per-tile grid term 2.3 B/particle at 64 ppc => 90 B/particle: `roofline.frac`.
+# The kernel here is ALSO the sort's reorder (it gathers through the slot->storage permutation and writes the other buffer
+# in sorted order): one full read + one full write of x,y,ux,uy,uz,q,tag = 104 B: `frac_104B`.
+PUSH_BYTES_SURVEY = 90.0
+PUSH_BYTES_FUSED_REORDER = 104.0
+# constant, NOT measured by the run that prints it: dram__bytes_read+write of one push launch in the saturated regime,
+# ncu --set full, profiles/r02a_ncu_full_push_saturated_raw.csv: 1.072 GB + 0.949 GB over 16 777 216 particles
+NCU_TRAFFIC_BYTES_PER_PARTICLE = 120.5
 SORT_BYTES_PER_PARTICLE = 8.0      # what is left of the sort: keys read (4) + permutation written (4); scan is per cell
 YEE_BYTES_3SWEEP = 216.0           # reference-faithful half-B, E, half-B: 3 x 72 B per cell
 YEE_BYTES_ALGO = 144.0             # SURVEY.md section 8(d) algorithmic figure (2 sweeps)
+YEE_BYTES_FUSED = 96.0             # fused step: every plane read once, written once
 
 
 def load_workload(sim, w):
@@ -70,6 +78,27 @@ def expected_particles(w, ny_global, cy_lo, cy_hi):
         lo, hi = int(round(w["beam_band"][0] * ny_global)), int(round(w["beam_band"][1] * ny_global))
         n += w["nx"] * max(0, min(hi, cy_hi) - max(lo, cy_lo)) * w["beam_ppc"]
     return n
+
+
+def workload_config(name, w, world=1):
+    """The `config` object of the JSON line.  Built by this one function for BOTH arms, so the two lines name the same
+    configuration key for key."""
+    strong = bool(w.get("strong"))
+    ny = w["ny"] if strong else w["ny"] * world
+    dx = w["dx"]
+    dt = 0.5 / np.sqrt(2.0 / (dx * dx))
+    c = {"workload": name}
+    c.update({k: (list(v) if isinstance(v, tuple) else v) for k, v in w.items()})
+    c.update({"ny_global": ny, "particles": int(expected_particles(w, ny, 0, ny)), "tile": f"{w['tn']}x{w['tn']}", "dt": float(dt)})
+    if w.get("saturate_steps"):
+        c["regime"] = (f"saturated two-stream: the GPU arm advances the plasma {w['saturate_steps']} untimed steps before the warm-up and timed "
+                       "steps; the CPU arm times the same configuration from the loader's quiet start (the scalar port's cost per "
+                       "push does not depend on the cell-crossing rate)")
+    if not w.get("fields_only"):
+        c["l2"] = "per-GPU particle state >> 126 MB L2 (no flush needed)"
+    else:
+        c["l2"] = "48 B/cell x 67 M cells = 3.2 GB >> 126 MB L2"
+    return c
 
 
 def measured_peak():
@@ -103,7 +132,9 @@ class ClockSampler:
 
     def __exit__(self, *a):
         if self.proc:
-            time.sleep(0.15)
+            t0 = time.time()
+            while len(self.rows) < 2 and time.time() - t0 < 1.5:      # a short timed region: wait for nvidia-smi's first lines
+                time.sleep(0.05)
             self.proc.terminate()
             self.t.join(timeout=2)
 
@@ -116,60 +147,50 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def cpu_port_pushes_per_s(w, steps=2, sample_cells=256, omp=True):
-    """The oracle port (OpenMP over particles, or the scalar build with omp=False) on a bounded sample: a (sample_cells x
-    sample_cells) piece of the workload."""
+# ------------------------------------------------------------------------------------------------ CPU legs
+def cpu_threads():
+    """All host cores, whatever a launcher exported (torchrun sets OMP_NUM_THREADS=1)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def cpu_port_run(w, nx, ny, steps, warmup=1, omp=True):
+    """The oracle port (scalar FP64 C, OpenMP over particles when omp) on an nx x ny piece of workload `w`: `warmup`
+    untimed + `steps` timed full PIC steps.  Returns (pushes/s, threads used, particles, seconds)."""
     from oracle import bindings as ob
     plasma = importlib.import_module(PKG + ".plasma")
     m = importlib.import_module(PKG)
     lib = ob.load_oracle(omp=omp)
-    nx = ny = min(sample_cells, w["nx"])
+    threads = 1
+    if omp:
+        lib.orc_set_threads(cpu_threads())
+        threads = int(lib.orc_num_threads())
     dx = dy = w["dx"]
     dt = m.courant_dt(dx, dy)
     P = ob.make_params(lib, nx, ny, w["tn"], w["tn"], dx, dy, dt)
     parts = plasma.load_uniform(nx, ny, w["tn"], w["tn"], dx, dy, w["ppc"], u_th=w["u_th"], two_stream=w["two_stream"])
     planes = [np.zeros((ny, nx)) for _ in range(6)]
-    ob.pic_steps(lib, P, planes, parts, 1)                      # warm-up (page faults, thread pool)
+    if warmup > 0:
+        ob.pic_steps(lib, P, planes, parts, warmup)             # page faults, thread pool
     t0 = time.perf_counter()
     ob.pic_steps(lib, P, planes, parts, steps)
     dtw = time.perf_counter() - t0
     n = parts["x"].shape[0]
-    return n * steps / dtw, (lib.orc_num_threads() if omp else 1), f"{nx}x{ny} cells x {w['ppc']} ppc = {n} particles, {steps} full PIC steps (push+deposit+Yee+sort)"
+    return n * steps / dtw, threads, n, dtw
 
 
-def run_reference(args):
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
-        return
-    w = WORKLOADS[args.workload]
-    if w.get("fields_only"):
-        # the reference's OWN field path (unmodified Field_update.cpp + pack/unpack under its loop structure), one rank
-        vals = [yee_cpu_reference(steps=10) for _ in range(max(1, min(args.steps, 3)))]
-        cb = sorted(vals, key=lambda c: c["value"])[len(vals) // 2]
-        v = cb["value"]
-        print(json.dumps({
-            "impl": "reference", "metric": "Yee cell-updates/s", "value": v, "unit": "cells/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * 1800.0 * 1800.0 / v, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": args.workload, "note": "bounded sample of the same pulse: " + cb["sample"]},
-            "cpu_baseline": cb, "e2e": {"value": v, "unit": "cells/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}))
-        return
-    vals = []
-    sample = cores = None
-    for _ in range(max(1, min(args.steps, 3))):
-        v, cores, sample = cpu_port_pushes_per_s(w, steps=2)
-        vals.append(v)
-    v = float(np.median(vals))
-    n_sample = min(256, w["nx"]) ** 2 * w["ppc"]
-    print(json.dumps({
-        "impl": "reference", "metric": "particle-pushes/s (push+deposit+sort)", "value": v, "unit": "particles/s",
-        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * n_sample / v,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": args.workload, **w, "note": "reference has no particle code; timed = repo's scalar FP64 oracle port, OpenMP over particles"},
-        "cpu_baseline": {"value": v, "unit": "particles/s", "cores": cores, "kind": "port", "sample": sample},
-        "e2e": {"value": v, "unit": "particles/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0}))
+def cpu_baseline_pic(w, cells=512, steps=3):
+    """`cpu_baseline` of the native line: bounded sample of the same workload on all host cores + a single-core figure."""
+    nx = min(cells, w["nx"])
+    ny = min(cells, w["ny"])
+    v, threads, n, sec = cpu_port_run(w, nx, ny, steps)
+    v1, _, n1, _ = cpu_port_run(w, min(128, nx), min(128, ny), 1, omp=False)
+    return {"value": v, "unit": "particles/s", "cores": threads, "kind": "port",
+            "sample": f"{nx}x{ny} cells x {w['ppc']} ppc = {n} particles, {steps} full PIC steps (push+deposit+Yee+sort) after 1 warm-up step, {sec:.1f} s",
+            "value_single_core": v1, "sample_single_core": f"{min(128, nx)}x{min(128, ny)} cells = {n1} particles, 1 step",
+            "note": "reference has no particle code (SURVEY.md F1); this is the repo's scalar FP64 oracle with OpenMP"}
 
 
 def yee_cpu_reference(n=1800, tile=25, steps=10):
@@ -200,14 +221,65 @@ def yee_cpu_reference(n=1800, tile=25, steps=10):
         # all host cores: the same reference functions, the loops over tiles run with OpenMP (oracle/ref_wrap.cpp).  NOT the
         # reference's own parallelisation (MPI ranks, unavailable here: no mpirun in the image) -- labelled as such.
         ref = ob.load_ref("libref_omp.so")
+        if hasattr(ref, "ref_set_threads"):
+            ref.ref_set_threads(cpu_threads())
         r = ob.ref_run_loop(ref, g6, 1, 1, n // tile, n // tile, 2, dt, dx, dx, steps, want_tiles=False)
         res["omp_over_tiles"] = {"value": float(n) * n * steps / r["seconds"], "cores": int(ref.ref_num_threads()),
                                  "note": "reference functions, OpenMP over tiles (not the reference's MPI decomposition)"}
     return res
 
 
+def run_reference(args):
+    """--impl reference: rank 0 alone times the CPU implementation of the path on the arm's own config; the line's
+    steps / warmup are the ones actually run."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    os.environ["OMP_NUM_THREADS"] = str(cpu_threads())          # before libgomp starts: torchrun exports OMP_NUM_THREADS=1
+    w = WORKLOADS[args.workload]
+    world = args.gpus
+    cfg = workload_config(args.workload, w, world)
+    K, W = max(1, args.steps), max(1, args.warmup)
+    if w.get("fields_only"):
+        # the reference's OWN field path (unmodified Field_update.cpp + pack/unpack under its loop structure), one rank:
+        # 17 M cell-updates/s, so the 67 M-cell config costs 4 s per step -- bounded sample of the same pulse, stated
+        cb = yee_cpu_reference(steps=min(K, 10))
+        v = cb["value"]
+        print(json.dumps({
+            "impl": "reference", "metric": "Yee cell-updates/s", "value": v, "unit": "cells/s", "n_gpus": args.gpus,
+            "steps": min(K, 10), "warmup": 0, "ms_per_step": 1e3 * 1800.0 * 1800.0 / v, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg,
+            "timed": "bounded sample of the same pulse: " + cb["sample"],
+            "cpu_baseline": cb, "e2e": {"value": v, "unit": "cells/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}))
+        return
+    nx, ny = w["nx"], cfg["ny_global"]
+    full = cfg["particles"]
+    sample = "the full configuration"
+    cap = 160_000_000                       # host image + the port's work arrays stay well inside the box's RAM
+    if full > cap:
+        ny = max(w["tn"], (cap // (w["nx"] * w["ppc"])) // w["tn"] * w["tn"])
+        sample = f"bounded sample: {nx}x{ny} cells of the {nx}x{cfg['ny_global']} domain (same ppc, same loader)"
+    if "beam_ppc" in w:
+        sample += "; background population only (the port's loader has no band option)"
+    v, threads, n, sec = cpu_port_run(w, nx, ny, K, warmup=W)
+    print(json.dumps({
+        "impl": "reference", "metric": "particle-pushes/s (push+deposit+sort)", "value": v, "unit": "particles/s",
+        "n_gpus": args.gpus, "steps": K, "warmup": W, "ms_per_step": 1e3 * sec / K,
+        "higher_is_better": True, "scaling": "strong" if w.get("strong") else "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": cfg,
+        "timed": f"{sample}: {n} particles, {W} warm-up + {K} timed full PIC steps from the loader's quiet start, {threads} threads",
+        "note": "reference has no particle code (SURVEY.md F1); timed = the repo's scalar FP64 oracle port, OpenMP over particles",
+        "cpu_baseline": {"value": v, "unit": "particles/s", "cores": threads, "kind": "port",
+                         "sample": f"{sample}: {nx}x{ny} cells x {w['ppc']} ppc = {n} particles, {K} full PIC steps, {sec:.1f} s"},
+        "e2e": {"value": v, "unit": "particles/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+# ------------------------------------------------------------------------------------------------ native, one GPU
 def yee_bench(m, torch, steps, warmup, n=8192):
-    """Field-only sub-benchmark (BASELINE.json configs[2]): n x n vacuum pulse, reference-faithful 3-sweep loop."""
+    """Field-only sub-benchmark (BASELINE.json configs[2]): n x n vacuum pulse.  `value` = the fused one-kernel step
+    (bit-identical to the reference-faithful three sweeps, which are timed beside it)."""
     dx = dy = 10.0 / n
     sim = m.Sim(n, n, 32, 32, dx, dy, m.courant_dt(dx, dy))
     x = (np.arange(n) + 0.5) * dx
@@ -215,28 +287,130 @@ def yee_bench(m, torch, steps, warmup, n=8192):
     z = np.zeros((n, n))
     sim.upload_planes([z, np.tile(prof, (n, 1)), z, z, z, np.tile(prof, (n, 1))])
     st = torch.cuda.ExternalStream(sim.stream)
-    sim.field_steps(warmup)
-    sim.sync()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    l0 = sim.kernel_launches
-    e0.record(st)
-    sim.field_steps(steps)
-    e1.record(st)
-    sim.sync()
-    ms = e0.elapsed_time(e1)
+    res = {}
+    for fused in (False, True):
+        sim.field_steps(warmup, fused=fused)
+        sim.sync()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = sim.kernel_launches
+        e0.record(st)
+        sim.field_steps(steps, fused=fused)
+        e1.record(st)
+        sim.sync()
+        res[fused] = (e0.elapsed_time(e1), sim.kernel_launches - l0)
+    ms, launches = res[True]
+    ms3 = res[False][0]
     cells = float(n) * n * steps
     peak, how = measured_peak()
+    gbs = cells * YEE_BYTES_FUSED / (ms * 1e-3) / 1e9
     out = {"metric": "Yee cell-updates/s", "value": cells / (ms * 1e-3), "unit": "cells/s", "ms_per_step": ms / steps,
-           "config": {"workload": f"vacuum pulse {n}x{n}, half-B/E/half-B per step", "fields_bytes": 48 * n * n},
-           "gpu_launches": sim.kernel_launches - l0,
-           "roofline": {"bound": "hbm", "achieved": cells * YEE_BYTES_3SWEEP / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
-                        "frac": cells * YEE_BYTES_3SWEEP / (ms * 1e-3) / 1e9 / peak,
-                        "traffic": (3.225 + 1.568 + 3.225 + 1.572 + 3.225 + 1.568) * 1e9 * (float(n) * n / 8192.0 ** 2),
-                        "traffic_source": "ncu --set full dram__bytes_read+write of b_sweep / e_sweep at 8192^2 (profiles/r01e_ncu_full_yee_8192.csv), three sweeps per step: 14.38 GB vs 14.50 GB algorithmic",
-                        "bytes_per_cell_update": YEE_BYTES_3SWEEP,
-                        "frac_of_144B_figure": cells * YEE_BYTES_ALGO / (ms * 1e-3) / 1e9 / peak, "peak_source": how}}
+           "config": {"workload": f"vacuum pulse {n}x{n}, half-B/E/half-B per step in one fused kernel", "fields_bytes": 48 * n * n},
+           "gpu_launches": launches,
+           "roofline": {"bound": "hbm", "kernel": "fused_yee_kernel", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
+                        "traffic": None, "bytes_per_cell_update": YEE_BYTES_FUSED,
+                        "frac_of_144B_figure": cells * YEE_BYTES_ALGO / (ms * 1e-3) / 1e9 / peak, "peak_source": how,
+                        "note": "96 B/cell: six planes read once + written once (halo ring re-reads are served by L2); SURVEY's 144 B "
+                                "figure assumes two sweeps, so its fraction exceeds 1"},
+           "three_sweeps": {"ms_per_step": ms3 / steps, "value": cells / (ms3 * 1e-3), "bytes_per_cell_update": YEE_BYTES_3SWEEP,
+                            "frac": cells * YEE_BYTES_3SWEEP / (ms3 * 1e-3) / 1e9 / peak,
+                            "frac_of_144B_figure": cells * YEE_BYTES_ALGO / (ms3 * 1e-3) / 1e9 / peak}}
     sim.close()
     return out
+
+
+def time_pic(sim, torch, K, W):
+    """W warm-up + K timed PIC steps on a single-slab handle, per-phase CUDA events on the library's stream."""
+    st = torch.cuda.ExternalStream(sim.stream)
+
+    def step(evs=None):
+        if evs:
+            evs[0].record(st)
+        sim.push_deposit()
+        if evs:
+            evs[1].record(st)
+        sim.step_fields_fused()            # half-B, E - dt*J (J guard ring folded on the fly), half-B: one kernel
+        if evs:
+            evs[2].record(st)
+        sim.sort_tiles()
+        if evs:
+            evs[3].record(st)
+
+    for _ in range(W):
+        step()
+    sim.sync()
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(K)]
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0 = sim.kernel_launches
+    torch.cuda.synchronize()
+    t0.record(st)
+    for k in range(K):
+        step(evs[k])
+    t1.record(st)
+    sim.sync()
+    torch.cuda.synchronize()
+    f = lambda a, b: float(np.mean([e[a].elapsed_time(e[b]) for e in evs]))
+    # cell-crossing fraction of the regime: one more push, counted before its sort
+    sim.push_deposit()
+    movers = sim.cell_crossers()
+    sim.step_fields_fused()
+    sim.sort_tiles()
+    sim.sync()
+    return {"ms": t0.elapsed_time(t1), "push_ms": f(0, 1), "fields_ms": f(1, 2), "sort_ms": f(2, 3),
+            "launches": int(sim.kernel_launches - l0), "movers": movers}
+
+
+def push_roofline(n, t, peak, peak_how):
+    gbs = n * PUSH_BYTES_SURVEY / (t["push_ms"] * 1e-3) / 1e9
+    return {"bound": "hbm", "kernel": "push_deposit_kernel", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
+            "bytes_per_particle": PUSH_BYTES_SURVEY,
+            "frac_104B": gbs / peak * PUSH_BYTES_FUSED_REORDER / PUSH_BYTES_SURVEY,
+            "traffic": NCU_TRAFFIC_BYTES_PER_PARTICLE * n,
+            "traffic_source": "CONSTANT from one ncu --set full capture of this kernel in the saturated regime (profiles/r02a_ncu_full_push_saturated_raw.csv: "
+                              "120.5 B/particle), scaled by the particle count; not measured by this run",
+            "pushes_per_s_kernel_only": n / (t["push_ms"] * 1e-3), "peak_source": peak_how,
+            "sort_gbs": n * SORT_BYTES_PER_PARTICLE / (t["sort_ms"] * 1e-3) / 1e9,
+            "note": "frac: SURVEY.md 8(d)'s 88 B push + 2.3 B grid = 90 B/particle.  frac_104B: what this kernel must move, since it is also the "
+                    "sort's reorder (52 B read + 52 B written per particle); the sort that remains (scan + permutation build) moves 8 B/particle"}
+
+
+def pic_record(m, torch, name, w, K, W, local, peak, peak_how, clocks=True, keep=False):
+    """Load workload `w` on one GPU, advance it into its regime, time K steps.  Returns (record, sim or None)."""
+    nx, ny, tn = w["nx"], w["ny"], w["tn"]
+    dx = dy = w["dx"]
+    dt = m.courant_dt(dx, dy)
+    n = expected_particles(w, ny, 0, ny)
+    sim = m.Sim(nx, ny, tn, tn, dx, dy, dt, max_particles=n + 1024, device=local)
+    load_workload(sim, w)
+    sim.sync()
+    assert sim.num_particles == n
+    sat = int(w.get("saturate_steps", 0))
+    with (ClockSampler(local) if clocks else contextlib.nullcontext()) as clk:      # sampled over the untimed run-in too (same kernels, same load)
+        if sat:
+            sim.pic_steps(sat)
+            sim.sync()
+        t = time_pic(sim, torch, K, W)
+    diag = sim.diagnostics()
+    rec = {"metric": "particle-pushes/s (push+deposit+sort)", "value": n * K / (t["ms"] * 1e-3), "unit": "particles/s",
+           "ms_per_step": t["ms"] / K, "particles": n,
+           "regime": (f"saturated: timed after {sat} untimed steps + {W} warm-up steps" if sat else f"thermal u_th={w['u_th']}: timed after {W} warm-up steps"),
+           "cell_crossing_fraction": t["movers"] / float(n),
+           "phases_ms": {"push_deposit": t["push_ms"], "fields_fused": t["fields_ms"], "sort": t["sort_ms"]},
+           "roofline": push_roofline(n, t, peak, peak_how), "gpu_launches": t["launches"],
+           "diagnostics_after": {k: float(v) for k, v in diag.items()}}
+    if clocks:
+        rec["clocks"] = clk.summary()
+    # self-check: nothing lost, charge conserved, Gauss's law at round-off (charge-conserving deposit)
+    q0 = -1.0 * dx * dy / w["ppc"] * n if "beam_ppc" not in w else diag["charge"]
+    ok = diag["particles"] == n and abs(diag["charge"] - q0) <= 1e-9 * abs(q0) and diag["gauss_residual"] < 1e-9
+    rec["self_check"] = {"ok": bool(ok), "particles": diag["particles"], "charge_error": float(diag["charge"] - q0),
+                         "gauss_residual": float(diag["gauss_residual"])}
+    if not ok:
+        print(f"bench.py: self-check FAILED for {name}: {rec['self_check']}", file=sys.stderr)
+        sys.exit(3)
+    if keep:
+        return rec, sim
+    sim.close()
+    return rec, None
 
 
 def main():
@@ -249,6 +423,7 @@ def main():
     ap.add_argument("--no-yee", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-sub", action="store_true", help="skip the c4_slab / quiet-start sub-records")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -267,86 +442,29 @@ def main():
 
     if world > 1:
         dist = importlib.import_module(PKG + ".slab")
-        if w.get("fields_only"):
-            return dist.bench_fields(args, w, rank, world, local, peak, peak_how)
-        return dist.bench_main(args, w, rank, world, local, peak, peak_how)
+        return dist.bench_multi(args, w, rank, world, local, peak, peak_how)
     if w.get("fields_only"):
         with ClockSampler(local) as clk:
             y = yee_bench(m, torch, K, W, n=w["nx"])
         out = {"metric": y["metric"], "value": y["value"], "unit": y["unit"], "n_gpus": 1, "steps": K, "warmup": W,
                "ms_per_step": y["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
-               "data": "synthetic", "config": {"workload": args.workload, **y["config"], "l2": "48 B/cell x 67 M cells = 3.2 GB >> 126 MB L2"},
-               "roofline": y["roofline"], "gpu_launches": y["gpu_launches"], "clocks": clk.summary()}
+               "data": "synthetic", "config": workload_config(args.workload, w), "roofline": y["roofline"], "three_sweeps": y["three_sweeps"],
+               "gpu_launches": y["gpu_launches"], "clocks": clk.summary()}
         if not args.no_cpu:
             out["cpu_baseline"] = yee_cpu_reference()
         print(json.dumps(out))
         return
 
-    nx, ny, tn, ppc = w["nx"], w["ny"], w["tn"], w["ppc"]
-    dx = dy = w["dx"]
-    dt = m.courant_dt(dx, dy)
-    n = expected_particles(w, ny, 0, ny)
-    sim = m.Sim(nx, ny, tn, tn, dx, dy, dt, max_particles=n + 1024, device=local)
-    load_workload(sim, w)
-    sim.sync()
-    assert sim.num_particles == n
-    st = torch.cuda.ExternalStream(sim.stream)
-
-    def step(evs=None):
-        if evs:
-            evs[0].record(st)
-        sim.push_deposit()
-        if evs:
-            evs[1].record(st)
-        sim.step_b_half()                 # (the E sweep folds the J guard ring on the fly)
-        sim.step_e_full()
-        sim.step_b_half()
-        if evs:
-            evs[2].record(st)
-        sim.sort_tiles()
-        if evs:
-            evs[3].record(st)
-
-    for _ in range(W):
-        step()
-    sim.sync()
-    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(K)]
-    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    l0 = sim.kernel_launches
-    with ClockSampler(local) as clk:
-        torch.cuda.synchronize()
-        t0.record(st)
-        for k in range(K):
-            step(evs[k])
-        t1.record(st)
-        sim.sync()
-        torch.cuda.synchronize()
-    ms = t0.elapsed_time(t1)
-    launches = sim.kernel_launches - l0
-    push_ms = float(np.mean([e[0].elapsed_time(e[1]) for e in evs]))
-    field_ms = float(np.mean([e[1].elapsed_time(e[2]) for e in evs]))
-    sort_ms = float(np.mean([e[2].elapsed_time(e[3]) for e in evs]))
-    value = n * K / (ms * 1e-3)
-    push_gbs = n * PUSH_BYTES_PER_PARTICLE / (push_ms * 1e-3) / 1e9
-    diag = sim.diagnostics()
-
+    nx, ny = w["nx"], w["ny"]
+    rec, sim = pic_record(m, torch, args.workload, w, K, W, local, peak, peak_how, keep=True)
+    n = rec["particles"]
     out = {
-        "metric": "particle-pushes/s (push+deposit+sort)", "value": value, "unit": "particles/s", "n_gpus": 1, "steps": K,
-        "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong" if w.get("strong") else "weak", "vs_baseline": None, "dtype": "f64",
-        "data": "synthetic",
-        "config": {"workload": args.workload, **w, "particles": n, "tile": f"{tn}x{tn}", "dt": dt,
-                   "regime": f"steps {W + 1}..{W + K} after the loader's quiet start (the whole 2000-step run of configs[1] averages 0.649 ms/step: DESIGN.md section 7.0)",
-                   "l2": f"particle state {n * 52 / 1e9:.2f} GB per pass >> 126 MB L2 (no flush needed)"},
-        "phases_ms": {"push_deposit": push_ms, "fields_and_fold": field_ms, "sort": sort_ms},
-        "roofline": {"bound": "hbm", "kernel": "push_deposit_kernel", "achieved": push_gbs, "peak": peak, "unit": "GB/s",
-                     "frac": push_gbs / peak, "traffic": NCU_TRAFFIC_BYTES_PER_PARTICLE * n, "bytes_per_particle": PUSH_BYTES_PER_PARTICLE,
-                     "frac_88B": push_gbs / peak * PUSH_ONLY_BYTES / PUSH_BYTES_PER_PARTICLE,
-                     "traffic_source": "ncu --set full dram__bytes_read+write of one launch, profiles/r01e_ncu_full_push_two_stream.csv (113.5 B/particle)",
-                     "pushes_per_s_kernel_only": n / (push_ms * 1e-3), "peak_source": peak_how,
-                     "sort_gbs": n * SORT_BYTES_PER_PARTICLE / (sort_ms * 1e-3) / 1e9,
-                     "note": "fused gather+push+deposit+reorder: 52 B read + 52 B written per particle; the sort that remains (scan + permutation build) moves 8 B/particle"},
-        "gpu_launches": int(launches), "clocks": clk.summary(),
-        "diagnostics_after": {k: float(v) for k, v in diag.items()},
+        "metric": rec["metric"], "value": rec["value"], "unit": rec["unit"], "n_gpus": 1, "steps": K,
+        "warmup": W, "ms_per_step": rec["ms_per_step"], "higher_is_better": True, "scaling": "strong" if w.get("strong") else "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(args.workload, w),
+        "regime": rec["regime"], "cell_crossing_fraction": rec["cell_crossing_fraction"],
+        "phases_ms": rec["phases_ms"], "roofline": rec["roofline"], "gpu_launches": rec["gpu_launches"], "clocks": rec["clocks"],
+        "diagnostics_after": rec["diagnostics_after"], "self_check": rec["self_check"],
     }
 
     if n * 52 > 16e9 and not args.no_e2e:
@@ -357,13 +475,10 @@ def main():
         host = {k: torch.empty(n, dtype=torch.float64).pin_memory() for k in m.PART_KEYS}
         host["tag"] = torch.empty(n, dtype=torch.int32).pin_memory()
         parts = {k: v.numpy() for k, v in host.items()}
-        cur = sim.download_particles()
-        for k in parts:
-            parts[k][:] = cur[k]
+        sim.download_particles(out=parts)
         hpl = [torch.empty((ny, nx), dtype=torch.float64).pin_memory() for _ in range(6)]
         planes = [t.numpy() for t in hpl]
-        for a, b in zip(planes, sim.download_planes()):
-            a[:] = b
+        sim.download_planes(out=planes)
         ke = max(2, min(K, 5))
         sim.pic_steps_host(1, planes, parts)
         torch.cuda.synchronize()
@@ -375,8 +490,19 @@ def main():
         nbytes = 6 * nx * ny * 8 + n * 52
         out["e2e"] = {"value": n * ke / tw, "unit": "particles/s", "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nbytes,
                       "steps": ke, "ms_per_step": 1e3 * tw / ke,
-                      "api": "mpic_pic_steps_host: pinned host fields+particles -> device, 1 PIC step, full state back"}
+                      "api": "mpic_pic_steps_host: pinned host fields+particles -> device, 1 PIC step, full state back (chunked, both PCIe directions overlapped with the compute)"}
     sim.close()
+    if not args.no_sub and args.workload == "two_stream_512":
+        # secondary figures: the loader's quiet start (round 1's headline regime) and the per-GPU share of configs[3]
+        wq = dict(w)
+        wq.pop("saturate_steps")
+        q, _ = pic_record(m, torch, "two_stream_512 (quiet start)", wq, K, W, local, peak, peak_how, clocks=False)
+        q["regime"] = f"quiet start: steps {W + 1}..{W + K} after the loader (almost no particle changes cell)"
+        out["quiet_start"] = {k: q[k] for k in ("value", "ms_per_step", "regime", "cell_crossing_fraction", "phases_ms", "roofline")}
+        c4, _ = pic_record(m, torch, "uniform_c4_slab", WORKLOADS["uniform_c4_slab"], K, W, local, peak, peak_how)
+        c4["config"] = workload_config("uniform_c4_slab", WORKLOADS["uniform_c4_slab"])
+        c4["scaling"] = "weak"
+        out["c4_slab"] = c4
     if not args.no_yee:
         out["yee"] = yee_bench(m, torch, max(K, 10), W)
     if not args.no_cpu:
@@ -387,11 +513,7 @@ def main():
                 cb = {"unavailable": repr(e)}
             if cb:
                 out["yee"]["cpu_baseline"] = cb
-        v, cores, sample = cpu_port_pushes_per_s(w, steps=2)
-        v1, _, sample1 = cpu_port_pushes_per_s(w, steps=1, sample_cells=128, omp=False)
-        out["cpu_baseline"] = {"value": v, "unit": "particles/s", "cores": cores, "kind": "port", "sample": sample,
-                               "value_single_core": v1, "sample_single_core": sample1,
-                               "note": "reference has no particle code (SURVEY.md F1); this is the repo's scalar FP64 oracle with OpenMP"}
+        out["cpu_baseline"] = cpu_baseline_pic(w)
     print(json.dumps(out))
 
 

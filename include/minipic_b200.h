@@ -144,6 +144,7 @@ typedef struct mpic_migr_desc {
 int mpic_migration_describe(mpic_sim* s, mpic_migr_desc* out);
 int mpic_migration_counts(mpic_sim* s, int leave[2], int arrive[2]);
 int mpic_migration_absorb(mpic_sim* s, int n_from_lo, int n_from_hi);
+int64_t mpic_migrated_total(mpic_sim* s);   /* harness: records this slab has handed to its neighbours so far */
 
 /* ---- peer-memory slab ring (nranks > 1; replaces, on the step path, the pack / transfer / unpack protocol above and
  * with it the reference's exchange phases PIC_2D.cpp:200-248,276-319,348-396 and MPI_Barriers :200,226,...).
@@ -171,6 +172,11 @@ int mpic_peer_field_step_fused(mpic_sim* s);
 int mpic_peer_step_begin(mpic_sim* s);      /* push+deposit, hand-off, J add, Yee phases: everything enqueued, no host wait */
 int mpic_peer_step_end(mpic_sim* s);        /* migration counts (the one host wait), arrivals absorbed, tile sort */
 
+/* Harness: per-phase device times of mpic_peer_step_begin/_end (events on the handle's stream; adds a host wait per step).
+ * enable 1 = start/reset, 0 = stop, -1 = read only.  out_ms[11] = mean ms of {wait for the neighbours' last phase, push+deposit,
+ * hand-off, -, -, first half-B, -, E, -, second half-B, migration counts + absorb + tile sort}. */
+int mpic_peer_trace(mpic_sim* s, int enable, double* out_ms, long long* steps);
+
 /* ---- particles (struct Particle, Auxiliar_functions.h:16-21, as SoA: x,y,px,py,pz,q doubles and int tag).
  * Upload accepts any order; the device sorts by (tile gid, cell) before the first push. */
 int mpic_upload_particles(mpic_sim* s, int64_t n, const double* x, const double* y, const double* ux, const double* uy,
@@ -194,11 +200,17 @@ int mpic_pic_steps(mpic_sim* s, int nsteps);
 /* tile occupancy (local tiles, gid order within the slab) and per-particle tile gid in current slot order */
 int mpic_get_tile_counts(mpic_sim* s, int* counts);
 int mpic_get_particle_tile_index(mpic_sim* s, int* gid_of_particle);
+/* Diagnostic: number of particles that changed CELL in the last push (slab leavers included).  Valid between
+ * mpic_push_deposit and mpic_sort_tiles.  bench.py reports it as the regime's cell-crossing fraction. */
+int mpic_cell_crossers(mpic_sim* s, int64_t* n_out);
 /* J accumulators of the last push as int64 fixed point (value * 2^52), three (nyl,nx) planes */
 int mpic_download_current(mpic_sim* s, int64_t* const jplanes[3]);
 /* out[0] field energy 1/2 sum dx dy (E^2+B^2) over the slab; out[1] kinetic energy sum m_p (gamma-1);
  * out[2] max |div E - rho + <rho>| (Gauss residual); out[3] total charge; out[4] number of particles */
 int mpic_diagnostics(mpic_sim* s, double out[5]);
+/* max |div E - rho + mean_rho| over this slab with the caller's (GLOBAL) mean charge density: the multi-slab form of out[2]
+ * (a slab's first cell row is skipped: its node charge needs the lower neighbour's particles). */
+int mpic_gauss_residual(mpic_sim* s, double mean_rho, double* out);
 
 /* ---- tile ownership (owner[] map, PIC_2D.cpp:55,144-148; removeTileFromRank/addTileToRank, Auxiliar_functions.cpp:242-272).
  * On one GPU ownership is bookkeeping only (fields never change); it drives currentRank in the dumps. */

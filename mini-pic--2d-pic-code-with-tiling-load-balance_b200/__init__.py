@@ -77,9 +77,11 @@ def lib():
     L.mpic_download_particles.argtypes = [C.c_void_p, C.c_int64] + [c_dp] * 6 + [c_ip, c_lp]
     L.mpic_load_uniform.argtypes = [C.c_void_p, C.c_int] + [C.c_double] * 8 + [C.c_uint64, C.c_int]
     L.mpic_get_tile_counts.argtypes = [C.c_void_p, c_ip]
+    L.mpic_cell_crossers.argtypes = [C.c_void_p, c_lp]
     L.mpic_get_particle_tile_index.argtypes = [C.c_void_p, c_ip]
     L.mpic_download_current.argtypes = [C.c_void_p, C.POINTER(c_lp)]
     L.mpic_diagnostics.argtypes = [C.c_void_p, c_dp]
+    L.mpic_gauss_residual.argtypes = [C.c_void_p, C.c_double, c_dp]
     L.mpic_get_owner.argtypes = [C.c_void_p, c_ip]
     L.mpic_migrate_tile.argtypes = [C.c_void_p, C.c_int, C.c_int]
     L.mpic_pic_steps_host.argtypes = [C.c_void_p, C.c_int, C.POINTER(c_dp), C.c_int64] + [c_dp] * 6 + [c_ip, c_lp]
@@ -103,6 +105,9 @@ def lib():
     for name in ("mpic_peer_refresh_begin", "mpic_peer_refresh_end", "mpic_peer_field_step", "mpic_peer_step_begin",
                  "mpic_peer_step_end"):
         getattr(L, name).argtypes = [C.c_void_p]
+    L.mpic_peer_trace.argtypes = [C.c_void_p, C.c_int, c_dp, c_lp]
+    L.mpic_migrated_total.restype = C.c_int64
+    L.mpic_migrated_total.argtypes = [C.c_void_p]
     _lib = L
     return L
 
@@ -217,6 +222,12 @@ class Sim:
         """n iterations of half-B / E / half-B (PIC_2D.cpp:171-396).  fused=True: one kernel per step (bit-identical)."""
         _chk((lib().mpic_field_steps_fused if fused else lib().mpic_field_steps)(self.h, n))
 
+    def cell_crossers(self):
+        """Particles that changed cell in the last push (call between push_deposit and sort_tiles)."""
+        n = C.c_int64()
+        _chk(lib().mpic_cell_crossers(self.h, C.byref(n)))
+        return int(n.value)
+
     def step_fields_fused(self):
         """Phases A..F of one step in ONE kernel, with the -dt*J term when particles are present (single slab)."""
         _chk(lib().mpic_step_fields_fused(self.h))
@@ -249,6 +260,10 @@ class Sim:
         _chk(lib().mpic_migration_counts(self.h, lv, ar))
         return [lv[0], lv[1]], [ar[0], ar[1]]
 
+    @property
+    def migrated_total(self):
+        return int(lib().mpic_migrated_total(self.h))
+
     def migration_absorb(self, n_from_lo, n_from_hi):
         _chk(lib().mpic_migration_absorb(self.h, n_from_lo, n_from_hi))
 
@@ -267,6 +282,14 @@ class Sim:
 
     def peer_refresh_end(self):
         _chk(lib().mpic_peer_refresh_end(self.h))
+
+    def peer_trace(self, enable=-1):
+        """Per-phase mean ms of the peer PIC step since the last reset (enable=1 starts/resets, 0 stops, -1 only reads)."""
+        out = np.zeros(11)
+        n = C.c_int64()
+        _chk(lib().mpic_peer_trace(self.h, enable, _dp(out), C.byref(n)))
+        names = ("wait_prev", "push_deposit", "handoff", "_3", "_4", "b_half_1", "_6", "e_full", "_8", "b_half_2", "counts_absorb_sort")
+        return {k: float(v) for k, v in zip(names, out) if not k.startswith("_")}, int(n.value)
 
     def peer_field_step(self, fused=False):
         _chk((lib().mpic_peer_field_step_fused if fused else lib().mpic_peer_field_step)(self.h))
@@ -354,6 +377,12 @@ class Sim:
         _chk(lib().mpic_diagnostics(self.h, _dp(out)))
         return {"field_energy": out[0], "kinetic_energy": out[1], "gauss_residual": out[2], "charge": out[3],
                 "particles": int(out[4])}
+
+    def gauss_residual(self, mean_rho):
+        """max |div E - rho + mean_rho| over this slab, mean_rho = GLOBAL mean charge density (multi-slab Gauss check)."""
+        out = C.c_double()
+        _chk(lib().mpic_gauss_residual(self.h, float(mean_rho), C.byref(out)))
+        return float(out.value)
 
     def dump_fields(self, filename, rank=-1):
         """Phase H: fields_rank_<r>_step_<s>.h5 in the reference layout (HDF5_output.cpp:10-79)."""

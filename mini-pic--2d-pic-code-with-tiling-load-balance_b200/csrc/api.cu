@@ -172,6 +172,9 @@ int mpic_create(const mpic_params* p, mpic_sim** out) {
             "nx, ny must be positive multiples of the tile size (the reference silently drops cells otherwise, PIC_2D.cpp:67-68)");
     REQUIRE(p->tnx >= 2 * p->guard && p->tny >= 2 * p->guard, MPIC_EINVAL, "tile interior must be >= 2*guard cells");
     REQUIRE(p->dx > 0 && p->dy > 0 && p->dt > 0, MPIC_EINVAL, "dx, dy, dt must be positive");
+    // the push (and its shared-memory count / current patches) assumes a particle moves less than one cell per step: |v| < c = 1
+    REQUIRE(p->max_particles == 0 || (p->dt <= p->dx && p->dt <= p->dy), MPIC_EINVAL,
+            "dt = %g exceeds min(dx, dy) = %g: a particle could cross more than one cell per step", p->dt, p->dx < p->dy ? p->dx : p->dy);
     REQUIRE(p->nranks >= 1 && p->rank >= 0 && p->rank < p->nranks, MPIC_EINVAL, "bad rank/nranks");
     const int gtr = p->ny / p->tny, gtc = p->nx / p->tnx;
     REQUIRE(p->row0 >= 0 && p->nrows >= 1 && p->row0 + p->nrows <= gtr, MPIC_EINVAL, "bad slab rows");
@@ -207,7 +210,9 @@ int mpic_create(const mpic_params* p, mpic_sim** out) {
     CUDA_TRY(cudaMemsetAsync(s->planes, 0, (size_t)6 * G.plane * 8, s->st));
     CUDA_TRY(cudaMalloc(&s->jacc, (size_t)3 * G.plane * 8));
     CUDA_TRY(cudaMemsetAsync(s->jacc, 0, (size_t)3 * G.plane * 8, s->st));
-    CUDA_TRY(cudaMalloc(&s->d_scratch, 64));
+    CUDA_TRY(cudaMalloc(&s->d_scratch, 64 + 8));
+    G.err = (unsigned int*)(s->d_scratch + 8);            // the handle's device error word
+    CUDA_TRY(cudaMemsetAsync(s->d_scratch, 0, 64 + 8, s->st));
     s->cap = p->max_particles;
     if (s->cap > 0) {
         TRY(alloc_particles(&s->pa[0], s->cap));
@@ -282,8 +287,20 @@ int mpic_destroy(mpic_sim* s) {
     delete s;
     return 0;
 }
+// device error word -> status (and reset).  Called wherever the host waits for the stream anyway.
+static int check_error_word(mpic_sim* s) {
+    unsigned int w = 0;
+    CUDA_TRY(cudaMemcpyAsync(&w, s->G.err, 4, cudaMemcpyDeviceToHost, s->st));
+    CUDA_TRY(cudaStreamSynchronize(s->st));
+    if (!w) return 0;
+    CUDA_TRY(cudaMemsetAsync(s->G.err, 0, 4, s->st));
+    REQUIRE(!(w & MPIC_ERR_POSITION), MPIC_EINVAL, "a particle position is outside [0,box_x) x [0,box_y) or not finite (binned into cell 0)");
+    REQUIRE(!(w & MPIC_ERR_JRANGE), MPIC_EINVAL, "current accumulator out of range: |J| >= 1024 in code units exceeds the int64 fixed point (value * 2^52)");
+    return 0;
+}
 int mpic_sync(mpic_sim* s) {
     if (s) cudaSetDevice(s->prm.device); REQUIRE(s, MPIC_EINVAL, "null handle"); CUDA_TRY(cudaStreamSynchronize(s->st));
+    TRY(check_error_word(s));
     if (s->peer_on) return mpic_peer_refresh_end(s);     // surfaces a timed-out neighbour wait
     return 0; }
 void* mpic_stream(mpic_sim* s) { return s ? (void*)s->st : nullptr; }
@@ -502,8 +519,10 @@ int mpic_migration_counts(mpic_sim* s, int leave[2], int arrive[2]) {
                 leave[d], arrive[d], s->lv.cap);
     }
     s->left = (int64_t)leave[0] + leave[1];
+    s->migrated_total += s->left;
     return 0;
 }
+int64_t mpic_migrated_total(mpic_sim* s) { return s ? s->migrated_total : 0; }
 int mpic_migration_absorb(mpic_sim* s, int n_from_lo, int n_from_hi) {
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && n_from_lo >= 0 && n_from_hi >= 0, MPIC_EINVAL, "bad argument");
@@ -511,9 +530,9 @@ int mpic_migration_absorb(mpic_sim* s, int n_from_lo, int n_from_hi) {
     REQUIRE(s->n + s->arrived + n_from_lo + n_from_hi <= s->cap, MPIC_ENOMEM, "particle capacity exceeded by arrivals");
     REQUIRE(s->counts_valid, MPIC_ESTATE, "mpic_migration_absorb must follow mpic_push_deposit");
     // arrivals are appended in (source rank order: lower, upper; source order) -- SURVEY.md B.8
-    TRY(launch_absorb(s->P, s->pa[s->cur], s->n + s->arrived, s->arrive[0], n_from_lo, s->cell_count, s->keys, s->st));
+    TRY(launch_absorb(s->P, s->pa[s->cur], s->n + s->arrived, s->arrive[0], n_from_lo, s->cell_count, s->keys, s->G.err, s->st));
     s->arrived += n_from_lo;
-    TRY(launch_absorb(s->P, s->pa[s->cur], s->n + s->arrived, s->arrive[1], n_from_hi, s->cell_count, s->keys, s->st));
+    TRY(launch_absorb(s->P, s->pa[s->cur], s->n + s->arrived, s->arrive[1], n_from_hi, s->cell_count, s->keys, s->G.err, s->st));
     s->arrived += n_from_hi;
     s->launches += (n_from_lo > 0) + (n_from_hi > 0);
     return 0;
@@ -539,7 +558,7 @@ static int sort_all(mpic_sim* s, bool counted) {
         if (s->perm_valid && s->arrived == 0) return 0;          // already sorted, nothing new
         TRY(materialise(s));
         CUDA_TRY(cudaMemsetAsync(s->cell_count, 0, (size_t)s->n_entries * 4, s->st));
-        TRY(launch_count_keys(s->P, s->pa[s->cur], 0, s->n + s->arrived, s->cell_count, nullptr, s->st));
+        TRY(launch_count_keys(s->P, s->pa[s->cur], 0, s->n + s->arrived, s->cell_count, s->G.err, s->st));
         s->launches++;
     }
     const int64_t total = s->n + s->arrived;
@@ -568,6 +587,7 @@ int mpic_upload_particles(mpic_sim* s, int64_t n, const double* x, const double*
                           const double* uz, const double* q, const int* tag) {
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && n >= 0, MPIC_EINVAL, "bad argument");
+    REQUIRE(n == 0 || (x && y && ux && uy && uz && q && tag), MPIC_EINVAL, "mpic_upload_particles: null particle array");
     REQUIRE(n <= s->cap, MPIC_ENOMEM, "particle capacity %lld exceeded (%lld)", (long long)s->cap, (long long)n);
     s->perm_valid = false; s->counts_valid = false; s->arrived = 0;
     Particles& p = s->pa[s->cur];
@@ -577,7 +597,7 @@ int mpic_upload_particles(mpic_sim* s, int64_t n, const double* x, const double*
     CUDA_TRY(cudaMemcpyAsync(p.tag, tag, (size_t)n * 4, cudaMemcpyHostToDevice, s->st));
     s->n = n;
     TRY(sort_all(s, false));
-    return 0;
+    return check_error_word(s);        // positions outside the box are reported here, not at some later launch
 }
 int mpic_download_particles(mpic_sim* s, int64_t cap, double* x, double* y, double* ux, double* uy, double* uz, double* q,
                             int* tag, int64_t* n_out) {
@@ -722,7 +742,7 @@ static int pic_step_host_pipelined(mpic_sim* s, double* const planes[6], int64_t
         CUDA_TRY(cudaStreamWaitEvent(s->st, s->pipe_ev_up[c], 0));
         CUDA_TRY(cudaMemsetAsync(s->pipe_count, 0, (size_t)s->n_entries * 4, s->st));
         const Particles Ac = offset_particles(A, lo), Bc = offset_particles(B, lo);
-        TRY(launch_count_keys(s->P, Ac, 0, m, s->pipe_count, nullptr, s->st));
+        TRY(launch_count_keys(s->P, Ac, 0, m, s->pipe_count, s->G.err, s->st));
         TRY(launch_scan_cells(s->pipe_count, s->pipe_start, s->n_entries, s->scan_tmp, s->st));
         TRY(launch_scatter(s->P, Ac, Bc, m, s->perm + lo, s->pipe_count, s->st));
         TRY(launch_push_deposit(s->P, s->G, &s->tmap, s->jacc, Bc, Ac, s->perm + lo, s->pipe_start, s->cell_count, s->keys + lo,
@@ -747,7 +767,7 @@ static int pic_step_host_pipelined(mpic_sim* s, double* const planes[6], int64_t
     CUDA_TRY(cudaStreamSynchronize(s->pipe_down));
     CUDA_TRY(cudaStreamSynchronize(s->st));
     if (n_out) *n_out = n;
-    return 0;
+    return check_error_word(s);
 }
 
 int mpic_pic_steps_host(mpic_sim* s, int nsteps, double* const planes[6], int64_t n, double* x, double* y, double* ux,
@@ -755,6 +775,8 @@ int mpic_pic_steps_host(mpic_sim* s, int nsteps, double* const planes[6], int64_
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && planes, MPIC_EINVAL, "bad argument");
     REQUIRE(n >= 0 && n <= s->cap, MPIC_ENOMEM, "particle capacity %lld exceeded (%lld)", (long long)s->cap, (long long)n);
+    REQUIRE(n == 0 || (x && y && ux && uy && uz && q && tag), MPIC_EINVAL, "mpic_pic_steps_host: null particle array");
+    for (int p = 0; p < 6; p++) REQUIRE(planes[p], MPIC_EINVAL, "mpic_pic_steps_host: null field plane %d", p);
     int64_t pipe_min = 1 << 20;        // below this the transfers are too short to be worth chunking
     if (const char* e = getenv("MPIC_PIPELINE_MIN")) pipe_min = atoll(e);
     if (nsteps == 1 && s->prm.nranks == 1 && n >= pipe_min && n >= 2 && !getenv("MPIC_NO_PIPELINE"))
@@ -772,6 +794,19 @@ int mpic_pic_steps_host(mpic_sim* s, int nsteps, double* const planes[6], int64_
     return mpic_download_particles(s, n, x, y, ux, uy, uz, q, tag, n_out);
 }
 
+int mpic_cell_crossers(mpic_sim* s, int64_t* n_out) {
+    if (s) cudaSetDevice(s->prm.device);
+    REQUIRE(s && n_out && s->cap > 0, MPIC_EINVAL, "bad argument");
+    REQUIRE(s->counts_valid && s->arrived == 0, MPIC_ESTATE, "mpic_cell_crossers: call between mpic_push_deposit and mpic_sort_tiles");
+    CUDA_TRY(cudaMemsetAsync(s->d_scratch, 0, 8, s->st));
+    TRY(launch_crossers(s->P, s->cell_start, s->keys, (unsigned long long*)s->d_scratch, s->st));
+    s->launches++;
+    unsigned long long h = 0;
+    CUDA_TRY(cudaMemcpyAsync(&h, s->d_scratch, 8, cudaMemcpyDeviceToHost, s->st));
+    CUDA_TRY(cudaStreamSynchronize(s->st));
+    *n_out = (int64_t)h;
+    return 0;
+}
 int mpic_get_tile_counts(mpic_sim* s, int* counts) {
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && counts && s->cap > 0, MPIC_EINVAL, "bad argument");
@@ -812,10 +847,22 @@ int mpic_download_current(mpic_sim* s, int64_t* const jplanes[3]) {
 int mpic_fold_current(mpic_sim* s) {
     if (s) cudaSetDevice(s->prm.device); REQUIRE(s, MPIC_EINVAL, "null handle"); return fold_current(s); }
 
+// rho of the stored particles (node weights) into s->rho, guard ring folded as far as this slab can
+static int deposit_rho_plane(mpic_sim* s) {
+    const FieldGeom& G = s->G;
+    TRY(materialise(s));
+    if (!s->rho) CUDA_TRY(cudaMalloc(&s->rho, (size_t)G.plane * 8));
+    CUDA_TRY(cudaMemsetAsync(s->rho, 0, (size_t)G.plane * 8, s->st));
+    TRY(launch_deposit_rho(s->P, G, s->pa[s->cur], s->n, s->rho, s->st));
+    TRY(launch_fold_current(G, s->rho, 1, G.ywrap, s->st));
+    s->launches += 3;
+    return 0;
+}
 int mpic_diagnostics(mpic_sim* s, double out[5]) {
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && out, MPIC_EINVAL, "bad argument");
     const FieldGeom& G = s->G;
+    if (s->peer_on) TRY(mpic_sync(s));
     CUDA_TRY(cudaMemsetAsync(s->d_scratch, 0, 64, s->st));
     TRY(launch_field_energy(G, s->planes, s->d_scratch, s->st));
     s->launches++;
@@ -824,11 +871,8 @@ int mpic_diagnostics(mpic_sim* s, double out[5]) {
     if (s->cap > 0 && s->n > 0) {
         TRY(materialise(s));
         TRY(launch_kinetic(s->pa[s->cur], s->n, s->d_scratch + 1, s->st));
-        if (!s->rho) CUDA_TRY(cudaMalloc(&s->rho, (size_t)G.plane * 8));
-        CUDA_TRY(cudaMemsetAsync(s->rho, 0, (size_t)G.plane * 8, s->st));
-        TRY(launch_deposit_rho(s->P, G, s->pa[s->cur], s->n, s->rho, s->st));
-        TRY(launch_fold_current(G, s->rho, 1, G.ywrap, s->st));
-        s->launches += 4;
+        s->launches++;
+        TRY(deposit_rho_plane(s));
     }
     CUDA_TRY(cudaMemcpyAsync(h, s->d_scratch, 64, cudaMemcpyDeviceToHost, s->st));
     CUDA_TRY(cudaStreamSynchronize(s->st));
@@ -838,13 +882,31 @@ int mpic_diagnostics(mpic_sim* s, double out[5]) {
     out[4] = (double)s->n;
     out[2] = 0.0;
     if (s->rho && s->n > 0) {
+        // single slab: the neutralising background is minus the mean charge density.  Slabs: the LOCAL mean is used and the
+        // first row is skipped (see mpic_gauss_residual, which takes the global mean)
         mean_rho = h[2] * s->P.cjz / ((double)G.nx * G.nyl);          // sum q /(dx dy) / cells
-        TRY(launch_gauss_residual(G, s->planes, s->rho, mean_rho, s->P.inv_dx, s->P.inv_dy, s->d_scratch + 4, s->st));
+        TRY(launch_gauss_residual(G, s->planes, s->rho, mean_rho, s->P.inv_dx, s->P.inv_dy, s->d_scratch + 4, G.ywrap ? 0 : 1, s->st));
         s->launches++;
         CUDA_TRY(cudaMemcpyAsync(h, s->d_scratch, 64, cudaMemcpyDeviceToHost, s->st));
         CUDA_TRY(cudaStreamSynchronize(s->st));
         out[2] = h[4];
     }
+    return 0;
+}
+int mpic_gauss_residual(mpic_sim* s, double mean_rho, double* out) {
+    if (s) cudaSetDevice(s->prm.device);
+    REQUIRE(s && out, MPIC_EINVAL, "bad argument");
+    REQUIRE(s->cap > 0, MPIC_ESTATE, "no particle storage");
+    if (s->peer_on) TRY(mpic_sync(s));
+    TRY(deposit_rho_plane(s));
+    CUDA_TRY(cudaMemsetAsync(s->d_scratch, 0, 64, s->st));
+    // a slab's row 0 misses the node charge of the particles in the lower neighbour's top cell row: rows 1.. are complete
+    TRY(launch_gauss_residual(s->G, s->planes, s->rho, mean_rho, s->P.inv_dx, s->P.inv_dy, s->d_scratch + 4, s->G.ywrap ? 0 : 1, s->st));
+    s->launches++;
+    double h[8];
+    CUDA_TRY(cudaMemcpyAsync(h, s->d_scratch, 64, cudaMemcpyDeviceToHost, s->st));
+    CUDA_TRY(cudaStreamSynchronize(s->st));
+    *out = h[4];
     return 0;
 }
 

@@ -28,7 +28,10 @@ struct FieldGeom {
     int rows;             // nyl + 2g
     int64_t plane;        // values per plane = rows*pitch
     int ywrap;            // 1: y guards are the local periodic image (single slab)
+    unsigned int* err;    // device error word of the handle (MPIC_ERR_* bits), read back by mpic_sync
 };
+#define MPIC_ERR_POSITION 1u   /* a stored particle position was outside [0,box) or not finite (upload / arrival) */
+#define MPIC_ERR_JRANGE 2u     /* a fixed-point current accumulator came within a factor 2 of the int64 range (|J| >= 1024) */
 
 // Peer-memory halo: where the Yee sweeps store the images of their edge rows in the two ring neighbours' guard rows
 // (device pointers into the neighbours' 6-plane blocks, mapped by peer.cu).  All null: single slab or staged transport.
@@ -126,7 +129,7 @@ int launch_tile_e_full(double* E3, const double* B3, int tnx, int tny, int g, do
 int launch_strip_copy(const double* src6, double* dst6, int TX, int r0, int c0, int nr, int nc, int to_strip, cudaStream_t st);
 int launch_field_energy(const FieldGeom& G, const double* planes, double* out, cudaStream_t st);
 int launch_gauss_residual(const FieldGeom& G, const double* planes, const int64_t* rho, double mean_rho, double inv_dx,
-                          double inv_dy, double* out_max, cudaStream_t st);
+                          double inv_dy, double* out_max, int j_first, cudaStream_t st);
 
 // ---- kernel launchers implemented in particles.cu
 int launch_push_deposit(const PicConst& P, const FieldGeom& G, const CUtensorMap* tmap, int64_t* jacc, Particles src,
@@ -135,10 +138,11 @@ int launch_push_deposit(const PicConst& P, const FieldGeom& G, const CUtensorMap
 int launch_perm_build(const PicConst& P, const int* keys, int64_t n, int* cursor, int* perm, cudaStream_t st);
 int launch_gather(Particles src, Particles dst, int* perm, int64_t n, cudaStream_t st);
 int launch_absorb(const PicConst& P, Particles p, int64_t first, const double* rec, int n, int* cell_count, int* keys,
-                  cudaStream_t st);
-int launch_count_keys(const PicConst& P, Particles p, int64_t first, int64_t n, int* cell_count, int* key_out, cudaStream_t st);
+                  unsigned int* err, cudaStream_t st);
+int launch_count_keys(const PicConst& P, Particles p, int64_t first, int64_t n, int* cell_count, unsigned int* err, cudaStream_t st);
 int launch_scan_cells(int* cell_count, int* cell_start, int n_entries, int* block_tmp, cudaStream_t st);
 int launch_scatter(const PicConst& P, Particles src, Particles dst, int64_t n, int* perm_identity_out, int* cursor, cudaStream_t st);
+int launch_crossers(const PicConst& P, const int* cell_start, const int* keys, unsigned long long* out, cudaStream_t st);
 int launch_tile_counts(const PicConst& P, const int* cell_start, int* counts, cudaStream_t st);
 int launch_particle_tiles(const PicConst& P, Particles p, int64_t n, int row0, int* gid, cudaStream_t st);
 int launch_kinetic(Particles p, int64_t n, double* out2, cudaStream_t st);

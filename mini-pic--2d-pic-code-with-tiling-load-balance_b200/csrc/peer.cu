@@ -306,6 +306,23 @@ int mpic_peer_connect(mpic_sim* s, const mpic_peer_info* lo, const mpic_peer_inf
     return 0;
 }
 
+// per-phase device times of the peer PIC step (CUDA events on the handle's stream; costs one extra host wait per step, so
+// it is switched on only around a measurement).  enable: 1 = start / reset, 0 = stop, -1 = leave as is.  out_ms[11]: mean ms
+// per step of {b2wait, push, handoff, -, -, B1+counts, -, E, -, B2, host+absorb+sort}; *steps = steps accumulated.
+int mpic_peer_trace(mpic_sim* s, int enable, double* out_ms, long long* steps) {
+    if (s) cudaSetDevice(s->prm.device);
+    REQUIRE(s && s->peer_on, MPIC_ESTATE, "peer ring not connected");
+    if (out_ms) for (int k = 0; k < 11; k++) out_ms[k] = s->tsteps ? s->tacc[k] / (double)s->tsteps : 0.0;
+    if (steps) *steps = s->tsteps;
+    if (enable == 1) {
+        for (int k = 0; k < 12; k++) if (!s->tev[k]) CUDA_TRY(cudaEventCreate(&s->tev[k]));
+        for (int k = 0; k < 16; k++) s->tacc[k] = 0.0;
+        s->tsteps = 0;
+        s->trace = true;
+    } else if (enable == 0) s->trace = false;
+    return 0;
+}
+
 int mpic_peer_refresh_begin(mpic_sim* s) {
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && s->peer_on, MPIC_ESTATE, "peer ring not connected");
@@ -440,11 +457,12 @@ int mpic_peer_step_end(mpic_sim* s) {
         REQUIRE(leave[d] <= s->lv.cap && leave[d] <= s->peer[d].lcap && (int64_t)arr[d] <= s->lv.cap, MPIC_ENOMEM,
                 "migration buffer overflow: %d leavers / %lld arrivals > capacity %d", leave[d], (long long)arr[d], s->lv.cap);
     s->left = (int64_t)leave[0] + leave[1];
+    s->migrated_total += s->left;
     REQUIRE(s->n + (int64_t)arr[0] + (int64_t)arr[1] <= s->cap, MPIC_ENOMEM, "particle capacity exceeded by arrivals");
     for (int side = 0; side < 2; side++) {               // appended in (lower, upper) order -- SURVEY.md B.8
         const int n = (int)arr[side];
         TRY(launch_absorb(s->P, s->pa[s->cur], s->n + s->arrived, s->arrive_blk + (int64_t)(par * 2 + side) * s->lv.cap * MPIC_REC_DOUBLES,
-                          n, s->cell_count, s->keys, s->st));
+                          n, s->cell_count, s->keys, s->G.err, s->st));
         s->arrived += n;
         s->launches += n > 0;
     }

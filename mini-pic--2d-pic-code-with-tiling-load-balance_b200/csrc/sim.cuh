@@ -45,6 +45,7 @@ struct mpic_sim {
     double* arrive[2] = {};        // records received from the lower / upper neighbour
     int64_t arrived = 0;           // records absorbed into the tail [n, n+arrived) and not yet sorted in
     int64_t left = -1;             // leavers of the last push (host copy; -1: unknown)
+    int64_t migrated_total = 0;    // records handed to the neighbours so far (harness counter)
     // ---- peer-memory ring (peer.cu)
     struct PeerSide {
         double* planes = nullptr;          // neighbour's 6 field planes

@@ -185,6 +185,7 @@ __global__ void __launch_bounds__(256) e_sweep_kernel(FieldGeom G, double* __res
         }
 #pragma unroll
         for (int c = 0; c < 3; c++) jacc[c * G.plane + k] = 0;
+        if (((jv[0] ^ (jv[0] << 1)) | (jv[1] ^ (jv[1] << 1)) | (jv[2] ^ (jv[2] << 1))) < 0) atomicOr(G.err, MPIC_ERR_JRANGE);   // |acc| >= 2^62
         nex = fma(-dt, __ll2double_rn(jv[0]) * MPIC_INV_JSCALE, nex);
         ney = fma(-dt, __ll2double_rn(jv[1]) * MPIC_INV_JSCALE, ney);
         nez = fma(-dt, __ll2double_rn(jv[2]) * MPIC_INV_JSCALE, nez);
@@ -331,6 +332,7 @@ __global__ void __launch_bounds__(FY_THREADS) fused_yee_kernel(FieldGeom G, cons
             if (i <= G.nx && j <= G.nyl) {
                 int64_t jv[3];
                 fy_folded_j(G, jacc, i, j, jv);
+                if (((jv[0] ^ (jv[0] << 1)) | (jv[1] ^ (jv[1] << 1)) | (jv[2] ^ (jv[2] << 1))) < 0) atomicOr(G.err, MPIC_ERR_JRANGE);   // |acc| >= 2^62
                 nex = fma(-dt, __ll2double_rn(jv[0]) * MPIC_INV_JSCALE, nex);
                 ney = fma(-dt, __ll2double_rn(jv[1]) * MPIC_INV_JSCALE, ney);
                 nez = fma(-dt, __ll2double_rn(jv[2]) * MPIC_INV_JSCALE, nez);
@@ -510,14 +512,14 @@ __global__ void field_energy_kernel(FieldGeom G, const double* __restrict__ f, d
     if (threadIdx.x == 0) atomicAdd(out, sh[0]);
 }
 __global__ void gauss_kernel(FieldGeom G, const double* __restrict__ f, const int64_t* __restrict__ rho, double mean_rho,
-                             double inv_dx, double inv_dy, double* __restrict__ out_max) {
+                             double inv_dx, double inv_dy, double* __restrict__ out_max, int j_first) {
     __shared__ double sh[256];
     double m = 0.0;
-    const int64_t n = (int64_t)G.nx * G.nyl;
+    const int64_t n = (int64_t)G.nx * (G.nyl - j_first);
     const double* ex = f;
     const double* ey = f + G.plane;
     for (int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; c < n; c += (int64_t)gridDim.x * blockDim.x) {
-        const int i = (int)(c % G.nx), j = (int)(c / G.nx);
+        const int i = (int)(c % G.nx), j = j_first + (int)(c / G.nx);
         const int64_t k = (int64_t)(G.g + j) * G.pitch + MPIC_X0 + i;
         double div = (ex[k] - ex[k - 1]) * inv_dx + (ey[k] - ey[k - G.pitch]) * inv_dy;
         double r = fabs(div - (__ll2double_rn(rho[k]) * MPIC_INV_JSCALE - mean_rho));
@@ -657,8 +659,8 @@ int launch_field_energy(const FieldGeom& G, const double* planes, double* out, c
     return 0;
 }
 int launch_gauss_residual(const FieldGeom& G, const double* planes, const int64_t* rho, double mean_rho, double inv_dx,
-                          double inv_dy, double* out_max, cudaStream_t st) {
-    gauss_kernel<<<296, 256, 0, st>>>(G, planes, rho, mean_rho, inv_dx, inv_dy, out_max);
+                          double inv_dy, double* out_max, int j_first, cudaStream_t st) {
+    gauss_kernel<<<296, 256, 0, st>>>(G, planes, rho, mean_rho, inv_dx, inv_dy, out_max, j_first);
     LAUNCH_CHECK();
     return 0;
 }

@@ -129,6 +129,7 @@ class PeerStepper:
     def step(self):
         self.sim.peer_step_begin()
         self.sim.peer_step_end()
+        self.moved = self.sim.migrated_total
 
 
 # Cost of one grid cell in particle-equivalents, fitted on B200 from two N=1 bench lines of the 4096 x 512 slab (2.1 M cells):
@@ -284,73 +285,95 @@ def rebalance(sim, rank, world, make_sim, dist=None, group=None, w_cell=None, mi
 
 
 # ------------------------------------------------------------------------------------------------ multi-GPU bench
-def bench_fields(args, w, rank, world, local, peak, peak_how):
-    """Field-only workload (BASELINE.json configs[2]) on N slabs: half-B / E / half-B per step over the peer ring (the
-    sweeps store their slab-edge rows straight into the neighbours' guard rows; flags order the phases) or, with
-    MPIC_TRANSPORT=nccl, pack -> send/recv -> unpack.  Strong scaling: the n x n domain is split into N slabs."""
+def _fail(rank, msg):
+    """A failed self-check must not print a number: every rank exits non-zero."""
+    print(f"bench.py (rank {rank}): self-check FAILED: {msg}", file=sys.stderr, flush=True)
+    sys.exit(3)
+
+
+def fields_record(args, name, w, rank, world, local, peak, peak_how, clocks=True):
+    """Field-only workload (BASELINE.json configs[2]) on N slabs, strong scaling: the n x n domain is split into N slabs.
+    `value` = the fused one-kernel step over the peer ring (slab-edge CTAs store their rows straight into the neighbours'
+    guard rows of the other plane block, ONE flag exchange per step); the reference-faithful three sweeps (three flag
+    exchanges) are timed beside it; MPIC_TRANSPORT=nccl: pack -> send/recv -> unpack (three sweeps only).
+    Self-check: the two paths agree bit for bit on the field energy.  Returns the record on rank 0, None elsewhere."""
     import torch
     import torch.distributed as dist
     m = importlib.import_module(__package__)
     bench = importlib.import_module("bench")
-    dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     nx, ny, tn = w["nx"], w["ny"], w["tn"]
     dx = dy = w["dx"]
     dt = m.courant_dt(dx, dy)
-    sim = m.Sim(nx, ny, tn, tn, dx, dy, dt, rank=rank, nranks=world, device=local)
-    x = (np.arange(nx) + 0.5) * dx
-    prof = 0.1 * np.sin(np.pi * x) * np.cos((x - 3.5) / 3.0 * np.pi / 2) ** 2 * (np.abs(x - 3.5) < 3.0)
-    z = np.zeros((sim.nyl, nx))
-    row = np.tile(prof, (sim.nyl, 1))
-    sim.upload_planes([z, row, z, z, z, row])
-    st = sim.torch_stream()
     K, W = args.steps, max(args.warmup, 3)
     transport = os.environ.get("MPIC_TRANSPORT", "peer")
-    stepper = PeerStepper(sim, rank, world) if transport == "peer" else SlabStepper(sim, Ring(rank, world))
-    with torch.cuda.stream(st):
-        stepper.refresh_guards()
-        for _ in range(W):
-            stepper.field_step()
-        sim.sync()
-        dist.barrier()
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        l0 = sim.kernel_launches
-        clk = bench.ClockSampler(local) if rank == 0 else contextlib.nullcontext()
-        with clk:
-            e0.record(st)
-            for _ in range(K):
-                stepper.field_step()
-            e1.record(st)
+    x = (np.arange(nx) + 0.5) * dx
+    prof = 0.1 * np.sin(np.pi * x) * np.cos((x - 3.5) / 3.0 * np.pi / 2) ** 2 * (np.abs(x - 3.5) < 3.0)
+    results = {}
+    for fused in ((False, True) if transport == "peer" else (False,)):
+        sim = m.Sim(nx, ny, tn, tn, dx, dy, dt, rank=rank, nranks=world, device=local)
+        z = np.zeros((sim.nyl, nx))
+        row = np.tile(prof, (sim.nyl, 1))
+        sim.upload_planes([z, row, z, z, z, row])
+        st = sim.torch_stream()
+        stepper = PeerStepper(sim, rank, world) if transport == "peer" else SlabStepper(sim, Ring(rank, world))
+        step = (lambda: sim.peer_field_step(fused=True)) if fused else stepper.field_step
+        with torch.cuda.stream(st):
+            stepper.refresh_guards()
+            for _ in range(W):
+                step()
             sim.sync()
+            dist.barrier()
             torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            l0 = sim.kernel_launches
+            clk = bench.ClockSampler(local) if (rank == 0 and clocks and (fused or transport != "peer")) else contextlib.nullcontext()
+            with clk:
+                e0.record(st)
+                for _ in range(K):
+                    step()
+                e1.record(st)
+                sim.sync()
+                torch.cuda.synchronize()
+            dist.barrier()
+            gathered = [None] * world
+            dist.all_gather_object(gathered, (float(e0.elapsed_time(e1)), float(sim.diagnostics()["field_energy"])))
+        results[fused] = {"ms": max(g[0] for g in gathered), "energy": [g[1] for g in gathered], "launches": int(sim.kernel_launches - l0),
+                          "clocks": clk.summary() if hasattr(clk, "summary") else None}
         dist.barrier()
-        gathered = [None] * world
-        dist.all_gather_object(gathered, (float(e0.elapsed_time(e1)), float(sim.diagnostics()["field_energy"])))
-    if rank == 0:
-        ms = max(g[0] for g in gathered)
-        cells = float(nx) * ny * K
-        gbs = cells * bench.YEE_BYTES_3SWEEP / (ms * 1e-3) / 1e9 / world
-        print(json.dumps({
-            "metric": "Yee cell-updates/s", "value": cells / (ms * 1e-3), "unit": "cells/s", "n_gpus": world, "steps": K, "warmup": W,
-            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": args.workload, "nx": nx, "ny": ny, "decomposition": f"{world} slabs of {ny // world} rows, transport={transport}",
-                       "l2": "48 B/cell x 67 M cells = 3.2 GB >> 126 MB L2 x N"},
-            "roofline": {"bound": "hbm", "kernel": "b_sweep/e_sweep/b_sweep", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
-                         "traffic": None, "bytes_per_cell_update": bench.YEE_BYTES_3SWEEP, "peak_source": peak_how, "note": "per GPU"},
-            "gpu_launches": int(sim.kernel_launches - l0), "clocks": clk.summary(),
-            "field_energy_total": sum(g[1] for g in gathered)}))
-    sim.close()
-    dist.destroy_process_group()
+        sim.close()
+    if transport == "peer" and results[True]["energy"] != results[False]["energy"]:
+        _fail(rank, f"fused and three-sweep field energies differ: {results[True]['energy']} vs {results[False]['energy']}")
+    if rank != 0:
+        return None
+    best = results[True] if transport == "peer" else results[False]
+    bpc = bench.YEE_BYTES_FUSED if transport == "peer" else bench.YEE_BYTES_3SWEEP
+    ms = best["ms"]
+    cells = float(nx) * ny * K
+    gbs = cells * bpc / (ms * 1e-3) / 1e9 / world
+    rec = {"metric": "Yee cell-updates/s", "value": cells / (ms * 1e-3), "unit": "cells/s", "n_gpus": world, "steps": K, "warmup": W,
+           "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+           "config": dict(bench.workload_config(name, w, world), decomposition=f"{world} slabs of {ny // world} rows, transport={transport}"),
+           "roofline": {"bound": "hbm", "kernel": "fused_yee_kernel" if transport == "peer" else "b_sweep/e_sweep/b_sweep", "achieved": gbs, "peak": peak,
+                        "unit": "GB/s", "frac": gbs / peak, "traffic": None, "bytes_per_cell_update": bpc,
+                        "frac_of_144B_figure": cells * bench.YEE_BYTES_ALGO / (ms * 1e-3) / 1e9 / world / peak, "peak_source": peak_how, "note": "per GPU"},
+           "gpu_launches": best["launches"], "clocks": best["clocks"], "field_energy_total": sum(best["energy"]),
+           "self_check": {"ok": True, "fused_equals_three_sweeps_bitwise": transport == "peer"}}
+    if transport == "peer":
+        ms3 = results[False]["ms"]
+        rec["three_sweeps"] = {"ms_per_step": ms3 / K, "value": cells / (ms3 * 1e-3),
+                               "frac": cells * bench.YEE_BYTES_3SWEEP / (ms3 * 1e-3) / 1e9 / world / peak}
+    return rec
 
 
-def bench_main(args, w, rank, world, local, peak, peak_how):
-    """bench.py for N > 1 (torchrun, one rank per GPU): weak scaling -- every rank owns an (ny x nx) slab of an
-    (N*ny x nx) domain.  Timed on the device (CUDA events on the library stream), max over ranks."""
+def slab_pic_record(args, name, w, rank, world, local, peak, peak_how, e2e=True, clocks=True):
+    """One PIC workload on N slabs (torchrun, one rank per GPU): weak scaling -- every rank owns an (ny x nx) slab of an
+    (N*ny x nx) domain -- or strong scaling when the workload says so.  Timed on the device (CUDA events on the library
+    stream), max over ranks.  Before anything is returned the run is CHECKED: total particle count, total charge, Gauss's
+    law, peer-ring error word.  Returns the record on rank 0, None elsewhere."""
     import torch
     import torch.distributed as dist
     m = importlib.import_module(__package__)
     bench = importlib.import_module("bench")
-    dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     strong = bool(w.get("strong"))                      # strong scaling: the global domain is the workload's, split N ways
     nx, ny, tn, ppc = w["nx"], (w["ny"] if strong else w["ny"] * world), w["tn"], w["ppc"]
     dx = dy = w["dx"]
@@ -358,6 +381,7 @@ def bench_main(args, w, rank, world, local, peak, peak_how):
     gtr = ny // tn
     row0, nrows = m.slab_rows(gtr, world, rank)
     n_local = bench.expected_particles(w, ny, row0 * tn, (row0 + nrows) * tn)
+    n_expected = bench.expected_particles(w, ny, 0, ny)
     make = lambda r0, nr, n=0: m.Sim(nx, ny, tn, tn, dx, dy, dt, max_particles=int(max(n, 1) * 1.05) + 4096, rank=rank,
                                      nranks=world, device=local, rows=(r0, nr))
     sim = make(row0, nrows, n_local)
@@ -367,12 +391,14 @@ def bench_main(args, w, rank, world, local, peak, peak_how):
     K, W = args.steps, max(args.warmup, 3)
     transport = os.environ.get("MPIC_TRANSPORT", "peer")
     new_stepper = lambda s_: PeerStepper(s_, rank, world) if transport == "peer" else SlabStepper(s_, Ring(rank, world))
+    sat = int(w.get("saturate_steps", 0))
 
-    def timed(stepper, s_, stream, clocks=False):
-        """W warm-up + K timed steps; returns (max-over-ranks ms, total particles, launches, per-rank (ms, particles), clocks)."""
+    def timed(stepper, s_, stream, clocks=False, pre=0):
+        """`pre` untimed steps into the regime + W warm-up + K timed steps; returns (max-over-ranks ms, total particles,
+        launches, per-rank (ms, particles, rows), clocks)."""
         with torch.cuda.stream(stream):
             stepper.refresh_guards()
-            for _ in range(W):
+            for _ in range(pre + W):
                 stepper.step()
             s_.sync()
             dist.barrier()
@@ -388,7 +414,7 @@ def bench_main(args, w, rank, world, local, peak, peak_how):
                 s_.sync()
                 torch.cuda.synchronize()
             dist.barrier()
-            # the two scalars go through the object collective (host values; no stream-ordering subtleties between the
+            # the scalars go through the object collective (host values; no stream-ordering subtleties between the
             # library's non-blocking stream and the collective's own stream)
             gathered = [None] * world
             dist.all_gather_object(gathered, (float(e0.elapsed_time(e1)), int(s_.num_particles), int(s_.nrows)))
@@ -400,26 +426,59 @@ def bench_main(args, w, rank, world, local, peak, peak_how):
     if "beam_ppc" in w and not os.environ.get("MPIC_NO_REBALANCE"):
         # configs[4]: time the even split first, then let the cost-driven rebalancer move tile rows (fields + particles)
         ms0, np0, _, per0, _ = timed(stepper, sim, st)
+        torch.cuda.synchronize()
+        tr0 = time.perf_counter()
         new, rows, changed = rebalance(sim, rank, world, make, dist)
+        torch.cuda.synchronize()
         dist.barrier()
+        tr = [None] * world
+        dist.all_gather_object(tr, time.perf_counter() - tr0)
         if changed:
             sim.close()
             sim = new
             st = sim.torch_stream()
             stepper = new_stepper(sim)
-        rebal = {"changed": bool(changed), "even_split": {"ms_per_step": ms0 / K, "particles_per_rank": [g[1] for g in per0],
-                                                          "tile_rows_per_rank": [g[2] for g in per0],
-                                                          "pushes_per_s": float(np0) * K / (ms0 * 1e-3)},
+        rebal = {"changed": bool(changed), "rebalance_ms": 1e3 * max(tr),
+                 "even_split": {"ms_per_step": ms0 / K, "particles_per_rank": [g[1] for g in per0],
+                                "tile_rows_per_rank": [g[2] for g in per0], "pushes_per_s": float(np0) * K / (ms0 * 1e-3)},
                  "policy": f"slab.balanced_slab_rows on cost = particles + {W_CELL:g} * cells per tile row"}
-    ms_max, npart_total, launches, per, clocks = timed(stepper, sim, st, clocks=True)
+    ms_max, npart_total, launches, per, clk = timed(stepper, sim, st, clocks=clocks, pre=sat)
     if rebal is not None:
         rebal["rebalanced"] = {"ms_per_step": ms_max / K, "particles_per_rank": [g[1] for g in per],
                                "tile_rows_per_rank": [g[2] for g in per]}
+    # ---- per-phase device times of a few more steps (peer ring): the push kernel's own roofline at N > 1
+    phases = None
+    if transport == "peer":
+        with torch.cuda.stream(st):
+            sim.peer_trace(1)
+            for _ in range(min(K, 10)):
+                stepper.step()
+            sim.sync()
+            phases, nsteps = sim.peer_trace(0)
+            dist.barrier()
+    # ---- self-check (the run must not print a number for a wrong state)
+    with torch.cuda.stream(st):
+        sim.sync()                                      # raises if the peer ring's error word is set (a neighbour wait timed out)
+        d = sim.diagnostics()
+        allq = [None] * world
+        dist.all_gather_object(allq, (float(d["charge"]), int(d["particles"])))
+        q_tot, n_tot = sum(a[0] for a in allq), sum(a[1] for a in allq)
+        mean_rho = q_tot / (dx * dy) / (float(nx) * ny)
+        g = sim.gauss_residual(mean_rho)
+        allg = [None] * world
+        dist.all_gather_object(allg, float(g))
+    q0 = -1.0 * dx * dy / ppc * n_expected if "beam_ppc" not in w else q_tot
+    check = {"ok": bool(n_tot == n_expected and abs(q_tot - q0) <= 1e-9 * abs(q0) and max(allg) < 1e-9), "particles": n_tot,
+             "particles_expected": int(n_expected), "charge_error": q_tot - q0, "gauss_residual_max": max(allg), "peer_error_word": 0}
+    if not check["ok"]:
+        _fail(rank, f"{name}: {check}")
+    migrated = [None] * world
+    dist.all_gather_object(migrated, int(sim.migrated_total))
     n_local = int(sim.num_particles)
+    e2e_rec = None
     with torch.cuda.stream(st):
         # end to end: every rank uploads its slab (fields + particles) from pinned host memory, steps once, reads it back
-        e2e = None
-        if not args.no_e2e:
+        if e2e and not args.no_e2e:
             # pinned host images of this rank's slab (capacity with head-room: migration changes the count a little)
             cap = int(n_local * 1.02) + 4096
             hp = {k: torch.empty(cap, dtype=torch.float64).pin_memory().numpy() for k in m.PART_KEYS}
@@ -448,25 +507,64 @@ def bench_main(args, w, rank, world, local, peak, peak_how):
             dist.all_gather_object(tws, time.perf_counter() - t0)
             tw_max = max(tws)
             nbytes = 6 * nx * ny * 8 + int(npart_total) * 52
-            e2e = {"value": float(npart_total) * ke / tw_max, "unit": "particles/s", "h2d_bytes_per_step": nbytes,
-                   "d2h_bytes_per_step": nbytes, "steps": ke, "ms_per_step": 1e3 * tw_max / ke,
-                   "api": "per rank, pinned host buffers: mpic_upload_planes + mpic_upload_particles, one ring step, mpic_download_particles + mpic_download_planes"}
+            e2e_rec = {"value": float(npart_total) * ke / tw_max, "unit": "particles/s", "h2d_bytes_per_step": nbytes,
+                       "d2h_bytes_per_step": nbytes, "steps": ke, "ms_per_step": 1e3 * tw_max / ke,
+                       "api": "per rank, pinned host buffers: mpic_upload_planes + mpic_upload_particles, one ring step, mpic_download_particles + mpic_download_planes"}
+    rec = None
     if rank == 0:
         value = float(npart_total) * K / (ms_max * 1e-3)
-        out = {"metric": "particle-pushes/s (push+deposit+sort)", "value": value, "unit": "particles/s", "n_gpus": world,
+        rec = {"metric": "particle-pushes/s (push+deposit+sort)", "value": value, "unit": "particles/s", "n_gpus": world,
                "steps": K, "warmup": W, "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "strong" if strong else "weak",
                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-               "config": {"workload": args.workload, **w, "ny_global": ny, "particles": int(npart_total),
-                          "decomposition": f"{world} slabs of {ny // world} cell rows, periodic ring, transport={transport}" + (" (CUDA-IPC peer memory: halos fused into the sweeps, remote atomics for J, flags for ordering)" if transport == "peer" else " (NCCL send/recv)"),
-                          "l2": "per-rank particle state >> 126 MB L2 (no flush needed)"},
-               "gpu_launches": int(launches), "clocks": clocks, "migrated_records_rank0": int(stepper.moved),
-               "roofline": {"bound": "hbm", "kernel": "whole step", "achieved": value * 112.0 / 1e9 / world, "peak": peak,
-                            "unit": "GB/s", "frac": value * 112.0 / 1e9 / world / peak, "traffic": None,
-                            "bytes_per_particle": 112.0, "peak_source": peak_how, "note": "per GPU: fused push+reorder 104 B + permutation sort 8 B per particle"}}
-        if e2e:
-            out["e2e"] = e2e
+               "config": dict(bench.workload_config(name, w, world),
+                              decomposition=f"{world} slabs of {ny // world} cell rows, periodic ring, transport={transport}" + (" (CUDA-IPC peer memory: halos fused into the sweeps, remote atomics for J, flags for ordering)" if transport == "peer" else " (NCCL send/recv)")),
+               "regime": (f"saturated: timed after {sat} untimed steps + {W} warm-up steps" if sat else f"timed after {W} warm-up steps"),
+               "gpu_launches": int(launches), "clocks": clk, "migrated_records_per_rank": migrated, "self_check": check}
+        if phases:
+            push_ms = phases["push_deposit"]
+            n_rank0 = per[0][1]
+            gbs = n_rank0 * bench.PUSH_BYTES_SURVEY / (push_ms * 1e-3) / 1e9 if push_ms > 0 else 0.0
+            rec["phases_ms_rank0"] = phases
+            rec["roofline"] = {"bound": "hbm", "kernel": "push_deposit_kernel (rank 0, CUDA events around the launch)", "achieved": gbs, "peak": peak,
+                               "unit": "GB/s", "frac": gbs / peak, "bytes_per_particle": bench.PUSH_BYTES_SURVEY,
+                               "frac_104B": gbs / peak * bench.PUSH_BYTES_FUSED_REORDER / bench.PUSH_BYTES_SURVEY, "traffic": None,
+                               "peak_source": peak_how,
+                               "whole_step_frac_112B": value * 112.0 / 1e9 / world / peak}
+        else:
+            rec["roofline"] = {"bound": "hbm", "kernel": "whole step", "achieved": value * 112.0 / 1e9 / world, "peak": peak,
+                               "unit": "GB/s", "frac": value * 112.0 / 1e9 / world / peak, "traffic": None,
+                               "bytes_per_particle": 112.0, "peak_source": peak_how, "note": "per GPU: fused push+reorder 104 B + permutation sort 8 B per particle"}
+        if e2e_rec:
+            rec["e2e"] = e2e_rec
         if rebal is not None:
-            out["rebalance"] = rebal
-        print(json.dumps(out))
+            rec["rebalance"] = rebal
+    dist.barrier()
     sim.close()
+    return rec
+
+
+def bench_multi(args, w, rank, world, local, peak, peak_how):
+    """bench.py for N > 1: the named workload's line, plus -- for the default workload -- the sub-records `c4_slab`
+    (configs[3]: 134 M particles per GPU; at N = 8 this is the 1.07 B-particle config, weak scaling) and `yee_8192`
+    (configs[2], strong scaling), and rank 0's bounded CPU baseline."""
+    import torch
+    import torch.distributed as dist
+    bench = importlib.import_module("bench")
+    dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    if w.get("fields_only"):
+        out = fields_record(args, args.workload, w, rank, world, local, peak, peak_how)
+    else:
+        out = slab_pic_record(args, args.workload, w, rank, world, local, peak, peak_how)
+        if not args.no_sub and args.workload == "two_stream_512":
+            c4 = slab_pic_record(args, "uniform_c4_slab", bench.WORKLOADS["uniform_c4_slab"], rank, world, local, peak, peak_how, e2e=False)
+            yee = None if args.no_yee else fields_record(args, "yee_8192", bench.WORKLOADS["yee_8192"], rank, world, local, peak, peak_how)
+            if rank == 0:
+                out["c4_slab"] = c4
+                if yee:
+                    out["yee_8192"] = yee
+        if rank == 0 and not args.no_cpu:
+            out["cpu_baseline"] = bench.cpu_baseline_pic(w)
+    dist.barrier()
+    if rank == 0:
+        print(json.dumps(out))
     dist.destroy_process_group()

@@ -346,3 +346,11 @@ int orc_num_threads(void) {
     return 1;
 #endif
 }
+/* the timed CPU arm pins its thread count explicitly: a launcher (torchrun) may have exported OMP_NUM_THREADS=1 */
+void orc_set_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}

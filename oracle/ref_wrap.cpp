@@ -50,8 +50,10 @@ extern "C" {
 int ref_sizeof_particle() { return (int)sizeof(Particle); }
 #ifdef _OPENMP
 int ref_num_threads() { return omp_get_max_threads(); }
+void ref_set_threads(int n) { if (n > 0) omp_set_num_threads(n); }   // a launcher (torchrun) may have exported OMP_NUM_THREADS=1
 #else
 int ref_num_threads() { return 1; }
+void ref_set_threads(int) {}
 #endif
 
 // ---- Field_update.h:36,54 on raw pointers (AoS triplets, tile incl. guards, row-major j*TX+i)

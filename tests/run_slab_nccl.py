@@ -1,5 +1,8 @@
-"""torchrun entry (one process per GPU): K PIC steps on N slabs over NCCL, rank 0 checks bit-exactness vs the CPU oracle.
-  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 tests/run_slab_nccl.py"""
+"""torchrun entry (one process per rank): K PIC steps on N slabs, rank 0 checks bit-exactness vs the CPU oracle.
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 tests/run_slab_nccl.py
+MPIC_TEST_TRANSPORT = nccl (default; one GPU per rank) | peer (CUDA-IPC peer ring) | staged (SlabStepper over gloo with host
+staging).  On a box with fewer GPUs than ranks every rank uses cuda:0 and the process group is gloo: CUDA IPC works between
+processes on one device, so the REAL two-process peer path (IPC mapping, .sys-scope flags between processes) still runs."""
 import importlib
 import os
 import sys
@@ -14,10 +17,42 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
 from util import PKG, by_tag, copy_parts  # noqa: E402
 
 
+class HostStagedRing:
+    """slab.Ring's interface over gloo: device staging buffers -> host -> isend/irecv (tagged) -> host -> device."""
+
+    def __init__(self, rank, world):
+        self.rank, self.world = rank, world
+        self.lo, self.hi = (rank - 1) % world, (rank + 1) % world
+
+    def sendrecv(self, send_lo, send_hi, recv_lo, recv_hi):
+        reqs, back = [], []
+        for t, dst, tag in ((send_lo, self.lo, 0), (send_hi, self.hi, 1)):
+            if t is not None:
+                reqs.append(dist.isend(t.cpu(), dst, tag=tag))
+        # the lower neighbour's "to upper" (tag 1) lands in my recv_lo; the upper neighbour's "to lower" (tag 0) in recv_hi
+        for t, src, tag in ((recv_hi, self.hi, 0), (recv_lo, self.lo, 1)):
+            if t is not None:
+                h = torch.empty(t.shape, dtype=t.dtype)
+                reqs.append(dist.irecv(h, src, tag=tag))
+                back.append((t, h))
+        for r in reqs:
+            r.wait()
+        for t, h in back:
+            t.copy_(h)
+
+
 def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    transport = os.environ.get("MPIC_TEST_TRANSPORT", "nccl")
+    one_device = torch.cuda.device_count() < world
+    if one_device:
+        local = 0
+        assert transport != "nccl", "NCCL needs one GPU per rank"
     torch.cuda.set_device(local)
-    dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    if one_device or transport == "staged":
+        dist.init_process_group("gloo")
+    else:
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     m = importlib.import_module(PKG)
     plasma = importlib.import_module(PKG + ".plasma")
     slab = importlib.import_module(PKG + ".slab")
@@ -32,15 +67,25 @@ def main():
     with torch.cuda.stream(s.torch_stream()):
         s.upload_planes([a[r0:r1] for a in planes])
         s.upload_particles(parts)
-        transport = os.environ.get("MPIC_TEST_TRANSPORT", "nccl")
-        st = slab.PeerStepper(s, rank, world) if transport == "peer" else slab.SlabStepper(s, slab.Ring(rank, world))
+        if transport == "peer":
+            st = slab.PeerStepper(s, rank, world)
+        else:
+            st = slab.SlabStepper(s, HostStagedRing(rank, world) if transport == "staged" else slab.Ring(rank, world))
         st.refresh_guards()
         for _ in range(steps):
             st.step()
+        fsteps = 0
+        if transport == "peer":                     # field-only steps on top: fused kernel (one flag exchange per step) mixed with the sweeps
+            for _ in range(3):
+                s.peer_field_step(fused=True)
+            s.peer_field_step()
+            for _ in range(2):
+                s.peer_field_step(fused=True)
+            fsteps = 6
         s.sync()
     dist.barrier()                                  # peer transport: nobody tears its memory down while a neighbour still steps
     mine = {"parts": s.download_particles(), "planes": s.download_planes(), "counts": s.tile_counts(),
-            "moved": st.moved if transport != "peer" else 1}
+            "moved": s.migrated_total}
     allr = [None] * world
     dist.all_gather_object(allr, mine)
     if rank == 0:
@@ -49,6 +94,8 @@ def main():
         P = ob.make_params(lib, nx, ny, tn, tn, dx, dy, dt)
         want, wf = copy_parts(parts), [a.copy() for a in planes]
         counts, _ = ob.pic_steps(lib, P, wf, want, steps)
+        if fsteps:
+            ob.yee_steps(lib, wf, dt, dx, dy, fsteps)
         got = by_tag({k: np.concatenate([a["parts"][k] for a in allr]) for k in ("x", "y", "ux", "uy", "uz", "q", "tag")})
         want = by_tag(want)
         assert np.array_equal(got["tag"], want["tag"])

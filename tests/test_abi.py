@@ -56,6 +56,18 @@ def test_compute_fails_loudly_without_gpu():
         m.update_e_full(E, E.copy(), 4, 4, 2, 0.01, 0.1, 0.1)
 
 
+def test_create_rejects_bad_parameters_before_touching_the_device():
+    """Argument validation needs no GPU: dt beyond one cell per step (the push assumes |v| dt < min(dx,dy)), tiles that do
+    not divide the grid, capacities beyond the 32-bit particle index."""
+    m = pkg()
+    with pytest.raises(m.MpicError, match="exceeds min"):
+        m.Sim(32, 32, 16, 16, 0.1, 0.1, 0.15, max_particles=100)
+    with pytest.raises(m.MpicError, match="multiples of the tile"):
+        m.Sim(30, 32, 16, 16, 0.1, 0.1, 0.03)
+    with pytest.raises(m.MpicError, match="32-bit"):
+        m.Sim(32, 32, 16, 16, 0.1, 0.1, 0.03, max_particles=2**31)
+
+
 def test_product_never_touches_the_oracle():
     """The product package and its CUDA sources must not import, link or dlopen anything under oracle/."""
     bad = []

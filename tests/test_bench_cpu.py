@@ -58,3 +58,30 @@ def test_rank_nonzero_of_the_reference_arm_does_no_work():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2"], capture_output=True,
                        text=True, timeout=120, env=env)
     assert r.returncode == 0 and r.stdout.strip() == ""
+
+
+def test_reference_arm_particle_line_is_honest():
+    """The CPU arm runs the FULL named configuration for the steps it is given, prints those steps, the same `config`
+    object the native arm prints, and uses every host core even when a launcher exported OMP_NUM_THREADS=1 (torchrun)."""
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--workload", "thermal_128", "--steps", "2",
+                        "--warmup", "1"], capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0, r.stderr
+    d = json.loads(r.stdout.strip().splitlines()[-1])
+    assert d["impl"] == "reference" and d["steps"] == 2 and d["warmup"] == 1
+    assert d["config"] == json.loads(json.dumps(bench.workload_config("thermal_128", bench.WORKLOADS["thermal_128"], 1)))
+    assert d["config"]["particles"] == 128 * 128 * 16 and "262144 particles" in d["cpu_baseline"]["sample"]
+    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] == bench.cpu_threads()
+    assert d["e2e"] == {"value": d["value"], "unit": "particles/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert abs(d["ms_per_step"] * 1e-3 * d["value"] - 262144) < 1.0          # ms_per_step is the measured time of one full step
+
+
+def test_both_arms_build_the_same_config_object():
+    for name, w in bench.WORKLOADS.items():
+        for world in (1, 8):
+            c = bench.workload_config(name, w, world)
+            assert c["workload"] == name and json.loads(json.dumps(c)) == c or isinstance(w.get("beam_band"), tuple)
+            if not w.get("strong"):
+                assert c["ny_global"] == w["ny"] * world
+    c8 = bench.workload_config("uniform_c4_slab", bench.WORKLOADS["uniform_c4_slab"], 8)
+    assert c8["particles"] == 1073741824          # at 8 GPUs the slab workload IS configs[3]

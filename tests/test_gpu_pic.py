@@ -255,3 +255,25 @@ def test_branch_free_division_and_sqrt_are_ieee():
     would only be statistical."""
     for seed in (1, 0xC0FFEE):
         assert pkg().selftest_math(1 << 30, seed) == 0
+
+
+def test_upload_rejects_positions_outside_the_box():
+    """caller input must not reach device indexing unvalidated.  x == box_x, a negative y and a NaN are reported as
+    MPIC_EINVAL by the upload (the particle is binned into cell 0, nothing is written out of bounds), and the handle stays
+    usable for a valid upload afterwards."""
+    m = pkg()
+    nx = ny = 32
+    dx = dy = 0.1
+    s = m.Sim(nx, ny, 16, 16, dx, dy, m.courant_dt(dx, dy), max_particles=4096)
+    good = plasma().load_uniform(nx, ny, 16, 16, dx, dy, 2, u_th=0.1, seed=3)
+    for bad_x, bad_y in ((nx * dx, 0.5), (0.5, -1e-9), (float("nan"), 0.5)):
+        p = copy_parts(good)
+        p["x"][7], p["y"][7] = bad_x, bad_y
+        with pytest.raises(m.MpicError, match="outside"):
+            s.upload_particles(p)
+    s.upload_particles(good)
+    s.pic_steps(2)
+    s.sync()
+    assert s.num_particles == good["x"].shape[0]
+    rc = m.lib().mpic_upload_particles(s.h, 4, None, None, None, None, None, None, None)
+    assert rc == -1 and b"null" in m.lib().mpic_last_error()
