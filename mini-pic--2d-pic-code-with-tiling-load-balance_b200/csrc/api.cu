@@ -223,7 +223,14 @@ int mpic_create(const mpic_params* p, mpic_sim** out) {
         CUDA_TRY(cudaMalloc(&s->scan_tmp, (size_t)(s->n_entries / 2048 + 2) * 4));
         CUDA_TRY(cudaMalloc(&s->keys, (size_t)s->cap * 4));
         CUDA_TRY(cudaMalloc(&s->perm, (size_t)s->cap * 4));
+        CUDA_TRY(cudaMalloc(&s->dirs, (size_t)s->cap));
+        CUDA_TRY(cudaMalloc(&s->cell_start_alt, (size_t)(s->n_entries + 1) * 4));
+        CUDA_TRY(cudaMalloc(&s->mcnt, (size_t)9 * P.ncells * 4));
+        CUDA_TRY(cudaMalloc(&s->offtab, (size_t)9 * P.ncells * 4));
+        CUDA_TRY(cudaMemsetAsync(s->mcnt, 0, (size_t)9 * P.ncells * 4, s->st));
         CUDA_TRY(cudaMemsetAsync(s->cell_start, 0, (size_t)(s->n_entries + 1) * 4, s->st));
+        CUDA_TRY(cudaMemsetAsync(s->cell_start_alt, 0, (size_t)(s->n_entries + 1) * 4, s->st));
+        if (p->nranks > 1) CUDA_TRY(cudaMalloc(&s->lv_off, (size_t)2 * p->nx * 4));
         TRY(make_tensor_map(s));
         // enough CTAs per tile that the grid covers >= 4 waves of 2 CTAs/SM even for few tiles
         int ntiles = P.ltr * P.gtc;
@@ -274,6 +281,7 @@ int mpic_destroy(mpic_sim* s) {
     cudaFree(s->planes); cudaFree(s->planes_alt); cudaFree(s->jacc); cudaFree(s->rho); cudaFree(s->d_scratch);
     for (int k = 0; k < 2; k++) { cudaFree(s->pa[k].x); cudaFree(s->pa[k].tag); }
     cudaFree(s->cell_start); cudaFree(s->cell_count); cudaFree(s->scan_tmp); cudaFree(s->keys); cudaFree(s->perm);
+    cudaFree(s->cell_start_alt); cudaFree(s->mcnt); cudaFree(s->offtab); cudaFree(s->dirs); cudaFree(s->lv_off);
     cudaFree(s->halo_send); cudaFree(s->halo_recv); cudaFree(s->lv.count);
     for (int d = 0; d < 2; d++) cudaFree(s->lv.rec[d]);
     cudaFree(s->arrive_blk);
@@ -542,36 +550,45 @@ int mpic_migration_absorb(mpic_sim* s, int n_from_lo, int n_from_hi) {
 // physical reorder on demand: after this pa[cur][0..n) is itself in sorted order
 static int materialise(mpic_sim* s) {
     if (!s->perm_valid) return 0;
-    TRY(launch_gather(s->pa[s->cur], s->pa[s->cur ^ 1], s->perm, s->n, s->st));
+    TRY(launch_gather(s->pa[s->cur], s->pa[s->cur ^ 1], s->perm, s->n, nullptr, s->st));
     s->launches++;
     s->cur ^= 1;
     s->perm_valid = false;
     return 0;
 }
-// counted (after a push): the push/absorb kernels left the destination-key histogram in cell_count and every stored
-// particle's key in keys[] -> scan + permutation build, no particle data moves (the next push gathers through perm).
-// Otherwise (uploads, loads): count from the stored positions, scan, physical scatter.
+// The sort (kernels in particles.cu).  Both forms are STABLE and reproducible: no atomic decides a final slot.
+// counted (after a push): the push left every particle's direction code in dirs[] and the per-cell move counts in mcnt, and
+//   mpic_push_deposit turned them into the destination histogram cell_count (arrivals absorbed since were added to it):
+//   scan -> offsets -> perm_stable (+ arrivals appended); no particle data moves, the next push gathers through perm.
+// otherwise (uploads, loads, appends: arbitrary storage order): keys from the stored positions, histogram, scan, provisional
+//   permutation, per-cell ascending sort of the permutation (== stable order), physical gather.
 static int sort_all(mpic_sim* s, bool counted) {
     counted = counted && s->counts_valid;
     s->counts_valid = false;
-    if (!counted) {
+    const int64_t total = s->n + s->arrived;
+    if (counted) {
+        TRY(launch_scan_cells(s->cell_count, s->cell_start_alt, s->n_entries, s->scan_tmp, s->st));
+        TRY(launch_offsets(s->P, s->G.ywrap, s->mcnt, s->cell_start_alt, s->offtab, s->cell_count, s->st));
+        TRY(launch_perm_stable(s->P, s->G.ywrap, s->cell_start, s->dirs, s->offtab, s->perm, s->n, s->st));
+        TRY(launch_arrivals(s->P, s->keys, s->n, (int)s->arrived, s->cell_count, s->cell_start_alt, s->perm, s->st));
+        std::swap(s->cell_start, s->cell_start_alt);
+        s->perm_valid = true;
+        s->launches += 5 + (s->arrived > 0 ? 2 : 0);
+    } else {
         if (s->perm_valid && s->arrived == 0) return 0;          // already sorted, nothing new
         TRY(materialise(s));
         CUDA_TRY(cudaMemsetAsync(s->cell_count, 0, (size_t)s->n_entries * 4, s->st));
-        TRY(launch_count_keys(s->P, s->pa[s->cur], 0, s->n + s->arrived, s->cell_count, s->G.err, s->st));
-        s->launches++;
-    }
-    const int64_t total = s->n + s->arrived;
-    TRY(launch_scan_cells(s->cell_count, s->cell_start, s->n_entries, s->scan_tmp, s->st));
-    if (counted) {
+        TRY(launch_count_keys(s->P, s->pa[s->cur], 0, total, s->cell_count, s->keys, s->G.err, s->st));
+        TRY(launch_scan_cells(s->cell_count, s->cell_start, s->n_entries, s->scan_tmp, s->st));
         TRY(launch_perm_build(s->P, s->keys, total, s->cell_count, s->perm, s->st));
-        s->perm_valid = true;
-    } else {
-        TRY(launch_scatter(s->P, s->pa[s->cur], s->pa[s->cur ^ 1], total, s->perm, s->cell_count, s->st));
+        TRY(launch_segsort(s->cell_start, s->P.ncells, s->perm, s->keys, s->st));
+        // physical reorder; slab leavers (keys >= ncells) are not in perm: only the first cell_start[ncells] slots exist
+        TRY(launch_gather(s->pa[s->cur], s->pa[s->cur ^ 1], s->perm, total, s->cell_start + s->P.ncells, s->st));
         s->cur ^= 1;
+        s->perm_valid = false;
+        s->launches += 8;
     }
-    s->launches += 4;
-    if (s->prm.nranks > 1) {       // particles whose key is a leaver bin are dropped by the scatter / not entered in perm
+    if (s->prm.nranks > 1) {       // particles whose key is a leaver bin are not entered in perm
         if (counted && s->left >= 0) s->n = total - s->left;
         else {
             int kept = 0;
@@ -642,14 +659,19 @@ int mpic_push_deposit(mpic_sim* s) {
     REQUIRE(s && s->cap > 0, MPIC_ESTATE, "no particle storage");
     REQUIRE(s->arrived == 0, MPIC_ESTATE, "arrivals absorbed but not sorted in: call mpic_sort_tiles before the next push");
     REQUIRE(!s->counts_valid, MPIC_ESTATE, "particles moved but not re-sorted: call mpic_sort_tiles between pushes");
-    CUDA_TRY(cudaMemsetAsync(s->cell_count, 0, (size_t)s->n_entries * 4, s->st));
-    if (s->prm.nranks > 1) CUDA_TRY(cudaMemsetAsync(s->lv.count, 0, 2 * sizeof(int), s->st));
     s->left = s->prm.nranks > 1 ? -1 : 0;
     TRY(launch_push_deposit(s->P, s->G, &s->tmap, s->jacc, s->pa[s->cur], s->pa[s->cur ^ 1], s->perm,
-                            s->cell_start, s->cell_count, s->keys, s->push_split, s->lv, s->st, s->n));
-    s->launches++;
+                            s->cell_start, s->mcnt, s->dirs, s->push_split, s->lv, s->st, s->n));
     s->cur ^= 1;                    // the push wrote the other buffer in slot order
     s->perm_valid = false;
+    // destination histogram of the push (a gather over the move counts, no atomics); slab leavers: their records are written in
+    // slot order into the send buffers, their counts into lv.count and the two leaver bins of the histogram
+    TRY(launch_count_moves(s->P, s->G.ywrap, s->mcnt, s->cell_count, s->st));
+    s->launches += 2;
+    if (s->prm.nranks > 1) {
+        TRY(launch_leavers(s->P, s->pa[s->cur], s->cell_start, s->dirs, s->mcnt, s->lv_off, s->cell_count, s->lv, s->st));
+        s->launches += 2;
+    }
     s->counts_valid = true;
     return 0;
 }
@@ -728,7 +750,6 @@ static int pic_step_host_pipelined(mpic_sim* s, double* const planes[6], int64_t
         CUDA_TRY(cudaMemcpy2DAsync(s->planes + p * G.plane + (int64_t)G.g * G.pitch + MPIC_X0, (size_t)G.pitch * 8, planes[p],
                                    (size_t)G.nx * 8, (size_t)G.nx * 8, G.nyl, cudaMemcpyHostToDevice, s->st));
     TRY(refresh_all_guards(s));
-    CUDA_TRY(cudaMemsetAsync(s->cell_count, 0, (size_t)s->n_entries * 4, s->st));
     const double* src[6] = { x, y, ux, uy, uz, q };
     double* hdst[6] = { x, y, ux, uy, uz, q };
     for (int c = 0; c < nchunk; c++) {
@@ -738,32 +759,38 @@ static int pic_step_host_pipelined(mpic_sim* s, double* const planes[6], int64_t
         for (int k = 0; k < 6; k++) CUDA_TRY(cudaMemcpyAsync(dA[k] + lo, src[k] + lo, (size_t)m * 8, cudaMemcpyHostToDevice, s->pipe_up));
         CUDA_TRY(cudaMemcpyAsync(A.tag + lo, tag + lo, (size_t)m * 4, cudaMemcpyHostToDevice, s->pipe_up));
         CUDA_TRY(cudaEventRecord(s->pipe_ev_up[c], s->pipe_up));
-        // sort the chunk inside [lo, hi): A -> B, then push B -> A
+        // sort the chunk inside [lo, hi) (stable: provisional permutation + per-cell ascending sort), then push A -> B through it
         CUDA_TRY(cudaStreamWaitEvent(s->st, s->pipe_ev_up[c], 0));
         CUDA_TRY(cudaMemsetAsync(s->pipe_count, 0, (size_t)s->n_entries * 4, s->st));
         const Particles Ac = offset_particles(A, lo), Bc = offset_particles(B, lo);
-        TRY(launch_count_keys(s->P, Ac, 0, m, s->pipe_count, s->G.err, s->st));
+        TRY(launch_count_keys(s->P, Ac, 0, m, s->pipe_count, s->keys + lo, s->G.err, s->st));
         TRY(launch_scan_cells(s->pipe_count, s->pipe_start, s->n_entries, s->scan_tmp, s->st));
-        TRY(launch_scatter(s->P, Ac, Bc, m, s->perm + lo, s->pipe_count, s->st));
-        TRY(launch_push_deposit(s->P, s->G, &s->tmap, s->jacc, Bc, Ac, s->perm + lo, s->pipe_start, s->cell_count, s->keys + lo,
+        TRY(launch_perm_build(s->P, s->keys + lo, m, s->pipe_count, s->perm + lo, s->st));
+        TRY(launch_segsort(s->pipe_start, s->P.ncells, s->perm + lo, s->keys + lo, s->st));
+        TRY(launch_push_deposit(s->P, s->G, &s->tmap, s->jacc, Ac, Bc, s->perm + lo, s->pipe_start, s->mcnt, s->dirs + lo,
                                 s->push_split, s->lv, s->st, 0));      // chunk occupancy unknown: adaptive lane groups
-        s->launches += 6;
+        s->launches += 8;
         CUDA_TRY(cudaEventRecord(s->pipe_ev_done[c], s->st));
         // results of the chunk go home while the next one is still arriving
         CUDA_TRY(cudaStreamWaitEvent(s->pipe_down, s->pipe_ev_done[c], 0));
-        for (int k = 0; k < 6; k++) CUDA_TRY(cudaMemcpyAsync(hdst[k] + lo, dA[k] + lo, (size_t)m * 8, cudaMemcpyDeviceToHost, s->pipe_down));
-        CUDA_TRY(cudaMemcpyAsync(tag + lo, A.tag + lo, (size_t)m * 4, cudaMemcpyDeviceToHost, s->pipe_down));
+        double* dB[6] = { B.x, B.y, B.ux, B.uy, B.uz, B.q };
+        for (int k = 0; k < 6; k++) CUDA_TRY(cudaMemcpyAsync(hdst[k] + lo, dB[k] + lo, (size_t)m * 8, cudaMemcpyDeviceToHost, s->pipe_down));
+        CUDA_TRY(cudaMemcpyAsync(tag + lo, B.tag + lo, (size_t)m * 4, cudaMemcpyDeviceToHost, s->pipe_down));
     }
+    s->cur ^= 1;                       // the pushed particles are in B, chunk by chunk
     s->n = n;
     s->left = 0;
-    s->counts_valid = true;            // cell_count = destination histogram of all chunks, keys[] = destination keys
-    TRY(mpic_step_b_half(s));
-    TRY(e_sweep(s, 1));
-    TRY(mpic_step_b_half(s));
+    if (s->prm.scheme == 0 && !getenv("MPIC_NO_FUSED_YEE")) TRY(fused_step_local(s, 1));
+    else {
+        TRY(mpic_step_b_half(s));
+        TRY(e_sweep(s, 1));
+        TRY(mpic_step_b_half(s));
+    }
     for (int p = 0; p < 6; p++)
         CUDA_TRY(cudaMemcpy2DAsync(planes[p], (size_t)G.nx * 8, s->planes + p * G.plane + (int64_t)G.g * G.pitch + MPIC_X0,
                                    (size_t)G.pitch * 8, (size_t)G.nx * 8, G.nyl, cudaMemcpyDeviceToHost, s->st));
-    TRY(sort_all(s, true));            // resident state stays usable: A read through perm
+    TRY(sort_all(s, false));           // resident state stays usable: one stable sort by position over all chunks (B -> A; the
+                                       // downloads above only read B)
     CUDA_TRY(cudaStreamSynchronize(s->pipe_down));
     CUDA_TRY(cudaStreamSynchronize(s->st));
     if (n_out) *n_out = n;
@@ -799,7 +826,7 @@ int mpic_cell_crossers(mpic_sim* s, int64_t* n_out) {
     REQUIRE(s && n_out && s->cap > 0, MPIC_EINVAL, "bad argument");
     REQUIRE(s->counts_valid && s->arrived == 0, MPIC_ESTATE, "mpic_cell_crossers: call between mpic_push_deposit and mpic_sort_tiles");
     CUDA_TRY(cudaMemsetAsync(s->d_scratch, 0, 8, s->st));
-    TRY(launch_crossers(s->P, s->cell_start, s->keys, (unsigned long long*)s->d_scratch, s->st));
+    TRY(launch_crossers(s->dirs, s->n, (unsigned long long*)s->d_scratch, s->st));
     s->launches++;
     unsigned long long h = 0;
     CUDA_TRY(cudaMemcpyAsync(&h, s->d_scratch, 8, cudaMemcpyDeviceToHost, s->st));

@@ -40,6 +40,10 @@ struct PeerHalo {
     double* hi = nullptr;     // upper neighbour's planes; my interior rows [nyl-g,nyl) -> its rows j-(nyl-g) (its lower guard)
     int64_t lo_plane = 0, hi_plane = 0;
     int lo_row0 = 0;          // g + nyl_lo
+    // fused PIC step on a slab: the current of the cell row just above the slab (needed for the ring of E') is the upper
+    // neighbour's first interior row of ITS accumulators (complete once both ranks' hand-offs are done), read over NVLink
+    const int64_t* hi_j = nullptr;
+    int64_t hi_jplane = 0;
 };
 
 // Phase ordering fused into the sweeps of a peer-memory ring (peer.cu): only the CTAs that own slab-edge rows wait for the
@@ -48,6 +52,8 @@ struct PeerHalo {
 struct PeerSync {
     const unsigned long long* wait_flags = nullptr;   // own control words of the awaited phase: [0] lower, [1] upper neighbour
     unsigned long long want = 0;                      // 0: nothing to await
+    const unsigned long long* wait_local = nullptr;   // an additional LOCAL word every edge CTA awaits (own hand-off finished)
+    unsigned long long want_local = 0;
     unsigned long long* sig_lo = nullptr;             // this sweep's flag word at the lower / upper neighbour
     unsigned long long* sig_hi = nullptr;
     unsigned long long sig = 0;
@@ -133,16 +139,23 @@ int launch_gauss_residual(const FieldGeom& G, const double* planes, const int64_
 
 // ---- kernel launchers implemented in particles.cu
 int launch_push_deposit(const PicConst& P, const FieldGeom& G, const CUtensorMap* tmap, int64_t* jacc, Particles src,
-                        Particles dst, const int* perm, const int* cell_start, int* cell_count_new, int* keys, int split,
+                        Particles dst, const int* perm, const int* cell_start, int* mcnt, unsigned char* dirs, int split,
                         LeaveBufs lv, cudaStream_t st, int64_t n_hint);   // n_hint: particles in the slab (picks the sparse-cell variant)
+int launch_count_moves(const PicConst& P, int ywrap, const int* mcnt, int* cell_count, cudaStream_t st);
+int launch_offsets(const PicConst& P, int ywrap, const int* mcnt, const int* start_new, int* offtab, int* cursor, cudaStream_t st);
+int launch_perm_stable(const PicConst& P, int ywrap, const int* cs_old, const unsigned char* dirs, const int* offtab, int* perm,
+                       int64_t n_hint, cudaStream_t st);
+int launch_arrivals(const PicConst& P, const int* keys, int64_t first, int n, int* cursor, const int* start_new, int* perm, cudaStream_t st);
+int launch_leavers(const PicConst& P, Particles o, const int* cs_old, const unsigned char* dirs, const int* mcnt, int* lv_off,
+                   int* cell_count, LeaveBufs lv, cudaStream_t st);
+int launch_segsort(const int* start, int ncells, int* perm, int* scratch, cudaStream_t st);
 int launch_perm_build(const PicConst& P, const int* keys, int64_t n, int* cursor, int* perm, cudaStream_t st);
-int launch_gather(Particles src, Particles dst, int* perm, int64_t n, cudaStream_t st);
+int launch_gather(Particles src, Particles dst, int* perm, int64_t n, const int* n_dev, cudaStream_t st);
 int launch_absorb(const PicConst& P, Particles p, int64_t first, const double* rec, int n, int* cell_count, int* keys,
                   unsigned int* err, cudaStream_t st);
-int launch_count_keys(const PicConst& P, Particles p, int64_t first, int64_t n, int* cell_count, unsigned int* err, cudaStream_t st);
+int launch_count_keys(const PicConst& P, Particles p, int64_t first, int64_t n, int* cell_count, int* keys, unsigned int* err, cudaStream_t st);
 int launch_scan_cells(int* cell_count, int* cell_start, int n_entries, int* block_tmp, cudaStream_t st);
-int launch_scatter(const PicConst& P, Particles src, Particles dst, int64_t n, int* perm_identity_out, int* cursor, cudaStream_t st);
-int launch_crossers(const PicConst& P, const int* cell_start, const int* keys, unsigned long long* out, cudaStream_t st);
+int launch_crossers(const unsigned char* dirs, int64_t n, unsigned long long* out, cudaStream_t st);
 int launch_tile_counts(const PicConst& P, const int* cell_start, int* counts, cudaStream_t st);
 int launch_particle_tiles(const PicConst& P, Particles p, int64_t n, int row0, int* gid, cudaStream_t st);
 int launch_kinetic(Particles p, int64_t n, double* out2, cudaStream_t st);

@@ -16,8 +16,13 @@ struct mpic_sim {
     Particles pa[2] = {};
     int cur = 0;
     int64_t n = 0, cap = 0;
-    int* cell_start = nullptr;     // n_entries + 1
-    int* cell_count = nullptr;     // n_entries (doubles as scatter cursor)
+    int* cell_start = nullptr;     // n_entries + 1: first slot of every cell in the CURRENT sorted order
+    int* cell_start_alt = nullptr; // n_entries + 1: the sort writes the new offsets here (the old ones are still being walked), then swaps
+    int* cell_count = nullptr;     // n_entries: destination histogram of the last push; after the scan: arrival / scatter cursor
+    int* mcnt = nullptr;           // 9 x ncells: per source cell and direction, particles moved by the last push (written by the push)
+    int* offtab = nullptr;         // 9 x ncells: first slot of the particles moving (source cell, direction) in the new order
+    unsigned char* dirs = nullptr; // cap: direction code of every stored particle's last move (written by the push)
+    int* lv_off = nullptr;         // 2 x nx: first record of every slab-edge cell's leavers (nranks > 1)
     int* scan_tmp = nullptr;
     int n_entries = 0;             // ncells + 2 (leave-down, leave-up bins)
     CUtensorMap tmap;               // push kernel: tile + 1-cell ring box on `planes`
@@ -33,7 +38,7 @@ struct mpic_sim {
     int push_split = 4;
     int nsm = 148;
     bool counts_valid = false;     // cell_count holds the destination-cell histogram of the last push
-    int* keys = nullptr;           // cap: destination key of every stored particle (written by the push / absorb kernels)
+    int* keys = nullptr;           // cap: sort key of stored particles in arbitrary order (uploads, arrivals); scratch of the segment sort
     int* perm = nullptr;           // cap: slot of the sorted order -> storage index in pa[cur]
     bool perm_valid = false;       // true: the sorted order is pa[cur] READ THROUGH perm (the sort moved no data; the next push
                                    // gathers); false: pa[cur][0..n) is itself in sorted order

@@ -243,11 +243,27 @@ __device__ __forceinline__ void fy_b_update(double* __restrict__ F, int k, doubl
 }
 
 // current of cell (i,j) with every periodic image folded in (the same sum the E sweep forms; integer adds, any order)
-__device__ __forceinline__ void fy_folded_j(const FieldGeom& G, const int64_t* __restrict__ jacc, int i, int j, int64_t (&jv)[3]) {
+__device__ __forceinline__ void fy_folded_j(const FieldGeom& G, const int64_t* __restrict__ jacc, const PeerHalo& H, int i, int j,
+                                            int64_t (&jv)[3]) {
     const int g = G.g;
-    const int ic = i >= G.nx ? i - G.nx : i, jc = j >= G.nyl ? j - G.nyl : j;       // ring cell beyond the edge -> its interior image
-    const int64_t k = fidx(G, ic, jc);
+    const int ic = i >= G.nx ? i - G.nx : i;                        // ring cell beyond the x edge -> its interior image
     const int xs = ic < g ? G.nx : (ic >= G.nx - g ? -G.nx : 0);
+    if (!G.ywrap) {
+        // slab: the guard rows were handed to the neighbours (peer.cu), rows 0..nyl-1 are complete as they stand; the ring
+        // row nyl is the upper neighbour's row 0
+        const int64_t* a0 = j >= G.nyl ? H.hi_j : jacc;
+        const int64_t pl = j >= G.nyl ? H.hi_jplane : G.plane;
+        const int64_t k = fidx(G, ic, j >= G.nyl ? 0 : j);
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            int64_t v = a0[c * pl + k];
+            if (xs) v += a0[c * pl + k + xs];
+            jv[c] = v;
+        }
+        return;
+    }
+    const int jc = j >= G.nyl ? j - G.nyl : j;
+    const int64_t k = fidx(G, ic, jc);
     const int64_t ys = jc < g ? (int64_t)G.nyl * G.pitch : (jc >= G.nyl - g ? -(int64_t)G.nyl * G.pitch : 0);
 #pragma unroll
     for (int c = 0; c < 3; c++) {
@@ -277,6 +293,14 @@ __global__ void __launch_bounds__(FY_THREADS) fused_yee_kernel(FieldGeom G, cons
             for (int side = 0; side < 2; side++) {
                 if (!(side ? hi_edge : lo_edge)) continue;
                 while (ld_acquire_sys_u64(S.wait_flags + side) < S.want) {
+                    unsigned long long t1;
+                    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+                    if (t1 - t0 > S.timeout_ns) { atomicExch(S.err, 1ull + S.phase); break; }
+                    __nanosleep(32);
+                }
+            }
+            if (S.wait_local) {
+                while (ld_acquire_sys_u64(S.wait_local) < S.want_local) {
                     unsigned long long t1;
                     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
                     if (t1 - t0 > S.timeout_ns) { atomicExch(S.err, 1ull + S.phase); break; }
@@ -331,7 +355,7 @@ __global__ void __launch_bounds__(FY_THREADS) fused_yee_kernel(FieldGeom G, cons
             const int i = x0 - 2 + lx, j = y0 - 1 + ly;
             if (i <= G.nx && j <= G.nyl) {
                 int64_t jv[3];
-                fy_folded_j(G, jacc, i, j, jv);
+                fy_folded_j(G, jacc, H, i, j, jv);
                 if (((jv[0] ^ (jv[0] << 1)) | (jv[1] ^ (jv[1] << 1)) | (jv[2] ^ (jv[2] << 1))) < 0) atomicOr(G.err, MPIC_ERR_JRANGE);   // |acc| >= 2^62
                 nex = fma(-dt, __ll2double_rn(jv[0]) * MPIC_INV_JSCALE, nex);
                 ney = fma(-dt, __ll2double_rn(jv[1]) * MPIC_INV_JSCALE, ney);

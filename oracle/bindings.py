@@ -71,6 +71,7 @@ def load_oracle(omp=False):
     lib.orc_push_deposit.argtypes = [C.POINTER(PicParams)] + [c_dp] * 6 + [c_lp] * 3 + [c_dp] * 6 + [C.c_long]
     lib.orc_apply_current.argtypes = [C.POINTER(PicParams)] + [c_dp] * 3 + [c_lp] * 3
     lib.orc_tile_keys.argtypes = [C.POINTER(PicParams), c_dp, c_dp, C.c_long, c_ip]
+    lib.orc_cell_keys.argtypes = [C.POINTER(PicParams), c_dp, c_dp, C.c_long, c_ip]
     lib.orc_sort_perm.argtypes = [c_ip, C.c_long, C.c_int, c_ip, c_lp]
     lib.orc_deposit_rho.argtypes = [C.POINTER(PicParams), c_dp, c_dp, c_dp, C.c_long, c_lp]
     lib.orc_pic_steps.argtypes = [C.POINTER(PicParams)] + [c_dp] * 6 + [c_dp] * 6 + [c_ip, C.c_long, C.c_int, C.c_int, c_ip, c_lp]
@@ -184,14 +185,15 @@ def field_energy(lib, planes, dx, dy):
 
 
 def pic_steps(lib, P, planes, parts, steps, do_sort=True):
-    """parts: dict x,y,ux,uy,uz,q (float64) and tag (int32), all advanced in place.  Returns (tile counts, J int64 (3,ny,nx))."""
+    """parts: dict x,y,ux,uy,uz,q (float64) and tag (int32), all advanced in place.  Returns (tile counts, J int64 (3,ny,nx)).
+    do_sort: True/1 = stable sort by tile key; 2 = stable sort by (tile, cell in tile), the GPU's slot order."""
     n = parts["x"].shape[0]
     ntiles = (P.nx // P.tnx) * (P.ny // P.tny)
     counts = np.zeros(ntiles, dtype=np.int32)
     J = np.zeros((3, P.ny, P.nx), dtype=np.int64)
     lib.orc_pic_steps(C.byref(P), *[_dp(a) for a in planes],
                       *[_dp(parts[k]) for k in ("x", "y", "ux", "uy", "uz", "q")], _ip(parts["tag"]), n,
-                      steps, 1 if do_sort else 0, _ip(counts), _lp(J))
+                      steps, int(do_sort), _ip(counts), _lp(J))
     return counts, J
 
 
@@ -207,6 +209,13 @@ def push_deposit(lib, P, planes, parts):
 def tile_keys(lib, P, x, y):
     key = np.zeros(x.shape[0], dtype=np.int32)
     lib.orc_tile_keys(C.byref(P), _dp(x), _dp(y), x.shape[0], _ip(key))
+    return key
+
+
+def cell_keys(lib, P, x, y):
+    """(tile, cell in tile) sort key of every particle: the GPU layout's slot order (a refinement of tile_keys)."""
+    key = np.zeros(x.shape[0], dtype=np.int32)
+    lib.orc_cell_keys(C.byref(P), _dp(x), _dp(y), x.shape[0], _ip(key))
     return key
 
 

@@ -82,6 +82,14 @@ static inline int tile_key(const orc_pic_params* P, double x, double y) {
     return (cy / P->tny) * (P->nx / P->tnx) + cx / P->tnx;
 }
 
+/* sort key of the GPU layout: tile-major, cell-in-tile minor -- a REFINEMENT of the tile key (same tile order, so tile
+ * counts and particle-to-tile indices are unchanged); a stable sort by it keeps the previous relative order inside a cell */
+static inline int cell_key(const orc_pic_params* P, double x, double y) {
+    int cx = (int)floor(x * P->inv_dx), cy = (int)floor(y * P->inv_dy);
+    int tr = cy / P->tny, tc = cx / P->tnx;
+    return ((tr * (P->nx / P->tnx) + tc) * P->tny + (cy - tr * P->tny)) * P->tnx + (cx - tc * P->tnx);
+}
+
 static inline double wrap_pos(double xn, double box, double inv_d, int n) {
     double xw = xn;
     if (xw < 0.0) xw = xw + box; else if (xw >= box) xw = xw - box;
@@ -217,6 +225,13 @@ void orc_tile_keys(const orc_pic_params* P, const double* x, const double* y, lo
     for (long p = 0; p < n; p++) key[p] = tile_key(P, x[p], y[p]);
 }
 
+void orc_cell_keys(const orc_pic_params* P, const double* x, const double* y, long n, int* key) {
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static)
+#endif
+    for (long p = 0; p < n; p++) key[p] = cell_key(P, x[p], y[p]);
+}
+
 /* Stable counting sort by tile key.  counts has ntiles entries; perm[new_slot] = old_slot. */
 void orc_sort_perm(const int* key, long n, int ntiles, int* counts, long* perm) {
 #ifdef _OPENMP
@@ -305,9 +320,19 @@ void orc_pic_steps(const orc_pic_params* P, double* ex, double* ey, double* ez, 
         orc_e_sweep_global(ex, ey, ez, bx, by, bz, P->nx, P->ny, P->dt, P->dx, P->dy, 0);
         orc_apply_current(P, ex, ey, ez, J, J + nc, J + 2 * nc);
         orc_b_sweep_global(ex, ey, ez, bx, by, bz, P->nx, P->ny, P->dt, P->dx, P->dy, 0, 0);
-        if (do_sort) {
+        if (do_sort == 2) {       /* stable sort by (tile, cell in tile): the slot order of the GPU layout */
+            int ncell = P->nx * P->ny;
+            int* ccount = (int*)malloc((size_t)ncell * sizeof(int));
+            orc_cell_keys(P, x, y, n, key);
+            orc_sort_perm(key, n, ncell, ccount, perm);
+            int cpt = P->tnx * P->tny;
+            for (int t = 0; t < ntiles; t++) { int c = 0; for (int k = 0; k < cpt; k++) c += ccount[(size_t)t * cpt + k]; counts[t] = c; }
+            free(ccount);
+        } else if (do_sort) {
             orc_tile_keys(P, x, y, n, key);
             orc_sort_perm(key, n, ntiles, counts, perm);
+        }
+        if (do_sort) {
             double* arrs[6] = { x, y, ux, uy, uz, q };
             for (int a = 0; a < 6; a++) {
                 double* src = arrs[a];

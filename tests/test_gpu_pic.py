@@ -277,3 +277,92 @@ def test_upload_rejects_positions_outside_the_box():
     assert s.num_particles == good["x"].shape[0]
     rc = m.lib().mpic_upload_particles(s.h, 4, None, None, None, None, None, None, None)
     assert rc == -1 and b"null" in m.lib().mpic_last_error()
+
+
+@pytest.mark.parametrize("cfg", [(32, 32, 16, 16, 8, 0.3, 0.0), (48, 32, 8, 8, 40, 0.6, 0.2), (64, 32, 16, 16, 3, 0.9, 0.0)])
+def test_sort_is_stable_and_reproducible(cfg):
+    """SURVEY.md B.8 / VERDICT r1 item 7: after 10 steps the slot order (the order a download returns) equals the oracle's
+    STABLE sort by (tile, cell) element-wise -- tag[] and every component --, and two identical runs return identical arrays.
+    Covers dense cells (two chunks per cell), sparse ones (lane groups of 8) and many cell crossers per step."""
+    nx, ny, tnx, tny, ppc, u_th, ts = cfg
+    outs = []
+    for rep in range(2):
+        s, P, parts, pl = _setup(nx, ny, tnx, tny, ppc, u_th, seed=5, two_stream=ts)
+        shuf = np.random.default_rng(1).permutation(parts["x"].shape[0])       # arbitrary upload order
+        up = {k: np.ascontiguousarray(v[shuf]) for k, v in parts.items()}
+        s.upload_planes(pl)
+        s.upload_particles(up)
+        if rep == 0:                                   # the upload itself sorts stably (per-cell ascending storage index)
+            got0 = s.download_particles()
+            k0 = ob.cell_keys(lib, P, up["x"], up["y"])
+            o0 = np.argsort(k0, kind="stable")
+            assert np.array_equal(got0["tag"], up["tag"][o0])
+        s.pic_steps(10)
+        outs.append(s.download_particles())
+        s.close()
+    for k in outs[0]:
+        assert np.array_equal(outs[0][k], outs[1][k]), k
+    # oracle: same upload order, stable sort by cell key once (the upload), then 10 steps each followed by the stable cell sort
+    want = {k: np.ascontiguousarray(v[shuf][o0]) for k, v in parts.items()}
+    wf = [a.copy() for a in pl]
+    ob.pic_steps(lib, P, wf, want, 10, do_sort=2)
+    for k in ("tag", "x", "y", "ux", "uy", "uz", "q"):
+        assert np.array_equal(outs[0][k], want[k]), k
+
+
+@pytest.mark.parametrize("cfg", [(32, 32, 16, 16, 40, 0.6, 0.0), (64, 32, 16, 16, 64, 0.05, 0.2), (48, 30, 8, 6, 30, 0.9, 0.0),
+                                 (64, 64, 32, 32, 26, 0.7, 0.0)])
+def test_packed_walk_bit_exact(cfg):
+    """Dense slabs (>= 24 particles per cell) run push_packed_kernel: warps walk contiguous slot ranges across cell boundaries
+    (carry cell + masked flushes).  Cases: half the particles crossing a cell face per step, a cold two-stream lattice (every
+    chunk boundary is a cell boundary), a generic (non-templated) tile shape, 32x32 tiles."""
+    nx, ny, tnx, tny, ppc, u_th, ts = cfg
+    s, P, parts, pl = _setup(nx, ny, tnx, tny, ppc, u_th, seed=9, two_stream=ts, fields=0.02)
+    s.upload_planes(pl)
+    s.upload_particles(parts)
+    s.pic_steps(5)
+    want, wf = copy_parts(parts), [a.copy() for a in pl]
+    counts, _ = ob.pic_steps(lib, P, wf, want, 5)
+    got, want = by_tag(s.download_particles()), by_tag(want)
+    for k in ("x", "y", "ux", "uy", "uz"):
+        assert np.array_equal(got[k], want[k]), k
+    for a, b in zip(s.download_planes(), wf):
+        assert np.array_equal(a, b)
+    assert np.array_equal(s.tile_counts(), counts)
+
+
+_VARIANT_SCRIPT = r"""
+import sys, numpy as np
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, sys.argv[1] + "/tests")
+from oracle import bindings as ob
+from util import pkg, plasma, by_tag, copy_parts
+lib = ob.load_oracle()
+nx, ny, tn, dx = 48, 32, 16, 0.1
+dt = pkg().courant_dt(dx, dx)
+P = ob.make_params(lib, nx, ny, tn, tn, dx, dx, dt)
+for ppc in (7, 33):
+    parts = plasma().load_uniform(nx, ny, tn, tn, dx, dx, ppc, u_th=0.5, seed=2)
+    rng = np.random.default_rng(3)
+    pl = [0.02 * rng.standard_normal((ny, nx)) for _ in range(6)]
+    s = pkg().Sim(nx, ny, tn, tn, dx, dx, dt, max_particles=parts["x"].shape[0] + 64)
+    s.upload_planes(pl); s.upload_particles(parts); s.pic_steps(6)
+    raw = s.download_particles()
+    want, wf = copy_parts(parts), [a.copy() for a in pl]
+    ob.pic_steps(lib, P, wf, want, 6, do_sort=2)
+    for k in ("tag", "x", "y", "ux", "uy", "uz"):
+        assert np.array_equal(raw[k], want[k]), (ppc, k)
+    for a, b in zip(s.download_planes(), wf):
+        assert np.array_equal(a, b)
+print("variant ok")
+"""
+
+
+@pytest.mark.parametrize("gl", ["0", "1", "8", "16", "32"])
+def test_every_push_variant_bit_exact_and_same_slot_order(gl):
+    """MPIC_PUSH_GL forces one walk (0 adaptive lane groups, 1 packed, 8/16/32 fixed lane groups) for sparse AND dense cells:
+    each must give the oracle's bits and the oracle's stable slot order (the variant is read once per process -> subprocess)."""
+    import os, subprocess, sys
+    from util import ROOT
+    env = dict(os.environ, MPIC_PUSH_GL=gl)
+    r = subprocess.run([sys.executable, "-c", _VARIANT_SCRIPT, ROOT], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "variant ok" in r.stdout, r.stdout + r.stderr

@@ -159,3 +159,29 @@ def test_two_stream_growth_rate_of_a_seeded_mode():
     theory = np.sqrt(wb2 * (np.sqrt(4 * x + 1) - (x + 1)))
     assert abs(theory - 0.343) < 2e-3
     assert abs(rate - theory) < 0.05 * theory, (rate, theory)
+
+
+def test_cell_key_sort_is_a_stable_refinement_of_the_tile_sort():
+    """do_sort=2 (the GPU's slot order): keys non-decreasing, same tile counts and the same particle set per tile as the
+    tile-key sort, and equal to one numpy stable argsort by cell key per step."""
+    nx, ny, tnx, tny = 32, 24, 8, 4; dx = dy = 0.1; dt = 0.035
+    P = ob.make_params(lib, nx, ny, tnx, tny, dx, dy, dt)
+    parts = plasma.load_uniform(nx, ny, tnx, tny, dx, dy, 5, u_th=0.5, seed=4)
+    a = {k: v.copy() for k, v in parts.items()}
+    b = {k: v.copy() for k, v in parts.items()}
+    c = {k: v.copy() for k, v in parts.items()}
+    ca, _ = ob.pic_steps(lib, P, _zero_planes(nx, ny), a, 4, do_sort=1)
+    cb, _ = ob.pic_steps(lib, P, _zero_planes(nx, ny), b, 4, do_sort=2)
+    assert np.array_equal(ca, cb)
+    kb = ob.cell_keys(lib, P, b["x"], b["y"])
+    assert (np.diff(kb) >= 0).all()
+    assert np.array_equal(ob.tile_keys(lib, P, b["x"], b["y"]), kb // (tnx * tny))
+    ta, tb = ob.tile_keys(lib, P, a["x"], a["y"]), ob.tile_keys(lib, P, b["x"], b["y"])
+    for t in range(len(ca)):
+        assert sorted(a["tag"][ta == t]) == sorted(b["tag"][tb == t])
+    pl = _zero_planes(nx, ny)
+    for _ in range(4):
+        ob.pic_steps(lib, P, pl, c, 1, do_sort=False)
+        perm = np.argsort(ob.cell_keys(lib, P, c["x"], c["y"]), kind="stable")
+        c = {k: np.ascontiguousarray(v[perm]) for k, v in c.items()}
+    assert np.array_equal(c["tag"], b["tag"]) and np.array_equal(c["x"], b["x"])
