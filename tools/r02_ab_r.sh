@@ -1,0 +1,4 @@
+OUT=gpurun_out/$1
+timeout 900 python -m pytest tests/test_gpu_pic.py -x -q 2>&1 | tail -2
+for r in quiet sat thermal c4; do timeout 300 python tools/push_ab.py $r >> $OUT; done
+cat $OUT
