@@ -17,6 +17,7 @@ the repo's scalar FP64 oracle port with OpenMP over particles ("kind": "port") o
 for exactly the --warmup/--steps it is given (bounded sample only when the state would not fit the host; stated).
 """
 import argparse
+import atexit
 import contextlib
 import importlib
 import json
@@ -55,9 +56,9 @@ WORKLOADS = {
 PUSH_BYTES_SURVEY = 90.0
 PUSH_BYTES_FUSED_REORDER = 104.0
 # constant, NOT measured by the run that prints it: dram__bytes_read+write of one push launch in the saturated regime,
-# ncu --set full, profiles/r02a_ncu_full_push_saturated_raw.csv: 1.072 GB + 0.949 GB over 16 777 216 particles
-NCU_TRAFFIC_BYTES_PER_PARTICLE = 120.5
-SORT_BYTES_PER_PARTICLE = 8.0      # what is left of the sort: keys read (4) + permutation written (4); scan is per cell
+# ncu --set full, profiles/r02q_ncu_full_push_packed_saturated_raw.csv: 1.045 GB + 0.869 GB over 16 777 216 particles
+NCU_TRAFFIC_BYTES_PER_PARTICLE = 114.1
+SORT_BYTES_PER_PARTICLE = 5.0      # what is left of the sort: direction codes read (1) + permutation written (4); the rest is per cell
 YEE_BYTES_3SWEEP = 216.0           # reference-faithful half-B, E, half-B: 3 x 72 B per cell
 YEE_BYTES_ALGO = 144.0             # SURVEY.md section 8(d) algorithmic figure (2 sweeps)
 YEE_BYTES_FUSED = 96.0             # fused step: every plane read once, written once
@@ -109,42 +110,67 @@ def measured_peak():
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons DURING the timed region."""
+    """nvidia-smi clocks + throttle reasons DURING the timed region.  ONE nvidia-smi process per bench run, started before any
+    GPU work (its start-up on a fresh box takes longer than a 13 ms timed region), every line stamped on arrival; a
+    `with ClockSampler(i) as clk:` block marks a window and `clk.summary()` reports the samples that fell inside it (widened
+    to the nearest samples, and saying so, when the window was shorter than the 100 ms sampling period)."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    _shared = {}
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index = index
+        self.t0 = self.t1 = None
+        self.log = ClockSampler._shared.get(index)
+        if self.log is None:
+            self.log = ClockSampler._shared[index] = {"rows": [], "proc": None}
+            try:
+                proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                         "-i", str(index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                self.log["proc"] = proc
+                atexit.register(ClockSampler.stop_all)          # the sampler must never outlive the bench process
+                threading.Thread(target=self._read, args=(proc, self.log["rows"]), daemon=True).start()
+            except Exception:
+                pass
+
+    @staticmethod
+    def _read(proc, rows):
+        for line in proc.stdout:
+            rows.append((time.time(), [c.strip() for c in line.split(",")]))
 
     def __enter__(self):
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
-                                          "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True)
-            self.t.start()
-        except Exception:
-            self.proc = None
+        self.t0 = time.time()
         return self
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
-
     def __exit__(self, *a):
-        if self.proc:
-            t0 = time.time()
-            while len(self.rows) < 2 and time.time() - t0 < 1.5:      # a short timed region: wait for nvidia-smi's first lines
+        self.t1 = time.time()
+        if self.log["proc"]:
+            t = time.time()
+            while not any(ts >= self.t1 for ts, _ in self.log["rows"]) and time.time() - t < 3.0:   # one sample past the window
                 time.sleep(0.05)
-            self.proc.terminate()
-            self.t.join(timeout=2)
+
+    @classmethod
+    def stop_all(cls):
+        for log in cls._shared.values():
+            if log["proc"]:
+                log["proc"].terminate()
+        cls._shared.clear()
 
     def summary(self):
-        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        rows = [(ts, r) for ts, r in list(self.log["rows"]) if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        inside = [r for ts, r in rows if self.t0 <= ts <= self.t1]
+        how = "inside the window"
+        if not inside and rows:                   # window shorter than the sampling period: the samples on either side of it
+            before = [r for ts, r in rows if ts < self.t0][-1:]
+            after = [r for ts, r in rows if ts > self.t1][:1]
+            inside = before + after
+            how = "window shorter than the 100 ms sampling period: nearest sample on either side"
+        sm = [float(r[0]) for r in inside]
+        mx = [float(r[1]) for r in inside if r[1].replace(".", "").isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[k] for r in self.rows if len(r) >= 6 for k in range(4) if r[2 + k].lower().startswith("active")})
+        reasons = sorted({names[k] for r in inside for k in range(4) if r[2 + k].lower().startswith("active")})
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
-                "samples": len(sm)}
+                "samples": len(sm), "sampled": how, "window_s": round(self.t1 - self.t0, 3)}
 
 
 # ------------------------------------------------------------------------------------------------ CPU legs
@@ -361,12 +387,12 @@ def time_pic(sim, torch, K, W):
 
 def push_roofline(n, t, peak, peak_how):
     gbs = n * PUSH_BYTES_SURVEY / (t["push_ms"] * 1e-3) / 1e9
-    return {"bound": "hbm", "kernel": "push_deposit_kernel", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
+    return {"bound": "hbm", "kernel": "push_packed_kernel (dense slabs; push_deposit_kernel for sparse ones) + the 9 us count_moves launch timed with it", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
             "bytes_per_particle": PUSH_BYTES_SURVEY,
             "frac_104B": gbs / peak * PUSH_BYTES_FUSED_REORDER / PUSH_BYTES_SURVEY,
             "traffic": NCU_TRAFFIC_BYTES_PER_PARTICLE * n,
-            "traffic_source": "CONSTANT from one ncu --set full capture of this kernel in the saturated regime (profiles/r02a_ncu_full_push_saturated_raw.csv: "
-                              "120.5 B/particle), scaled by the particle count; not measured by this run",
+            "traffic_source": "CONSTANT from one ncu --set full capture of this kernel in the saturated regime (profiles/r02q_ncu_full_push_packed_saturated_raw.csv: "
+                              "114.1 B/particle), scaled by the particle count; not measured by this run",
             "pushes_per_s_kernel_only": n / (t["push_ms"] * 1e-3), "peak_source": peak_how,
             "sort_gbs": n * SORT_BYTES_PER_PARTICLE / (t["sort_ms"] * 1e-3) / 1e9,
             "note": "frac: SURVEY.md 8(d)'s 88 B push + 2.3 B grid = 90 B/particle.  frac_104B: what this kernel must move, since it is also the "
@@ -435,6 +461,7 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if world != args.gpus:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun --nproc-per-node {args.gpus}")
+    ClockSampler(local)                    # start nvidia-smi now: its start-up must not eat the first timed window
     torch.cuda.set_device(local)
     w = WORKLOADS[args.workload]
     K, W = args.steps, max(args.warmup, 3)
@@ -514,6 +541,7 @@ def main():
             if cb:
                 out["yee"]["cpu_baseline"] = cb
         out["cpu_baseline"] = cpu_baseline_pic(w)
+    ClockSampler.stop_all()
     print(json.dumps(out))
 
 

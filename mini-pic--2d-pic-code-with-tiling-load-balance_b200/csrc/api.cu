@@ -206,6 +206,11 @@ int mpic_create(const mpic_params* p, mpic_sim** out) {
     CUDA_TRY(cudaGetDeviceProperties(&prop, p->device));
     s->nsm = prop.multiProcessorCount;
     CUDA_TRY(cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking));
+    if (p->nranks == 1 && !getenv("MPIC_NO_SORT_OVERLAP")) {
+        CUDA_TRY(cudaStreamCreateWithFlags(&s->st_sort, cudaStreamNonBlocking));
+        CUDA_TRY(cudaEventCreateWithFlags(&s->ev_push, cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&s->ev_sort, cudaEventDisableTiming));
+    }
     CUDA_TRY(cudaMalloc(&s->planes, (size_t)6 * G.plane * 8));
     CUDA_TRY(cudaMemsetAsync(s->planes, 0, (size_t)6 * G.plane * 8, s->st));
     CUDA_TRY(cudaMalloc(&s->jacc, (size_t)3 * G.plane * 8));
@@ -285,6 +290,7 @@ int mpic_destroy(mpic_sim* s) {
     cudaFree(s->halo_send); cudaFree(s->halo_recv); cudaFree(s->lv.count);
     for (int d = 0; d < 2; d++) cudaFree(s->lv.rec[d]);
     cudaFree(s->arrive_blk);
+    if (s->st_sort) { cudaStreamDestroy(s->st_sort); cudaEventDestroy(s->ev_push); cudaEventDestroy(s->ev_sort); }
     if (s->pipe_up) {
         cudaStreamDestroy(s->pipe_up); cudaStreamDestroy(s->pipe_down);
         for (int c = 0; c < MPIC_PIPE_MAX; c++) { cudaEventDestroy(s->pipe_ev_up[c]); cudaEventDestroy(s->pipe_ev_done[c]); }
@@ -567,10 +573,18 @@ static int sort_all(mpic_sim* s, bool counted) {
     s->counts_valid = false;
     const int64_t total = s->n + s->arrived;
     if (counted) {
-        TRY(launch_scan_cells(s->cell_count, s->cell_start_alt, s->n_entries, s->scan_tmp, s->st));
-        TRY(launch_offsets(s->P, s->G.ywrap, s->mcnt, s->cell_start_alt, s->offtab, s->cell_count, s->st));
-        TRY(launch_perm_stable(s->P, s->G.ywrap, s->cell_start, s->dirs, s->offtab, s->perm, s->n, s->st));
-        TRY(launch_arrivals(s->P, s->keys, s->n, (int)s->arrived, s->cell_count, s->cell_start_alt, s->perm, s->st));
+        // single slab: on the sort stream, behind the push only -- whatever was queued on the main stream since (the field
+        // update: it touches the planes and the current, the sort the move counts and the permutation) runs next to it; the
+        // main stream continues once both are done
+        cudaStream_t st = s->st;
+        if (s->st_sort && s->arrived == 0) { st = s->st_sort; CUDA_TRY(cudaStreamWaitEvent(st, s->ev_push, 0)); }
+        if (!s->moves_counted) { TRY(launch_count_moves(s->P, s->G.ywrap, s->mcnt, s->cell_count, st)); s->launches++; }
+        s->moves_counted = false;
+        TRY(launch_scan_cells(s->cell_count, s->cell_start_alt, s->n_entries, s->scan_tmp, st));
+        TRY(launch_offsets(s->P, s->G.ywrap, s->mcnt, s->cell_start_alt, s->offtab, s->cell_count, st));
+        TRY(launch_perm_stable(s->P, s->G.ywrap, s->cell_start, s->dirs, s->offtab, s->perm, s->n, st));
+        TRY(launch_arrivals(s->P, s->keys, s->n, (int)s->arrived, s->cell_count, s->cell_start_alt, s->perm, st));
+        if (st != s->st) { CUDA_TRY(cudaEventRecord(s->ev_sort, st)); CUDA_TRY(cudaStreamWaitEvent(s->st, s->ev_sort, 0)); }
         std::swap(s->cell_start, s->cell_start_alt);
         s->perm_valid = true;
         s->launches += 5 + (s->arrived > 0 ? 2 : 0);
@@ -666,8 +680,10 @@ int mpic_push_deposit(mpic_sim* s) {
     s->perm_valid = false;
     // destination histogram of the push (a gather over the move counts, no atomics); slab leavers: their records are written in
     // slot order into the send buffers, their counts into lv.count and the two leaver bins of the histogram
-    TRY(launch_count_moves(s->P, s->G.ywrap, s->mcnt, s->cell_count, s->st));
-    s->launches += 2;
+    s->launches++;
+    s->moves_counted = false;
+    if (s->st_sort) CUDA_TRY(cudaEventRecord(s->ev_push, s->st));     // single slab: the histogram is formed by the sort, on its stream
+    else { TRY(launch_count_moves(s->P, s->G.ywrap, s->mcnt, s->cell_count, s->st)); s->launches++; s->moves_counted = true; }
     if (s->prm.nranks > 1) {
         TRY(launch_leavers(s->P, s->pa[s->cur], s->cell_start, s->dirs, s->mcnt, s->lv_off, s->cell_count, s->lv, s->st));
         s->launches += 2;

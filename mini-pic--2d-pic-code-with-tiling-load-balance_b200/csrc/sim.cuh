@@ -79,6 +79,10 @@ struct mpic_sim {
     cudaEvent_t ev_counts = nullptr;
     // ---- pipelined host-buffer step (api.cu: pic_step_host_pipelined)
     cudaStream_t pipe_up = nullptr, pipe_down = nullptr;
+    // single slab: the sort after a push runs on its own stream, next to the field update (neither reads what the other writes)
+    cudaStream_t st_sort = nullptr;
+    cudaEvent_t ev_push = nullptr, ev_sort = nullptr;
+    bool moves_counted = false;    // cell_count already holds the destination histogram of the last push (count_moves ran)
     cudaEvent_t pipe_ev_up[MPIC_PIPE_MAX] = {}, pipe_ev_done[MPIC_PIPE_MAX] = {}, pipe_ev_free = nullptr;
     int* pipe_count = nullptr;     // per-chunk cell histogram / scatter cursor
     int* pipe_start = nullptr;     // per-chunk cell offsets (relative to the chunk's first slot)

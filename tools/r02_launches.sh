@@ -1,8 +1,9 @@
-set -x
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -s 200 -c 40 --csv --log-file gpurun_out/r02h_launches.csv python tools/prof_push.py 40 0.05 0.0 > gpurun_out/ncu_l.log 2>&1
-python - <<'PY'
-import csv
-rows=list(csv.reader(open('gpurun_out/r02h_launches.csv')))
+# launch list (per-kernel durations, serialised by ncu) of steady-state PIC steps: bash tools/r02_launches.sh OUT.csv [prof_push args]
+OUT=${1:-gpurun_out/r02h_launches.csv}; shift
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -s ${SKIP:-200} -c 60 --csv --log-file $OUT python tools/prof_push.py "$@" > gpurun_out/ncu_l.log 2>&1
+python - $OUT <<'PY'
+import csv, sys
+rows=list(csv.reader(open(sys.argv[1])))
 hdr=[i for i,r in enumerate(rows) if r and r[0]=='ID'][0]
 h=rows[hdr]; kn=h.index('Kernel Name'); mv=h.index('Metric Value')
 agg={}
