@@ -11,6 +11,7 @@
 #include "minipic_compat.h"
 #include "../include/minipic_b200.h"
 #include <sys/stat.h>
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -45,6 +46,9 @@ struct Options {
     double beam_density = 0.0, beam_lo = 0.45, beam_hi = 0.55, beam_drift = 0.5, beam_uth = 0.01;
     unsigned long long seed = 12345;
     int diag_every = 0;
+    int rebalance_every = 0;                // > 0: every K steps re-partition the tile rows over the GPUs when it pays (mpic_ring_rebalance)
+    double rebalance_w_cell = 8.0, rebalance_min_gain = 0.05;
+    bool async_dump = false;                // dumps leave the step path: D2H on a side stream + writer thread (mpic_dump_fields_async)
     bool quiet = false;
 };
 
@@ -53,7 +57,7 @@ void usage() {
               "      [--sim-time t | --steps n] [--cfl f] [--save-frequency k] [--ic test1|test2|test3|zero] [--out dir]\n"
               "      [--gpus N] [--scheme 0|1 --fma 0|1] [--no-migrate-demo]\n"
               "      [--ppc n --uth u --two-stream u0 --drift-x u | --beam-density d --beam-lo f --beam-hi f --beam-drift u --beam-uth u]\n"
-              "      [--seed s] [--diag-every k] [--quiet]\n"
+              "      [--seed s] [--diag-every k] [--rebalance-every k --rebalance-w-cell w --rebalance-min-gain f] [--async-dump] [--quiet]\n"
               "defaults = the literals of the reference's PIC_2D.cpp (450x450, 9 ranks x 36 tiles of 25x25, Test-3 pulse, t=500)");
 }
 
@@ -76,6 +80,9 @@ bool parse(int argc, char** argv, Options& o) {
         else if (a == "--beam-hi") o.beam_hi = atof(val()); else if (a == "--beam-drift") o.beam_drift = atof(val());
         else if (a == "--beam-uth") o.beam_uth = atof(val());
         else if (a == "--seed") o.seed = strtoull(val(), nullptr, 10); else if (a == "--diag-every") o.diag_every = atoi(val());
+        else if (a == "--rebalance-every") o.rebalance_every = atoi(val()); else if (a == "--rebalance-w-cell") o.rebalance_w_cell = atof(val());
+        else if (a == "--rebalance-min-gain") o.rebalance_min_gain = atof(val());
+        else if (a == "--async-dump") o.async_dump = true;
         else if (a == "--quiet") o.quiet = true;
         else if (a == "--help" || a == "-h") { usage(); std::exit(0); }
         else { std::fprintf(stderr, "unknown option %s\n", a.c_str()); usage(); return false; }
@@ -198,12 +205,21 @@ int main(int argc, char** argv) {
     mkdirs(o.out);
     // which slabs hold tiles of which logical rank (a rank's tiles span several slabs when ranks do not nest in slabs)
     vector<vector<int>> tiles_on(o.ranks, vector<int>(N, 0));
-    for (int r = 0; r < N; r++) {
-        int row0, nrows;
-        mpic_slab_rows(globalTileRows, N, r, &row0, &nrows);
-        for (int gr = row0; gr < row0 + nrows; gr++)
-            for (int gc = 0; gc < globalTileCols; gc++) tiles_on[owner[getGlobalID(gr, gc, globalTileCols)]][r]++;
-    }
+    auto slab_of_row = [&](int gr) {                     // the rows a handle owns change when the load balancer runs
+        for (int r = 0; r < N; r++) { int row0, nrows; mpic_get_rows(sims[r], &row0, &nrows); if (gr >= row0 && gr < row0 + nrows) return r; }
+        return 0;
+    };
+    auto recount_tiles_on = [&]() {
+        for (auto& v : tiles_on) std::fill(v.begin(), v.end(), 0);
+        for (int gr = 0; gr < globalTileRows; gr++) {
+            const int r = slab_of_row(gr);
+            for (int gc = 0; gc < globalTileCols; gc++) {
+                const int own = owner[getGlobalID(gr, gc, globalTileCols)];
+                if (own >= 0 && own < o.ranks) tiles_on[own][r]++;
+            }
+        }
+    };
+    recount_tiles_on();
     auto dump = [&](long step) {
         for (int rank = 0; rank < o.ranks; rank++) {
             int holders = 0;
@@ -212,8 +228,9 @@ int main(int argc, char** argv) {
                 if (N > 1 && tiles_on[rank][r] == 0 && !(holders == 0 && r == 0)) continue;
                 std::string fn = o.out + "/fields_rank_" + std::to_string(rank) + (holders > 1 ? "_gpu_" + std::to_string(r) : "") +
                                  "_step_" + std::to_string(step) + ".h5";
-                must(mpic_dump_fields(sims[r], fn.c_str(), rank), "mpic_dump_fields");
-            }
+                if (o.async_dump && o.ranks == 1) must(mpic_dump_fields_async(sims[r], fn.c_str(), rank), "mpic_dump_fields_async");
+                else must(mpic_dump_fields(sims[r], fn.c_str(), rank), "mpic_dump_fields");   // one dump in flight per handle: several
+            }                                                                                 // logical ranks per slab stay synchronous
         }
     };
     auto diagnostics = [&](long step) {
@@ -238,6 +255,7 @@ int main(int argc, char** argv) {
         if (o.save_frequency > 0) next = std::min(next, (step / o.save_frequency + 1) * (long)o.save_frequency);
         if (o.diag_every > 0) next = std::min(next, (step / o.diag_every + 1) * (long)o.diag_every);
         if (o.migrate_demo && o.ranks == 9 && step < 5) next = std::min(next, 5L);
+        if (o.rebalance_every > 0 && N > 1) next = std::min(next, (step / o.rebalance_every + 1) * (long)o.rebalance_every);
         const int k = (int)(next - step);
         if (N == 1) must(o.ppc > 0 ? mpic_pic_steps(sims[0], k) : mpic_field_steps(sims[0], k), "time step");
         else must(o.ppc > 0 ? mpic_ring_pic_steps(sims.data(), N, k) : mpic_ring_field_steps(sims.data(), N, k), "time step (ring)");
@@ -248,7 +266,7 @@ int main(int argc, char** argv) {
             for (int src = 0; src < 3; src++) {
                 const int gRow = tileGlobalRow(src / C, tileRows, 3 / tileCols), gCol = tileGlobalCol(src % C, tileCols, 3 % tileCols);
                 const int gid = getGlobalID(gRow, gCol, globalTileCols);
-                for (int r = 0; r < N; r++) { int row0, nrows; mpic_slab_rows(globalTileRows, N, r, &row0, &nrows); if (gRow >= row0 && gRow < row0 + nrows) { tiles_on[owner[gid]][r]--; tiles_on[3][r]++; } }
+                { const int r = slab_of_row(gRow); tiles_on[owner[gid]][r]--; tiles_on[3][r]++; }
                 owner[gid] = 3;
                 for (int r = 0; r < N; r++) must(mpic_migrate_tile(sims[r], gid, 3), "mpic_migrate_tile");
                 if (!o.quiet) {
@@ -257,10 +275,29 @@ int main(int argc, char** argv) {
                 }
             }
         }
+        // --- Phase G as a load balancer (the policy the report leaves as future work, p.10): every K steps the tile rows are
+        // re-partitioned over the GPUs when the most loaded slab gets >= min_gain lighter; rows travel WITH their fields and
+        // particles, device to device, and the handles change their rows in place
+        if (o.rebalance_every > 0 && N > 1 && step % o.rebalance_every == 0 && step < total_steps) {
+            int changed = 0;
+            vector<int> rows(2 * (size_t)N);
+            auto tb = std::chrono::steady_clock::now();
+            must(mpic_ring_rebalance(sims.data(), N, o.rebalance_w_cell, o.rebalance_min_gain, &changed, rows.data()), "mpic_ring_rebalance");
+            if (changed) {
+                must(mpic_get_owner(sims[0], owner.data()), "mpic_get_owner");
+                recount_tiles_on();
+                if (!o.quiet) {
+                    std::printf("step %ld: rebalanced in %.2f ms, tile rows per GPU:", step,
+                                1e3 * std::chrono::duration<double>(std::chrono::steady_clock::now() - tb).count());
+                    for (int r = 0; r < N; r++) std::printf(" %d", rows[2 * r + 1]);
+                    std::printf("\n");
+                }
+            }
+        }
         if (o.save_frequency > 0 && step % o.save_frequency == 0) dump(step);
         if (o.diag_every > 0 && step % o.diag_every == 0) diagnostics(step);
     }
-    for (int r = 0; r < N; r++) must(mpic_sync(sims[r]), "mpic_sync");
+    for (int r = 0; r < N; r++) { must(mpic_sync(sims[r]), "mpic_sync"); must(mpic_dump_wait(sims[r]), "mpic_dump_wait"); }
     const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 
     must(mpic_write_params((o.out + "/params.txt").c_str(), o.box_x, o.box_y, o.nx, o.ny, o.guard, interior_nx, interior_ny,

@@ -31,7 +31,7 @@ extern "C" {
 const char* mpic_last_error(void);
 int mpic_device_count(void);
 /* ABI version; bumped whenever a signature or struct below changes. */
-int mpic_abi_version(void);   /* currently 2 */
+int mpic_abi_version(void);   /* currently 3 */
 
 /* ============================================================ integer helpers (host, exact)
  * Replace Auxiliar_functions.h:55-65 (findBestGrid, findBestTileGrid, tileGlobalRow/Col, getGlobalID, getGlobalRowCol,
@@ -172,6 +172,10 @@ int mpic_peer_field_step_fused(mpic_sim* s);
 int mpic_peer_step_begin(mpic_sim* s);      /* push+deposit, hand-off, J add, Yee phases: everything enqueued, no host wait */
 int mpic_peer_step_end(mpic_sim* s);        /* migration counts (the one host wait), arrivals absorbed, tile sort */
 
+/* Unmap both neighbours (closes the CUDA-IPC mappings, drops the flags); the handle keeps its own state.  Called on EVERY rank
+ * before any rank frees or re-partitions memory the others have mapped (mpic_reslab_apply, mpic_destroy); idempotent. */
+int mpic_peer_disconnect(mpic_sim* s);
+
 /* Harness: per-phase device times of mpic_peer_step_begin/_end (events on the handle's stream; adds a host wait per step).
  * enable 1 = start/reset, 0 = stop, -1 = read only.  out_ms[11] = mean ms of {wait for the neighbours' last phase, push+deposit,
  * hand-off, -, -, first half-B, -, E, -, second half-B, migration counts + absorb + tile sort}. */
@@ -218,6 +222,49 @@ int mpic_get_owner(mpic_sim* s, int* owner /* global tiles */);
 int mpic_set_owner(mpic_sim* s, const int* owner /* global tiles */);
 int mpic_migrate_tile(mpic_sim* s, int gid, int dest_rank);
 
+/* ---- run-time load balancing: cost-driven re-partition of the tile rows over the slabs, on the device.
+ * Replaces the mechanism removeTileFromRank / addTileToRank (Auxiliar_functions.cpp:242-272: MPI_Send/Recv of one tile's grid, the
+ * particle vector is dropped) and the hard-coded trigger of PIC_2D.cpp:399-412; the policy is the one the reference leaves as
+ * future work (Report p.10).  A tile row is one contiguous slot range of every particle array (particles are tile-sorted) and
+ * one contiguous row block of every field plane, so moving it is a handful of device-to-device copies over NVLink -- no host
+ * staging, no new handle: the handle changes row0 / nrows IN PLACE.
+ *
+ * Policy (host, exact).  mpic_partition_rows: contiguous partition of n rows with the given costs into nranks non-empty slabs
+ * minimising the most expensive slab (binary search on the bottleneck + greedy sweep); rows_out[2*k] = first row, [2*k+1] = rows.
+ * mpic_rebalance_plan: cost of a tile row = its particles + w_cell * cells_per_tile_row (the per-cell work of the push and
+ * the Yee sweeps does not vanish in empty tiles; w_cell ~ 8 on B200).  Returns 1 when new_rows differs from
+ * old_rows AND lowers the bottleneck by more than min_gain (fraction), 0 when the partition should stay (new_rows = old_rows),
+ * < 0 on error.  cost[0] / cost[1] (optional): bottleneck cost of the old / proposed partition. */
+int mpic_partition_rows(int n, const double* row_cost, int nranks, int* rows_out);
+int mpic_rebalance_plan(int global_tile_rows, int nranks, const int64_t* row_particles, int64_t cells_per_tile_row,
+                        double w_cell, double min_gain, const int* old_rows, int* new_rows, double cost[2]);
+/* Particles per LOCAL tile row (the occupancy the sort maintains), counts[nrows]. */
+int mpic_get_tile_row_counts(mpic_sim* s, int64_t* counts);
+
+/* Mechanism.  Collective over the ranks, between two steps (after mpic_sort_tiles / mpic_peer_step_end):
+ *   1. every rank PACKS the global tile rows [row_lo, row_hi) of its slab that go to one new owner (itself included) into a
+ *      parcel in device memory: the interior rows of the six field planes and the particles inside them (the current
+ *      accumulators are zero between steps; guard rows are rebuilt).  The parcel is exported: mpic_parcel_info is an opaque,
+ *      fixed-size, trivially copyable blob (CUDA IPC handle + sizes) that any transport can move (torch.distributed
+ *      all_gather in slab.py; plain memory inside one process);
+ *   2. every rank calls mpic_peer_disconnect; the blobs travel (this exchange is the barrier after which nobody maps anybody);
+ *   3. every rank APPLIES: the handle is rebuilt in place on [new_row0, new_row0 + new_nrows) -- old device state freed, new
+ *      state allocated, the parcels (which must tile the new rows exactly, any order) pulled over NVLink with device-to-device
+ *      copies, x guards rebuilt, particles re-indexed (cell offsets; their order IS already the tile/cell order).
+ *      new_max_particles == 0: keep the capacity if the new population fits, else grow to 1.25 x.  all_rows (optional,
+ *      2*nranks ints: row0, nrows of every rank) updates the replicated owner[] map (PIC_2D.cpp:55) explicitly (no MPI_MAX
+ *      trick);
+ *   4. after a barrier of the caller's, mpic_reslab_finish frees the parcels this handle exported; the ring is re-connected
+ *      (mpic_peer_export / _connect, or mpic_ring_enable_peer_access) and the y guards refreshed from the neighbours.
+ * Results are partition-independent bit for bit (fixed-point current): a re-partitioned run equals the original. */
+typedef struct mpic_parcel_info { unsigned char bytes[192]; } mpic_parcel_info;
+int mpic_reslab_pack(mpic_sim* s, int row_lo, int row_hi, mpic_parcel_info* out);
+int mpic_reslab_apply(mpic_sim* s, int new_row0, int new_nrows, int64_t new_max_particles, const mpic_parcel_info* parcels,
+                      int nparcels, const int* all_rows);
+int mpic_reslab_finish(mpic_sim* s);
+/* rows of the handle as they are now */
+int mpic_get_rows(mpic_sim* s, int* row0, int* nrows);
+
 /* ---- single-process ring: one host thread drives N slab handles (sims[r] is rank r of N, one per GPU; handles may
  * share a device) and moves halo messages and migrating particles with CUDA peer copies over NVLink, ordered by events
  * -- no host synchronisation on the field path.  Replaces the MPI exchange phases (PIC_2D.cpp:200-248,276-319,348-396)
@@ -228,6 +275,11 @@ int mpic_ring_refresh_guards(mpic_sim* const* sims, int n);          /* after up
 int mpic_ring_field_steps(mpic_sim* const* sims, int n, int nsteps);  /* phases A..F with ring exchanges */
 int mpic_ring_migrate(mpic_sim* const* sims, int n);                  /* particle hand-off after a push */
 int mpic_ring_pic_steps(mpic_sim* const* sims, int n, int nsteps);    /* full PIC steps */
+/* The whole re-partition for a single-process ring: occupancy -> mpic_rebalance_plan -> pack / apply / finish on every handle
+ * -> guards refreshed.  *changed = 1 when tile rows moved; rows_out (optional, 2*n ints) = the partition in force afterwards.
+ * The trigger the reference hard-codes at step 5 (PIC_2D.cpp:399-412) becomes: call this every K steps (host/pic2d.cpp
+ * --rebalance-every K). */
+int mpic_ring_rebalance(mpic_sim* const* sims, int n, double w_cell, double min_gain, int* changed, int* rows_out);
 
 /* ---- field dumps in the reference's HDF5 layout, written without libhdf5 (host code; works without a GPU).
  * mpic_save_rank_data replaces saveRankData (HDF5_output.h:11, HDF5_output.cpp:10-79): one file, for each listed tile a
@@ -238,6 +290,12 @@ int mpic_save_rank_data(const char* filename, int ntiles, const int* gids, const
 /* Dump the tiles of this slab whose owner[] entry equals `rank` (all local tiles if rank < 0) to `filename`:
  * device -> tile patches with guards -> mpic_save_rank_data.  Phase H of the loop (PIC_2D.cpp:414-419). */
 int mpic_dump_fields(mpic_sim* s, const char* filename, int rank);
+/* The same dump, asynchronous: the tile patches are formed on the device and copied to pinned host memory on a side stream
+ * behind the work queued so far; a writer thread then builds the HDF5 file while the caller keeps stepping (the step path
+ * never waits for the disk).  At most one dump is in flight per handle: a second call first waits for the previous one.
+ * mpic_dump_wait blocks until the file is complete and returns its status (0 when there is none). */
+int mpic_dump_fields_async(mpic_sim* s, const char* filename, int rank);
+int mpic_dump_wait(mpic_sim* s);
 /* params.txt next to the dumps (PIC_2D.cpp:425-438), consumed by File_reader.py:read_params. */
 int mpic_write_params(const char* path, double box_x, double box_y, int nx, int ny, int guard, int interior_nx,
                       int interior_ny, double sim_time, double dt, int total_steps);

@@ -18,6 +18,7 @@ c_lp = C.POINTER(C.c_int64)
 
 
 PEER_INFO_BYTES = 512   # sizeof(mpic_peer_info)
+PARCEL_INFO_BYTES = 192  # sizeof(mpic_parcel_info)
 
 
 class MpicError(RuntimeError):
@@ -108,6 +109,17 @@ def lib():
     L.mpic_peer_trace.argtypes = [C.c_void_p, C.c_int, c_dp, c_lp]
     L.mpic_migrated_total.restype = C.c_int64
     L.mpic_migrated_total.argtypes = [C.c_void_p]
+    L.mpic_peer_disconnect.argtypes = [C.c_void_p]
+    L.mpic_partition_rows.argtypes = [C.c_int, c_dp, C.c_int, c_ip]
+    L.mpic_rebalance_plan.argtypes = [C.c_int, C.c_int, c_lp, C.c_int64, C.c_double, C.c_double, c_ip, c_ip, c_dp]
+    L.mpic_get_tile_row_counts.argtypes = [C.c_void_p, c_lp]
+    L.mpic_reslab_pack.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_char_p]
+    L.mpic_reslab_apply.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int64, C.c_char_p, C.c_int, c_ip]
+    L.mpic_reslab_finish.argtypes = [C.c_void_p]
+    L.mpic_get_rows.argtypes = [C.c_void_p, c_ip, c_ip]
+    L.mpic_ring_rebalance.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_double, C.c_double, c_ip, c_ip]
+    L.mpic_dump_fields_async.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
+    L.mpic_dump_wait.argtypes = [C.c_void_p]
     _lib = L
     return L
 
@@ -130,6 +142,26 @@ def slab_rows(global_tile_rows, nranks, rank):
     r0, nr = C.c_int(), C.c_int()
     lib().mpic_slab_rows(global_tile_rows, nranks, rank, C.byref(r0), C.byref(nr))
     return r0.value, nr.value
+
+
+def partition_rows(row_costs, nranks):
+    """mpic_partition_rows: contiguous partition of the rows into `nranks` non-empty slabs minimising the most expensive
+    slab (exact).  Returns [(row0, nrows)]."""
+    c = np.ascontiguousarray(row_costs, dtype=np.float64)
+    out = np.zeros(2 * nranks, dtype=np.int32)
+    _chk(lib().mpic_partition_rows(int(c.shape[0]), _dp(c), int(nranks), _ip(out)))
+    return [(int(out[2 * k]), int(out[2 * k + 1])) for k in range(nranks)]
+
+
+def rebalance_plan(row_particles, cells_per_tile_row, old_rows, w_cell, min_gain=0.05):
+    """mpic_rebalance_plan: (changed, [(row0, nrows)] per rank, (bottleneck cost before, after))."""
+    rp = np.ascontiguousarray(row_particles, dtype=np.int64)
+    old = np.ascontiguousarray(np.asarray(old_rows, dtype=np.int32).ravel())
+    new = np.zeros_like(old)
+    cost = np.zeros(2)
+    rc = _chk(lib().mpic_rebalance_plan(int(rp.shape[0]), old.shape[0] // 2, rp.ctypes.data_as(c_lp), int(cells_per_tile_row),
+                                        float(w_cell), float(min_gain), _ip(old), _ip(new), _dp(cost)))
+    return bool(rc), [(int(new[2 * k]), int(new[2 * k + 1])) for k in range(old.shape[0] // 2)], (float(cost[0]), float(cost[1]))
 
 
 def courant_dt(dx, dy, factor=0.5):
@@ -277,6 +309,36 @@ class Sim:
     def peer_connect(self, lo_blob, hi_blob):
         _chk(lib().mpic_peer_connect(self.h, lo_blob, hi_blob))
 
+    def peer_disconnect(self):
+        _chk(lib().mpic_peer_disconnect(self.h))
+
+    # ---- run-time re-partition (csrc/reslab.cu)
+    def tile_row_counts(self):
+        out = np.zeros(self.nrows, dtype=np.int64)
+        _chk(lib().mpic_get_tile_row_counts(self.h, out.ctypes.data_as(c_lp)))
+        return out
+
+    def reslab_pack(self, row_lo, row_hi):
+        """Pack global tile rows [row_lo, row_hi) of this slab (fields + particles) into an exported device parcel; returns
+        the 192-byte blob for the new owner."""
+        buf = C.create_string_buffer(PARCEL_INFO_BYTES)
+        _chk(lib().mpic_reslab_pack(self.h, int(row_lo), int(row_hi), buf))
+        return buf.raw
+
+    def reslab_apply(self, row0, nrows, parcels, all_rows=None, max_particles=0):
+        """Rebuild this handle IN PLACE on tile rows [row0, row0 + nrows) from the parcels that tile them."""
+        blob = b"".join(parcels)
+        ar = None if all_rows is None else np.ascontiguousarray(np.asarray(all_rows, dtype=np.int32).ravel())
+        _chk(lib().mpic_reslab_apply(self.h, int(row0), int(nrows), int(max_particles), blob, len(parcels),
+                                     None if ar is None else _ip(ar)))
+        self.row0, self.nrows = int(row0), int(nrows)
+        self.nyl = self.nrows * self.tny
+        self.ntiles_local = self.nrows * self.gtc
+        self.p.row0, self.p.nrows = self.row0, self.nrows
+
+    def reslab_finish(self):
+        _chk(lib().mpic_reslab_finish(self.h))
+
     def peer_refresh_begin(self):
         _chk(lib().mpic_peer_refresh_begin(self.h))
 
@@ -388,6 +450,13 @@ class Sim:
         """Phase H: fields_rank_<r>_step_<s>.h5 in the reference layout (HDF5_output.cpp:10-79)."""
         _chk(lib().mpic_dump_fields(self.h, os.fsencode(filename), rank))
 
+    def dump_fields_async(self, filename, rank=-1):
+        """Phase H off the step path: patches formed on the device, D2H on a side stream, file written by a worker thread."""
+        _chk(lib().mpic_dump_fields_async(self.h, os.fsencode(filename), rank))
+
+    def dump_wait(self):
+        _chk(lib().mpic_dump_wait(self.h))
+
     # ---- ownership
     def owner(self):
         out = np.empty(self.gtr * self.gtc, dtype=np.int32)
@@ -473,6 +542,17 @@ class SlabRing:
     def pic_steps(self, nsteps):
         _chk(lib().mpic_ring_pic_steps(self.arr, self.n, nsteps))
 
+    def rebalance(self, w_cell=8.0, min_gain=0.05):
+        """mpic_ring_rebalance: cost-driven re-partition of the tile rows, handles rebuilt in place.  Returns (changed, rows)."""
+        changed = C.c_int(0)
+        rows = np.zeros(2 * self.n, dtype=np.int32)
+        _chk(lib().mpic_ring_rebalance(self.arr, self.n, float(w_cell), float(min_gain), C.byref(changed), _ip(rows)))
+        for k, s in enumerate(self.sims):
+            s.row0, s.nrows = int(rows[2 * k]), int(rows[2 * k + 1])
+            s.nyl, s.ntiles_local = s.nrows * s.tny, s.nrows * s.gtc
+            s.p.row0, s.p.nrows = s.row0, s.nrows
+        return bool(changed.value), [(int(rows[2 * k]), int(rows[2 * k + 1])) for k in range(self.n)]
+
     def sync(self):
         for s in self.sims:
             s.sync()
@@ -484,10 +564,22 @@ class PeerRing:
 
     def __init__(self, sims):
         self.sims = list(sims)
+        self.connect()
+
+    def connect(self):
         n = len(self.sims)
         blobs = [s.peer_export() for s in self.sims]
         for r, s in enumerate(self.sims):
             s.peer_connect(blobs[(r - 1) % n], blobs[(r + 1) % n])
+
+    def rebalance(self, w_cell=8.0, min_gain=0.05):
+        """Same re-partition as SlabRing.rebalance for a peer-memory ring inside one process: unmap, re-partition, re-map."""
+        ring = SlabRing(self.sims)
+        changed, rows = ring.rebalance(w_cell, min_gain)
+        if changed:
+            self.connect()
+            self.refresh_guards()
+        return changed, rows
 
     def refresh_guards(self):
         for s in self.sims:

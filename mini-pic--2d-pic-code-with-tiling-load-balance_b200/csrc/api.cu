@@ -10,6 +10,7 @@
 #include <vector>
 #include <string>
 #include <utility>
+#include <thread>
 
 static thread_local char g_err[512] = "";
 void mpic_set_error(const char* fmt, ...) {
@@ -17,11 +18,12 @@ void mpic_set_error(const char* fmt, ...) {
 }
 
 #include "sim.cuh"
+static void dump_release(mpic_sim* s);
 
 extern "C" {
 
 const char* mpic_last_error(void) { return g_err; }
-int mpic_abi_version(void) { return 2; }
+int mpic_abi_version(void) { return 3; }
 int mpic_device_count(void) {
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
@@ -165,8 +167,11 @@ static int alloc_particles(Particles* p, int64_t cap) {
     return 0;
 }
 
-int mpic_create(const mpic_params* p, mpic_sim** out) {
-    REQUIRE(p && out, MPIC_EINVAL, "mpic_create: null argument");
+// ---- handle state in three layers: (1) geometry = everything derived from prm (set_geometry), (2) device state sized by the
+// slab's rows and the particle capacity (alloc_state / free_state), (3) streams, events, owner map, counters (mpic_create /
+// mpic_destroy).  mpic_reslab_apply (reslab.cu) re-partitions a LIVE handle by replacing layers 1 and 2 only.
+}  // extern "C"
+static int validate_params(const mpic_params* p) {
     REQUIRE(p->guard == 2, MPIC_EINVAL, "guard must be 2 (PIC_2D.cpp:65)");
     REQUIRE(p->nx > 0 && p->ny > 0 && p->tnx > 0 && p->tny > 0 && p->nx % p->tnx == 0 && p->ny % p->tny == 0, MPIC_EINVAL,
             "nx, ny must be positive multiples of the tile size (the reference silently drops cells otherwise, PIC_2D.cpp:67-68)");
@@ -176,14 +181,17 @@ int mpic_create(const mpic_params* p, mpic_sim** out) {
     REQUIRE(p->max_particles == 0 || (p->dt <= p->dx && p->dt <= p->dy), MPIC_EINVAL,
             "dt = %g exceeds min(dx, dy) = %g: a particle could cross more than one cell per step", p->dt, p->dx < p->dy ? p->dx : p->dy);
     REQUIRE(p->nranks >= 1 && p->rank >= 0 && p->rank < p->nranks, MPIC_EINVAL, "bad rank/nranks");
-    const int gtr = p->ny / p->tny, gtc = p->nx / p->tnx;
+    const int gtr = p->ny / p->tny;
     REQUIRE(p->row0 >= 0 && p->nrows >= 1 && p->row0 + p->nrows <= gtr, MPIC_EINVAL, "bad slab rows");
     REQUIRE(p->nranks > 1 || (p->row0 == 0 && p->nrows == gtr), MPIC_EINVAL, "single rank must own every tile row");
-    REQUIRE((int64_t)p->nx * p->nrows * p->tny < (1ll << 31) - 8 && p->max_particles < (1ll << 31) - 64, MPIC_EINVAL, "slab too large for 32-bit indices");
-    TRY(need_device());
-    CUDA_TRY(cudaSetDevice(p->device));
-    mpic_sim* s = new mpic_sim();
-    s->prm = *p;
+    // 32-bit slot / cell indices and int32 tags (mpic_load_uniform numbers particles globally: 1.07 B fits, 2^31 does not)
+    REQUIRE((int64_t)p->nx * p->nrows * p->tny < (1ll << 31) - 8 && p->max_particles >= 0 && p->max_particles < (1ll << 31) - 64, MPIC_EINVAL,
+            "slab too large for 32-bit indices (cells and max_particles must stay below 2^31)");
+    return 0;
+}
+int mpic_set_geometry(mpic_sim* s) {
+    const mpic_params* p = &s->prm;
+    const int gtc = p->nx / p->tnx;
     FieldGeom& G = s->G;
     G.nx = p->nx; G.nyl = p->nrows * p->tny; G.g = p->guard;
     G.pitch = (MPIC_X0 + p->nx + p->guard + 15) / 16 * 16;
@@ -202,15 +210,12 @@ int mpic_create(const mpic_params* p, mpic_sim** out) {
     c.bx = p->scheme ? p->dt / p->dx : p->dt / (2 * p->dx);
     c.by = p->scheme ? p->dt / p->dy : p->dt / (2 * p->dy);
     c.ex = p->dt / p->dx; c.ey = p->dt / p->dy; c.dt = p->dt; c.fma = p->fma_mode;
-    cudaDeviceProp prop;
-    CUDA_TRY(cudaGetDeviceProperties(&prop, p->device));
-    s->nsm = prop.multiProcessorCount;
-    CUDA_TRY(cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking));
-    if (p->nranks == 1 && !getenv("MPIC_NO_SORT_OVERLAP")) {
-        CUDA_TRY(cudaStreamCreateWithFlags(&s->st_sort, cudaStreamNonBlocking));
-        CUDA_TRY(cudaEventCreateWithFlags(&s->ev_push, cudaEventDisableTiming));
-        CUDA_TRY(cudaEventCreateWithFlags(&s->ev_sort, cudaEventDisableTiming));
-    }
+    return 0;
+}
+int mpic_alloc_state(mpic_sim* s) {
+    const mpic_params* p = &s->prm;
+    FieldGeom& G = s->G;
+    const PicConst& P = s->P;
     CUDA_TRY(cudaMalloc(&s->planes, (size_t)6 * G.plane * 8));
     CUDA_TRY(cudaMemsetAsync(s->planes, 0, (size_t)6 * G.plane * 8, s->st));
     CUDA_TRY(cudaMalloc(&s->jacc, (size_t)3 * G.plane * 8));
@@ -264,6 +269,57 @@ int mpic_create(const mpic_params* p, mpic_sim** out) {
     }
     CUDA_TRY(cudaMalloc(&s->lv.count, 2 * sizeof(int)));
     CUDA_TRY(cudaMemsetAsync(s->lv.count, 0, 2 * sizeof(int), s->st));
+    return 0;
+}
+// frees layer 2 and resets every flag that describes it (the peer / ring mappings into OTHER handles are released first; the
+// caller guarantees that no other handle still maps THIS one's memory)
+void mpic_free_state(mpic_sim* s) {
+    mpic_ring_release(s);
+    mpic_peer_release(s);
+    cudaFree(s->planes); cudaFree(s->planes_alt); cudaFree(s->jacc); cudaFree(s->rho); cudaFree(s->d_scratch);
+    s->planes = s->planes_alt = nullptr; s->jacc = s->rho = nullptr; s->d_scratch = nullptr;
+    for (int k = 0; k < 2; k++) { cudaFree(s->pa[k].x); cudaFree(s->pa[k].tag); s->pa[k] = Particles(); }
+    cudaFree(s->cell_start); cudaFree(s->cell_count); cudaFree(s->scan_tmp); cudaFree(s->keys); cudaFree(s->perm);
+    cudaFree(s->cell_start_alt); cudaFree(s->mcnt); cudaFree(s->offtab); cudaFree(s->dirs); cudaFree(s->lv_off);
+    s->cell_start = s->cell_count = s->scan_tmp = s->keys = s->perm = s->cell_start_alt = s->mcnt = s->offtab = s->lv_off = nullptr;
+    s->dirs = nullptr;
+    cudaFree(s->halo_send); cudaFree(s->halo_recv); cudaFree(s->lv.count);
+    s->halo_send = s->halo_recv = nullptr;
+    for (int d = 0; d < 2; d++) { cudaFree(s->lv.rec[d]); s->arrive[d] = nullptr; }
+    cudaFree(s->arrive_blk);
+    s->arrive_blk = nullptr;
+    s->lv = LeaveBufs();
+    cudaFree(s->pipe_count); cudaFree(s->pipe_start);
+    s->pipe_count = s->pipe_start = nullptr;
+    cudaFree(s->tile_tmp); cudaFree(s->tile_stage);
+    s->tile_tmp = nullptr; s->tile_stage = nullptr; s->tile_tmp_bytes = s->tile_stage_bytes = 0;
+    s->has_tmap = s->fused_ready = false;
+    s->cur = 0; s->n = 0; s->cap = 0; s->n_entries = 0; s->arrived = 0; s->left = -1;
+    s->counts_valid = s->perm_valid = s->moves_counted = false;
+    for (int k = 0; k < 8; k++) s->epoch[k] = 0;
+    s->step_no = 0; s->b2_pending = false; s->pending_ph = 3;
+}
+extern "C" {
+
+int mpic_create(const mpic_params* p, mpic_sim** out) {
+    REQUIRE(p && out, MPIC_EINVAL, "mpic_create: null argument");
+    TRY(validate_params(p));
+    const int gtr = p->ny / p->tny, gtc = p->nx / p->tnx;
+    TRY(need_device());
+    CUDA_TRY(cudaSetDevice(p->device));
+    mpic_sim* s = new mpic_sim();
+    s->prm = *p;
+    TRY(mpic_set_geometry(s));
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, p->device));
+    s->nsm = prop.multiProcessorCount;
+    CUDA_TRY(cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking));
+    if (p->nranks == 1 && !getenv("MPIC_NO_SORT_OVERLAP")) {
+        CUDA_TRY(cudaStreamCreateWithFlags(&s->st_sort, cudaStreamNonBlocking));
+        CUDA_TRY(cudaEventCreateWithFlags(&s->ev_push, cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&s->ev_sort, cudaEventDisableTiming));
+    }
+    TRY(mpic_alloc_state(s));
     s->owner.resize((size_t)gtr * gtc);
     for (int r = 0; r < gtr; r++) {
         int owner_rank = 0;
@@ -277,25 +333,17 @@ int mpic_create(const mpic_params* p, mpic_sim** out) {
 }
 
 int mpic_destroy(mpic_sim* s) {
-    if (s) cudaSetDevice(s->prm.device);
     if (!s) return 0;
     cudaSetDevice(s->prm.device);
     if (s->st) cudaStreamSynchronize(s->st);
-    mpic_ring_release(s);
-    mpic_peer_release(s);
-    cudaFree(s->planes); cudaFree(s->planes_alt); cudaFree(s->jacc); cudaFree(s->rho); cudaFree(s->d_scratch);
-    for (int k = 0; k < 2; k++) { cudaFree(s->pa[k].x); cudaFree(s->pa[k].tag); }
-    cudaFree(s->cell_start); cudaFree(s->cell_count); cudaFree(s->scan_tmp); cudaFree(s->keys); cudaFree(s->perm);
-    cudaFree(s->cell_start_alt); cudaFree(s->mcnt); cudaFree(s->offtab); cudaFree(s->dirs); cudaFree(s->lv_off);
-    cudaFree(s->halo_send); cudaFree(s->halo_recv); cudaFree(s->lv.count);
-    for (int d = 0; d < 2; d++) cudaFree(s->lv.rec[d]);
-    cudaFree(s->arrive_blk);
+    dump_release(s);
+    mpic_reslab_finish(s);
+    mpic_free_state(s);
     if (s->st_sort) { cudaStreamDestroy(s->st_sort); cudaEventDestroy(s->ev_push); cudaEventDestroy(s->ev_sort); }
     if (s->pipe_up) {
         cudaStreamDestroy(s->pipe_up); cudaStreamDestroy(s->pipe_down);
         for (int c = 0; c < MPIC_PIPE_MAX; c++) { cudaEventDestroy(s->pipe_ev_up[c]); cudaEventDestroy(s->pipe_ev_done[c]); }
         cudaEventDestroy(s->pipe_ev_free);
-        cudaFree(s->pipe_count); cudaFree(s->pipe_start);
     }
     if (s->st) cudaStreamDestroy(s->st);
     delete s;
@@ -329,6 +377,18 @@ static int refresh_all_guards(mpic_sim* s) {
     s->launches += s->G.ywrap ? 2 : 1;
     return 0;
 }
+}  // extern "C"
+// grow-only device scratch (reused by the tile converters and occupancy queries: no cudaMalloc / cudaFree per call)
+int mpic_scratch(void** buf, size_t* have, size_t need) {
+    if (*have >= need && *buf) return 0;
+    if (*buf) { cudaFree(*buf); *buf = nullptr; *have = 0; }
+    const size_t want = need + need / 4 + 256;
+    CUDA_TRY(cudaMalloc(buf, want));
+    *have = want;
+    return 0;
+}
+int mpic_refresh_x_guards(mpic_sim* s) { return refresh_all_guards(s); }
+extern "C" {
 int mpic_upload_planes(mpic_sim* s, const double* const planes[6]) {
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && planes, MPIC_EINVAL, "null argument");
@@ -357,9 +417,10 @@ static int tile_lists(mpic_sim* s, const int* gids, int ntiles, int** d_lists) {
         REQUIRE(gids[t] >= 0 && row >= s->prm.row0 && row < s->prm.row0 + s->prm.nrows, MPIC_EINVAL, "tile %d is not on this slab", gids[t]);
         h[t] = row - s->prm.row0; h[ntiles + t] = col;
     }
-    CUDA_TRY(cudaMalloc(d_lists, h.size() * 4));
+    TRY(mpic_scratch(&s->tile_tmp, &s->tile_tmp_bytes, h.size() * 4));
+    *d_lists = (int*)s->tile_tmp;
     CUDA_TRY(cudaMemcpyAsync(*d_lists, h.data(), h.size() * 4, cudaMemcpyHostToDevice, s->st));
-    CUDA_TRY(cudaStreamSynchronize(s->st));
+    CUDA_TRY(cudaStreamSynchronize(s->st));              // h goes out of scope
     return 0;
 }
 int mpic_upload_tiles(mpic_sim* s, const double* grid6, const int* gids, int ntiles) {
@@ -369,15 +430,14 @@ int mpic_upload_tiles(mpic_sim* s, const double* grid6, const int* gids, int nti
     int* lists = nullptr;
     TRY(tile_lists(s, gids, ntiles, &lists));
     const size_t bytes = (size_t)ntiles * (s->P.tnx + 4) * (s->P.tny + 4) * 48;
-    double* d;
-    CUDA_TRY(cudaMalloc(&d, bytes));
+    TRY(mpic_scratch(&s->tile_stage, &s->tile_stage_bytes, bytes));
+    double* d = (double*)s->tile_stage;
     CUDA_TRY(cudaMemcpyAsync(d, grid6, bytes, cudaMemcpyHostToDevice, s->st));
-    int r = launch_tiles_to_planes(s->G, s->planes, d, lists, lists + ntiles, ntiles, s->P.tnx, s->P.tny, s->st);
+    TRY(launch_tiles_to_planes(s->G, s->planes, d, lists, lists + ntiles, ntiles, s->P.tnx, s->P.tny, s->st));
     s->launches++;
-    if (!r) r = refresh_all_guards(s);
-    cudaStreamSynchronize(s->st);
-    cudaFree(d); cudaFree(lists);
-    return r;
+    TRY(refresh_all_guards(s));
+    CUDA_TRY(cudaStreamSynchronize(s->st));
+    return 0;
 }
 int mpic_download_tiles(mpic_sim* s, double* grid6, const int* gids, int ntiles) {
     if (s) cudaSetDevice(s->prm.device);
@@ -387,14 +447,13 @@ int mpic_download_tiles(mpic_sim* s, double* grid6, const int* gids, int ntiles)
     int* lists = nullptr;
     TRY(tile_lists(s, gids, ntiles, &lists));
     const size_t bytes = (size_t)ntiles * (s->P.tnx + 4) * (s->P.tny + 4) * 48;
-    double* d;
-    CUDA_TRY(cudaMalloc(&d, bytes));
-    int r = launch_planes_to_tiles(s->G, s->planes, d, lists, lists + ntiles, ntiles, s->P.tnx, s->P.tny, s->st);
+    TRY(mpic_scratch(&s->tile_stage, &s->tile_stage_bytes, bytes));
+    double* d = (double*)s->tile_stage;
+    TRY(launch_planes_to_tiles(s->G, s->planes, d, lists, lists + ntiles, ntiles, s->P.tnx, s->P.tny, s->st));
     s->launches++;
-    if (!r) { cudaError_t e = cudaMemcpyAsync(grid6, d, bytes, cudaMemcpyDeviceToHost, s->st); if (e != cudaSuccess) { mpic_set_error("D2H: %s", cudaGetErrorString(e)); r = MPIC_ECUDA; } }
-    cudaStreamSynchronize(s->st);
-    cudaFree(d); cudaFree(lists);
-    return r;
+    CUDA_TRY(cudaMemcpyAsync(grid6, d, bytes, cudaMemcpyDeviceToHost, s->st));
+    CUDA_TRY(cudaStreamSynchronize(s->st));
+    return 0;
 }
 
 int mpic_step_b_half(mpic_sim* s) {
@@ -692,6 +751,7 @@ int mpic_push_deposit(mpic_sim* s) {
     return 0;
 }
 int mpic_sort_after_push(mpic_sim* s) { return sort_all(s, true); }
+int mpic_sort_uploaded(mpic_sim* s) { s->perm_valid = false; s->counts_valid = false; s->arrived = 0; return sort_all(s, false); }
 int mpic_sort_tiles(mpic_sim* s) {
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && s->cap > 0, MPIC_ESTATE, "no particle storage");
@@ -725,6 +785,10 @@ static Particles offset_particles(const Particles& p, int64_t o) {
     return r;
 }
 static int pipe_setup(mpic_sim* s) {
+    if (!s->pipe_count) {
+        CUDA_TRY(cudaMalloc(&s->pipe_count, (size_t)s->n_entries * 4));
+        CUDA_TRY(cudaMalloc(&s->pipe_start, (size_t)(s->n_entries + 1) * 4));
+    }
     if (s->pipe_up) return 0;
     CUDA_TRY(cudaStreamCreateWithFlags(&s->pipe_up, cudaStreamNonBlocking));
     CUDA_TRY(cudaStreamCreateWithFlags(&s->pipe_down, cudaStreamNonBlocking));
@@ -733,8 +797,6 @@ static int pipe_setup(mpic_sim* s) {
         CUDA_TRY(cudaEventCreateWithFlags(&s->pipe_ev_done[c], cudaEventDisableTiming));
     }
     CUDA_TRY(cudaEventCreateWithFlags(&s->pipe_ev_free, cudaEventDisableTiming));
-    CUDA_TRY(cudaMalloc(&s->pipe_count, (size_t)s->n_entries * 4));
-    CUDA_TRY(cudaMalloc(&s->pipe_start, (size_t)(s->n_entries + 1) * 4));
     return 0;
 }
 
@@ -854,28 +916,26 @@ int mpic_get_tile_counts(mpic_sim* s, int* counts) {
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && counts && s->cap > 0, MPIC_EINVAL, "bad argument");
     const int nt = s->P.ltr * s->P.gtc;
-    int* d;
-    CUDA_TRY(cudaMalloc(&d, (size_t)nt * 4));
-    int r = launch_tile_counts(s->P, s->cell_start, d, s->st);
+    TRY(mpic_scratch(&s->tile_tmp, &s->tile_tmp_bytes, (size_t)nt * 4));
+    int* d = (int*)s->tile_tmp;
+    TRY(launch_tile_counts(s->P, s->cell_start, d, s->st));
     s->launches++;
-    if (!r) { cudaError_t e = cudaMemcpyAsync(counts, d, (size_t)nt * 4, cudaMemcpyDeviceToHost, s->st); if (e != cudaSuccess) r = MPIC_ECUDA; }
-    cudaStreamSynchronize(s->st);
-    cudaFree(d);
-    return r;
+    CUDA_TRY(cudaMemcpyAsync(counts, d, (size_t)nt * 4, cudaMemcpyDeviceToHost, s->st));
+    CUDA_TRY(cudaStreamSynchronize(s->st));
+    return 0;
 }
 int mpic_get_particle_tile_index(mpic_sim* s, int* gid) {
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && gid && s->cap > 0, MPIC_EINVAL, "bad argument");
     if (!s->n) return 0;
     TRY(materialise(s));
-    int* d;
-    CUDA_TRY(cudaMalloc(&d, (size_t)s->n * 4));
-    int r = launch_particle_tiles(s->P, s->pa[s->cur], s->n, s->prm.row0, d, s->st);
+    TRY(mpic_scratch(&s->tile_tmp, &s->tile_tmp_bytes, (size_t)s->n * 4));
+    int* d = (int*)s->tile_tmp;
+    TRY(launch_particle_tiles(s->P, s->pa[s->cur], s->n, s->prm.row0, d, s->st));
     s->launches++;
-    if (!r) { cudaError_t e = cudaMemcpyAsync(gid, d, (size_t)s->n * 4, cudaMemcpyDeviceToHost, s->st); if (e != cudaSuccess) r = MPIC_ECUDA; }
-    cudaStreamSynchronize(s->st);
-    cudaFree(d);
-    return r;
+    CUDA_TRY(cudaMemcpyAsync(gid, d, (size_t)s->n * 4, cudaMemcpyDeviceToHost, s->st));
+    CUDA_TRY(cudaStreamSynchronize(s->st));
+    return 0;
 }
 int mpic_download_current(mpic_sim* s, int64_t* const jplanes[3]) {
     if (s) cudaSetDevice(s->prm.device);
@@ -953,22 +1013,116 @@ int mpic_gauss_residual(mpic_sim* s, double mean_rho, double* out) {
     return 0;
 }
 
-int mpic_dump_fields(mpic_sim* s, const char* filename, int rank) {
-    if (s) cudaSetDevice(s->prm.device);
-    REQUIRE(s && filename, MPIC_EINVAL, "bad argument");
+// tiles of this slab owned by `rank` (all when rank < 0), in gid order, with the attributes saveRankData writes
+static void dump_tile_list(mpic_sim* s, int rank, std::vector<int>& gids, std::vector<int>& rows, std::vector<int>& cols, std::vector<int>& cur) {
     const int gtc = s->P.gtc;
-    std::vector<int> gids, rows, cols, cur;
     for (int r = s->prm.row0; r < s->prm.row0 + s->prm.nrows; r++)
         for (int c = 0; c < gtc; c++) {
             const int gid = r * gtc + c;
             if (rank >= 0 && s->owner[gid] != rank) continue;
             gids.push_back(gid); rows.push_back(r); cols.push_back(c); cur.push_back(s->owner[gid]);
         }
+}
+int mpic_dump_fields(mpic_sim* s, const char* filename, int rank) {
+    if (s) cudaSetDevice(s->prm.device);
+    REQUIRE(s && filename, MPIC_EINVAL, "bad argument");
+    std::vector<int> gids, rows, cols, cur;
+    dump_tile_list(s, rank, gids, rows, cols, cur);
     const size_t per = (size_t)(s->P.tnx + 4) * (s->P.tny + 4) * 6;
     std::vector<double> grid(per * gids.size());
     if (!gids.empty()) TRY(mpic_download_tiles(s, grid.data(), gids.data(), (int)gids.size()));
     return mpic_save_rank_data(filename, (int)gids.size(), gids.data(), rows.data(), cols.data(), cur.data(), s->P.tnx, s->P.tny,
                                s->prm.guard, grid.data());
+}
+}  // extern "C"
+
+// ---- asynchronous dump: phase H of the loop (PIC_2D.cpp:414-419) off the step path.  The reference stops all ranks while
+// saveRankData copies tile after tile into libhdf5; here the patches are formed by one kernel on the step stream (the only
+// part the steps wait for: one read of the planes), travel to pinned host memory on a side stream, and a writer thread builds
+// the file -- both overlap the following steps.
+struct DumpState {
+    cudaStream_t st = nullptr;
+    cudaEvent_t ev_patches = nullptr, ev_host = nullptr;
+    double* d_grid = nullptr; size_t d_bytes = 0;
+    int* d_lists = nullptr; size_t l_bytes = 0;
+    double* h_grid = nullptr; size_t h_bytes = 0;       // pinned
+    std::vector<int> gids, rows, cols, cur, lists;
+    std::string filename, err;
+    std::thread worker;
+    bool busy = false;
+    int status = 0;
+    int tnx = 0, tny = 0, guard = 0, device = 0;
+};
+static void dump_release(mpic_sim* s) {
+    DumpState* d = s->dump;
+    if (!d) return;
+    if (d->worker.joinable()) d->worker.join();
+    cudaFree(d->d_grid); cudaFree(d->d_lists); cudaFreeHost(d->h_grid);
+    if (d->ev_patches) cudaEventDestroy(d->ev_patches);
+    if (d->ev_host) cudaEventDestroy(d->ev_host);
+    if (d->st) cudaStreamDestroy(d->st);
+    delete d;
+    s->dump = nullptr;
+}
+extern "C" {
+int mpic_dump_wait(mpic_sim* s) {
+    REQUIRE(s, MPIC_EINVAL, "null handle");
+    DumpState* d = s->dump;
+    if (!d || !d->busy) return 0;
+    if (d->worker.joinable()) d->worker.join();
+    d->busy = false;
+    if (d->status) mpic_set_error("%s", d->err.c_str());
+    return d->status;
+}
+int mpic_dump_fields_async(mpic_sim* s, const char* filename, int rank) {
+    if (s) cudaSetDevice(s->prm.device);
+    REQUIRE(s && filename, MPIC_EINVAL, "bad argument");
+    if (!s->dump) {
+        DumpState* d = new DumpState();
+        s->dump = d;
+        CUDA_TRY(cudaStreamCreateWithFlags(&d->st, cudaStreamNonBlocking));
+        CUDA_TRY(cudaEventCreateWithFlags(&d->ev_patches, cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&d->ev_host, cudaEventDisableTiming));
+    }
+    DumpState* d = s->dump;
+    TRY(mpic_dump_wait(s));                              // one dump in flight: the staging buffers are single
+    if (s->peer_on) TRY(mpic_sync(s));                   // guard rows are written by the neighbours: await their last phase
+    d->gids.clear(); d->rows.clear(); d->cols.clear(); d->cur.clear();
+    dump_tile_list(s, rank, d->gids, d->rows, d->cols, d->cur);
+    const int nt = (int)d->gids.size();
+    d->filename = filename; d->tnx = s->P.tnx; d->tny = s->P.tny; d->guard = s->prm.guard; d->device = s->prm.device;
+    d->status = 0; d->err.clear();
+    const size_t bytes = (size_t)nt * (s->P.tnx + 4) * (s->P.tny + 4) * 48;
+    if (nt > 0) {
+        d->lists.resize(2 * (size_t)nt);
+        for (int t = 0; t < nt; t++) { d->lists[t] = d->rows[t] - s->prm.row0; d->lists[nt + t] = d->cols[t]; }
+        TRY(mpic_scratch((void**)&d->d_lists, &d->l_bytes, d->lists.size() * 4));
+        TRY(mpic_scratch((void**)&d->d_grid, &d->d_bytes, bytes));
+        if (d->h_bytes < bytes) {
+            if (d->h_grid) cudaFreeHost(d->h_grid);
+            d->h_grid = nullptr; d->h_bytes = 0;
+            CUDA_TRY(cudaMallocHost(&d->h_grid, bytes));
+            d->h_bytes = bytes;
+        }
+        // the list outlives the copy (member of the dump state); the patch kernel is the only piece on the step stream
+        CUDA_TRY(cudaMemcpyAsync(d->d_lists, d->lists.data(), d->lists.size() * 4, cudaMemcpyHostToDevice, s->st));
+        TRY(launch_planes_to_tiles(s->G, s->planes, d->d_grid, d->d_lists, d->d_lists + nt, nt, s->P.tnx, s->P.tny, s->st));
+        s->launches++;
+        CUDA_TRY(cudaEventRecord(d->ev_patches, s->st));
+        CUDA_TRY(cudaStreamWaitEvent(d->st, d->ev_patches, 0));
+        CUDA_TRY(cudaMemcpyAsync(d->h_grid, d->d_grid, bytes, cudaMemcpyDeviceToHost, d->st));
+    }
+    CUDA_TRY(cudaEventRecord(d->ev_host, d->st));
+    d->busy = true;
+    d->worker = std::thread([d, nt]() {
+        cudaSetDevice(d->device);
+        cudaError_t e = cudaEventSynchronize(d->ev_host);
+        if (e != cudaSuccess) { d->status = MPIC_ECUDA; d->err = std::string("async dump: ") + cudaGetErrorString(e); return; }
+        const int rc = mpic_save_rank_data(d->filename.c_str(), nt, d->gids.data(), d->rows.data(), d->cols.data(), d->cur.data(),
+                                           d->tnx, d->tny, d->guard, d->h_grid);
+        if (rc) { d->status = rc; d->err = mpic_last_error(); }
+    });
+    return 0;
 }
 
 int mpic_selftest_math(int64_t n, uint64_t seed, int64_t* mismatches) {

@@ -236,17 +236,23 @@ int open_side(mpic_sim* s, int side, const PeerBlob& b, const mpic_sim::PeerSide
 
 }  // namespace
 
-void mpic_peer_release(mpic_sim* s) {
-    if (!s) return;
+// unmap the neighbours; the handle's own peer-visible memory (control block, planes, ...) stays: the neighbours may still hold
+// mappings of it until THEY disconnect
+static void peer_unmap(mpic_sim* s) {
     for (int side = 0; side < 2; side++) {
         mpic_sim::PeerSide& p = s->peer[side];
         if (p.ipc) { cudaIpcCloseMemHandle(p.planes); if (p.planes_alt) cudaIpcCloseMemHandle(p.planes_alt); cudaIpcCloseMemHandle(p.jacc); if (p.arrive) cudaIpcCloseMemHandle(p.arrive); cudaIpcCloseMemHandle(p.ctl); }
         p = mpic_sim::PeerSide();
     }
+    s->peer_on = false;
+    s->b2_pending = false;
+}
+void mpic_peer_release(mpic_sim* s) {
+    if (!s) return;
+    peer_unmap(s);
     trace_report(s);
     for (int k = 0; k < 16; k++) if (s->tev[k]) { cudaEventDestroy(s->tev[k]); s->tev[k] = nullptr; }
     s->trace = false;
-    s->peer_on = false;
     if (s->h_counts) { cudaFreeHost(s->h_counts); s->h_counts = nullptr; }
     if (s->ev_counts) { cudaEventDestroy(s->ev_counts); s->ev_counts = nullptr; }
     if (s->ctl) { cudaFree(s->ctl); s->ctl = nullptr; }
@@ -275,6 +281,18 @@ int mpic_peer_export(mpic_sim* s, mpic_peer_info* out) {
         if (b.raw[k]) { CUDA_TRY(cudaIpcGetMemHandle(&b.h[k], b.raw[k])); b.has[k] = 1; }
     memcpy(out->bytes, &b, sizeof b);
     return 0;
+}
+
+int mpic_peer_disconnect(mpic_sim* s) {
+    if (s) cudaSetDevice(s->prm.device);
+    REQUIRE(s, MPIC_EINVAL, "null handle");
+    if (!s->peer_on) return 0;
+    // everything this handle still has in flight towards its neighbours (edge rows, flags) lands before the mappings go
+    CUDA_TRY(cudaStreamSynchronize(s->st));
+    unsigned long long w = 0;
+    CUDA_TRY(cudaMemcpy(&w, s->ctl + CTL_ERROR, 8, cudaMemcpyDeviceToHost));
+    peer_unmap(s);
+    return check_error_word(s, w);
 }
 
 int mpic_peer_connect(mpic_sim* s, const mpic_peer_info* lo, const mpic_peer_info* hi) {

@@ -8,6 +8,7 @@
 // synchronisation and no barrier on the field path; the sender's next pack waits on the receivers' "copied" events
 // (write-after-read on the staging buffer).  Handles may share a device (used by the one-GPU tests).
 #include "sim.cuh"
+#include <algorithm>
 
 namespace {
 
@@ -158,6 +159,52 @@ int mpic_ring_pic_steps(mpic_sim* const* sims, int n, int nsteps) {
         for (int r = 0; r < n; r++) TRY(mpic_sort_tiles(sims[r]));
     }
     return 0;
+}
+
+// Cost-driven re-partition of the ring (reslab.cu holds policy and mechanism; this is the sequence for handles that share a
+// process): occupancy per tile row -> plan -> every handle packs one parcel per new owner -> every handle is rebuilt in place
+// from the parcels of its new rows (device-to-device / peer copies) -> parcels freed -> y guards refreshed over the ring.
+int mpic_ring_rebalance(mpic_sim* const* sims, int n, double w_cell, double min_gain, int* changed, int* rows_out) {
+    TRY(check_ring(sims, n));
+    const mpic_params& p0 = sims[0]->prm;
+    const int gtr = p0.ny / p0.tny;
+    std::vector<int64_t> rowp((size_t)gtr, 0);
+    std::vector<int> old_rows(2 * (size_t)n), new_rows(2 * (size_t)n);
+    for (int r = 0; r < n; r++) {
+        old_rows[2 * r] = sims[r]->prm.row0; old_rows[2 * r + 1] = sims[r]->prm.nrows;
+        TRY(mpic_get_tile_row_counts(sims[r], rowp.data() + sims[r]->prm.row0));
+    }
+    double cost[2];
+    const int plan = mpic_rebalance_plan(gtr, n, rowp.data(), (int64_t)p0.nx * p0.tny, w_cell, min_gain, old_rows.data(), new_rows.data(), cost);
+    if (plan < 0) return plan;
+    if (changed) *changed = plan;
+    if (rows_out) for (int k = 0; k < 2 * n; k++) rows_out[k] = new_rows[k];
+    if (!plan) return 0;
+    // owner[] follows the slabs only where it described them before (the default); a caller-defined map of logical ranks
+    // (host/pic2d --ranks R: dump grouping) is left alone
+    bool owner_is_slab = true;
+    for (int r = 0; r < n && owner_is_slab; r++) {
+        const int gtc = sims[r]->P.gtc;
+        for (int k = 0; k < n && owner_is_slab; k++)
+            for (int row = old_rows[2 * k]; row < old_rows[2 * k] + old_rows[2 * k + 1] && owner_is_slab; row++)
+                for (int c = 0; c < gtc; c++) if (sims[r]->owner[(size_t)row * gtc + c] != k) { owner_is_slab = false; break; }
+    }
+    for (int r = 0; r < n; r++) TRY(mpic_peer_disconnect(sims[r]));     // a peer-memory ring over the same handles: unmap first
+    std::vector<std::vector<mpic_parcel_info>> inbox((size_t)n);
+    for (int r = 0; r < n; r++)
+        for (int d = 0; d < n; d++) {
+            const int lo = std::max(old_rows[2 * r], new_rows[2 * d]);
+            const int hi = std::min(old_rows[2 * r] + old_rows[2 * r + 1], new_rows[2 * d] + new_rows[2 * d + 1]);
+            if (hi <= lo) continue;
+            mpic_parcel_info info;
+            TRY(mpic_reslab_pack(sims[r], lo, hi, &info));
+            inbox[d].push_back(info);
+        }
+    for (int r = 0; r < n; r++)
+        TRY(mpic_reslab_apply(sims[r], new_rows[2 * r], new_rows[2 * r + 1], 0, inbox[r].data(), (int)inbox[r].size(), owner_is_slab ? new_rows.data() : nullptr));
+    for (int r = 0; r < n; r++) TRY(mpic_reslab_finish(sims[r]));
+    TRY(mpic_ring_enable_peer_access(sims, n));
+    return mpic_ring_refresh_guards(sims, n);
 }
 
 }  // extern "C"

@@ -87,10 +87,23 @@ struct mpic_sim {
     int* pipe_count = nullptr;     // per-chunk cell histogram / scatter cursor
     int* pipe_start = nullptr;     // per-chunk cell offsets (relative to the chunk's first slot)
     std::vector<int> owner;        // global tiles
+    // device scratch of the tile-layout converters and the occupancy queries (grown on demand, reused: no cudaMalloc per call)
+    void* tile_tmp = nullptr;   size_t tile_tmp_bytes = 0;     // tile lists / counts / per-particle tile ids
+    void* tile_stage = nullptr; size_t tile_stage_bytes = 0;   // tile patches with guards
+    // run-time re-partition (reslab.cu): parcels this handle packed and exported, freed by mpic_reslab_finish
+    std::vector<void*> parcels;
+    // asynchronous field dumps (dump.cu): side stream, pinned staging, writer thread
+    struct DumpState* dump = nullptr;
     void* ring_events = nullptr;   // ring.cu: per-handle events of the single-process peer-copy ring
 };
 
 void mpic_ring_release(mpic_sim* s);
+int mpic_set_geometry(mpic_sim* s);                  // api.cu: G, P, cf from prm
+int mpic_alloc_state(mpic_sim* s);                   // api.cu: every device array sized by the slab rows / particle capacity
+void mpic_free_state(mpic_sim* s);                   // api.cu: ... and back (releases the peer / ring mappings first)
+int mpic_scratch(void** buf, size_t* have, size_t need);   // api.cu: grow-only device scratch
+extern "C" int mpic_sort_uploaded(mpic_sim* s);      // api.cu: sort_all(false) -- keys from the stored positions
+int mpic_refresh_x_guards(mpic_sim* s);              // api.cu: periodic x images (and y on a single slab) of the six planes
 int mpic_fused_setup(mpic_sim* s);                   // api.cu: second plane block + tensor maps (idempotent)
 void mpic_fused_swap(mpic_sim* s);                   // api.cu: planes <-> planes_alt (+ maps, + peer pointers)
 void mpic_peer_release(mpic_sim* s);

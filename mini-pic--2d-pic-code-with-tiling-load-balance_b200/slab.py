@@ -150,43 +150,56 @@ def tile_row_costs(counts, gtc, cells_per_tile, w_particle=1.0, w_cell=None):
 def balanced_slab_rows(row_costs, nranks):
     """Contiguous partition of tile rows into `nranks` slabs minimising the maximum slab cost (exact: binary search on the
     bottleneck + greedy sweep).  Returns [(row0, nrows)] with every slab non-empty.  This is the policy the reference
-    leaves as future work (Report p.10); the mechanism it offers is removeTileFromRank/addTileToRank."""
-    c = np.asarray(row_costs, dtype=np.float64)
-    n = len(c)
-    if nranks > n:
-        raise ValueError("more ranks than tile rows")
+    leaves as future work (Report p.10); the mechanism it offers is removeTileFromRank/addTileToRank.  The implementation
+    is the library's (mpic_partition_rows, csrc/reslab.cu: host code, runs without a GPU)."""
+    m = importlib.import_module(__package__)
+    try:
+        return m.partition_rows(row_costs, nranks)
+    except m.MpicError as e:
+        raise ValueError(str(e))
 
-    def cuts(limit):
-        out, start, acc = [], 0, 0.0
-        for i in range(n):
-            remaining_ranks = nranks - len(out) - 1            # slabs still to open after the current one
-            must_cut = (n - i) == remaining_ranks and i > start  # leave one row for each remaining slab
-            if i > start and (acc + c[i] > limit or must_cut):
-                out.append((start, i - start))
-                start, acc = i, 0.0
-            acc += c[i]
-        out.append((start, n - start))
-        return out
 
-    lo, hi = float(c.max()), float(c.sum())
-    for _ in range(60):
-        mid = 0.5 * (lo + hi)
-        if len(cuts(mid)) <= nranks:
-            hi = mid
-        else:
-            lo = mid
-    parts = cuts(hi)
-    while len(parts) < nranks:                                  # split the widest slab until every rank owns rows
-        k = max(range(len(parts)), key=lambda j: parts[j][1])
-        r0, nr = parts[k]
-        if nr < 2:
-            raise ValueError("cannot give every rank a tile row")
-        parts[k:k + 1] = [(r0, nr // 2), (r0 + nr // 2, nr - nr // 2)]
-    return parts
+def rebalance_device(sim, rank, world, dist=None, group=None, w_cell=None, min_gain=0.05):
+    """Cost-driven re-partition of the tile rows ON THE DEVICE through the C ABI (csrc/reslab.cu): policy
+    mpic_rebalance_plan, mechanism mpic_reslab_pack / _apply / _finish.  Replaces removeTileFromRank / addTileToRank
+    (Auxiliar_functions.cpp:242-272) and the hard-coded trigger PIC_2D.cpp:399-412.
+
+    Collective.  torch.distributed only carries two small object all-gathers (per-tile-row occupancy, then the parcel
+    blobs -- the second one is also the barrier after which no rank maps another's memory); fields and particles move as
+    device-to-device copies over NVLink from the old owner's parcel into the new owner's arrays, and the handle changes its
+    rows IN PLACE.  Returns ([(row0, nrows)] per rank, changed); the caller re-connects its PeerStepper (new IPC handles)
+    and refreshes the guards."""
+    if dist is None:
+        import torch.distributed as dist
+    m = importlib.import_module(__package__)
+    allr = [None] * world
+    dist.all_gather_object(allr, (int(sim.row0), int(sim.nrows), sim.tile_row_counts().tolist()), group=group)
+    old = [(a[0], a[1]) for a in allr]
+    gtr = sum(nr for _, nr in old)
+    rowp = np.zeros(gtr, dtype=np.int64)
+    for r0, nr, c in allr:
+        rowp[r0:r0 + nr] = c
+    changed, new, _ = m.rebalance_plan(rowp, sim.nx * sim.tny, old, W_CELL if w_cell is None else w_cell, min_gain)
+    if not changed:
+        return old, False
+    mine = {}
+    for d in range(world):                                   # one parcel per new owner of some of my rows (myself included)
+        lo, hi = max(old[rank][0], new[d][0]), min(old[rank][0] + old[rank][1], new[d][0] + new[d][1])
+        if hi > lo:
+            mine[d] = sim.reslab_pack(lo, hi)
+    sim.peer_disconnect()                                    # nobody may map memory that is about to be freed
+    posted = [None] * world
+    dist.all_gather_object(posted, mine, group=group)
+    sim.reslab_apply(new[rank][0], new[rank][1], [posted[src][rank] for src in range(world) if rank in posted[src]], all_rows=new)
+    dist.barrier(group=group)                                # every parcel has been pulled
+    sim.reslab_finish()
+    return new, True
 
 
 def rebalance(sim, rank, world, make_sim, dist=None, group=None, w_cell=None, min_gain=0.05):
-    """Cost-driven re-partition of the tile rows over the ranks -- the load balancer the reference names as its purpose
+    """HOST-STAGED re-partition, kept as the test double of `rebalance_device` for the gloo CPU tests (any object with the
+    Sim slab interface; the product path is rebalance_device: C ABI, device-to-device, handle rebuilt in place).
+    Cost-driven re-partition of the tile rows over the ranks -- the load balancer the reference names as its purpose
     but ships only as a hard-coded demo (PIC_2D.cpp:399-412 moves three tiles at step 5; removeTileFromRank /
     addTileToRank, Auxiliar_functions.cpp:242-272, send the grid and DROP the particles).
 
@@ -428,20 +441,18 @@ def slab_pic_record(args, name, w, rank, world, local, peak, peak_how, e2e=True,
         ms0, np0, _, per0, _ = timed(stepper, sim, st)
         torch.cuda.synchronize()
         tr0 = time.perf_counter()
-        new, rows, changed = rebalance(sim, rank, world, make, dist)
+        rows, changed = rebalance_device(sim, rank, world, dist)
+        if changed:
+            stepper = new_stepper(sim)           # new IPC handles: the handle itself (and its stream) stayed
         torch.cuda.synchronize()
         dist.barrier()
         tr = [None] * world
         dist.all_gather_object(tr, time.perf_counter() - tr0)
-        if changed:
-            sim.close()
-            sim = new
-            st = sim.torch_stream()
-            stepper = new_stepper(sim)
         rebal = {"changed": bool(changed), "rebalance_ms": 1e3 * max(tr),
                  "even_split": {"ms_per_step": ms0 / K, "particles_per_rank": [g[1] for g in per0],
                                 "tile_rows_per_rank": [g[2] for g in per0], "pushes_per_s": float(np0) * K / (ms0 * 1e-3)},
-                 "policy": f"slab.balanced_slab_rows on cost = particles + {W_CELL:g} * cells per tile row"}
+                 "mechanism": "C ABI, on the device: mpic_rebalance_plan -> mpic_reslab_pack -> parcels pulled over NVLink (CUDA IPC) -> mpic_reslab_apply rebuilds the handle in place (csrc/reslab.cu)",
+                 "policy": f"mpic_rebalance_plan on cost = particles + {W_CELL:g} * cells per tile row"}
     ms_max, npart_total, launches, per, clk = timed(stepper, sim, st, clocks=clocks, pre=sat)
     if rebal is not None:
         rebal["rebalanced"] = {"ms_per_step": ms_max / K, "particles_per_rank": [g[1] for g in per],

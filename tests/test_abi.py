@@ -20,7 +20,7 @@ def test_library_exports_every_declared_symbol():
     assert len(names) > 40
     for n in names:
         assert hasattr(L, n), n
-    assert L.mpic_abi_version() == 2
+    assert L.mpic_abi_version() == 3
 
 
 def test_integer_helpers_on_cpu():

@@ -197,3 +197,51 @@ def test_c5_beam_plasma_occupancy_and_policy():
     assert max(even) / np.mean(even) > 1.7
     assert max(bal) / np.mean(bal) < 1.25
     s.close()
+
+
+def test_c3_dump_of_65536_tiles_off_the_step_path(tmp_path):
+    """SURVEY.md f1 at scale: configs[2] (8192^2) in 32^2 tiles = 65 536 tile groups, 4.1 GB in the reference's HDF5 layout.
+    The asynchronous dump costs the step path one patch kernel; the device-to-host copy and the file writer run next to the
+    following steps.  The file is parsed back (mmap) and a sample of tiles is compared with the planes of the dump step."""
+    import time
+    from h5mini import H5Mini, GRID_DTYPE
+    m = pkg()
+    n, tn = 8192, 32
+    dx = 10.0 / n
+    s = m.Sim(n, n, tn, tn, dx, dx, m.courant_dt(dx, dx))
+    x = (np.arange(n) + 0.5) * dx
+    prof = 0.1 * np.sin(np.pi * x) * np.cos((x - 3.5) / 3.0 * np.pi / 2) ** 2 * (np.abs(x - 3.5) < 3.0)
+    z = np.zeros((n, n))
+    row = np.tile(prof, (n, 1))
+    s.upload_planes([z, row, z, z, z, row])
+    del z, row
+    s.field_steps(5, fused=True)
+    want = s.download_planes()
+    path = str(tmp_path / "fields_rank_0_step_5.h5")
+    s.dump_fields_async(path)                            # warm-up of the pinned staging (4 GB cudaMallocHost) is part of this call
+    s.dump_wait()
+    os_size = __import__("os").path.getsize(path)
+    assert os_size > 65536 * 36 * 36 * 48
+    s.sync()
+    t0 = time.perf_counter()
+    s.dump_fields_async(path)
+    t_issue = time.perf_counter() - t0
+    s.field_steps(20, fused=True)
+    s.sync()
+    t_steps = time.perf_counter() - t0
+    s.dump_wait()
+    t_all = time.perf_counter() - t0
+    print(f"async dump of 65536 tiles: issue {1e3 * t_issue:.1f} ms, 20 steps done after {1e3 * t_steps:.1f} ms, file complete after {1e3 * t_all:.1f} ms")
+    assert t_steps < t_all                               # the steps did not wait for the file
+    h = H5Mini(path)
+    links = h.links()
+    assert len(links) == 65536 and h.eof == os_size
+    gtc = n // tn
+    pad = lambda a, r, c: np.take(np.take(a, np.arange(r * tn - 2, (r + 1) * tn + 2) % n, axis=0), np.arange(c * tn - 2, (c + 1) * tn + 2) % n, axis=1)
+    for name, ohdr in links[::4099] + links[-1:]:
+        gid = int(name[5:])
+        r, c = divmod(gid, gtc)
+        assert h.attrs(ohdr) == {"tileRow": r, "tileCol": c, "currentRank": 0}
+        d = h.dataset(dict(h.links(ohdr))["fields"])
+        for k, nm in enumerate(GRID_DTYPE.names):
+            assert np.array_equal(d[nm], pad(want[k], r, c)), (gid, nm)

@@ -266,11 +266,12 @@ def _rebalance_gpu_worker(rank, world, port, steps, outdir):
             st.step()
         sim.sync()
         before = sim.num_particles
-        new, rows, changed = slab.rebalance(sim, rank, world, make, dist, w_cell=0.25)
-        dist.barrier()                     # nobody touches the old handles any more
-        if changed:
-            sim.close()
-        sim = new
+        handle = sim.h.value
+        rows, changed = slab.rebalance_device(sim, rank, world, dist, w_cell=0.25)
+        assert sim.h.value == handle and (sim.row0, sim.nrows) == tuple(rows[rank])     # same handle, new rows, in place
+        own = sim.owner().reshape(-1, sim.gtc)
+        for r, (r0, nr) in enumerate(rows):
+            assert (own[r0:r0 + nr] == r).all()
         st = slab.PeerStepper(sim, rank, world, dist)
         st.refresh_guards()
         for _ in range(steps):
@@ -289,8 +290,9 @@ def _rebalance_gpu_worker(rank, world, port, steps, outdir):
 @pytest.mark.parametrize("world", [2, 3])
 def test_runtime_rebalance_over_the_peer_ring(world):
     """One process per rank (CUDA IPC between them, all on one GPU when the box has one): peer-ring steps, cost-driven
-    re-partition of tile rows with their fields and particles (slab.rebalance), peer-ring steps on the new, uneven slabs.
-    Bit-exact versus the single-rank oracle; the most loaded rank gets lighter."""
+    re-partition of tile rows with their fields and particles ON THE DEVICE through the C ABI (slab.rebalance_device:
+    mpic_rebalance_plan, mpic_reslab_pack / _apply / _finish; parcels pulled through CUDA IPC, handles rebuilt in place),
+    peer-ring steps on the new, uneven slabs.  Bit-exact versus the single-rank oracle; the most loaded rank gets lighter."""
     import tempfile
     import torch.multiprocessing as mp
     from test_slab_gloo import _beam_problem, _free_port
@@ -314,3 +316,78 @@ def test_runtime_rebalance_over_the_peer_ring(world):
     assert np.array_equal(np.concatenate([o["counts"] for o in outs]), counts)
     assert all(bool(o["changed"]) for o in outs)
     assert max(int(o["after"]) for o in outs) < 0.8 * max(int(o["before"]) for o in outs)
+
+
+@pytest.mark.parametrize("world,kind", [(2, "copy"), (3, "copy"), (4, "peer"), (3, "peer")])
+def test_single_process_ring_rebalance_in_place(world, kind):
+    """mpic_ring_rebalance (what host/pic2d --rebalance-every uses): steps, cost-driven re-partition with the handles rebuilt
+    in place from device parcels, more steps on the uneven slabs -- for the peer-copy ring (csrc/ring.cu) and the peer-memory
+    ring (csrc/peer.cu).  Bit-exact versus the single-rank oracle; a second call changes nothing (the plan is a fixed point)."""
+    import torch
+    from test_slab_gloo import _beam_problem
+    m = pkg()
+    g, parts, planes = _beam_problem()
+    nx, ny, tn, dx, dy, dt = g["nx"], g["ny"], g["tnx"], g["dx"], g["dy"], g["dt"]
+    ndev = max(1, torch.cuda.device_count())
+    cap = parts["x"].shape[0]
+    sims = [m.Sim(nx, ny, tn, g["tny"], dx, dy, dt, max_particles=cap // world + 64, rank=r, nranks=world, device=r % ndev) for r in range(world)]
+    for s in sims:
+        r0, r1 = s.row0 * g["tny"], (s.row0 + s.nrows) * g["tny"]
+        s.upload_planes([a[r0:r1] for a in planes])
+        cy = np.floor(parts["y"] * (1.0 / dy)).astype(np.int64)
+        sel = (cy >= r0) & (cy < r1)
+        s.upload_particles({k: np.ascontiguousarray(v[sel]) for k, v in parts.items()})
+    ring = m.SlabRing(sims) if kind == "copy" else m.PeerRing(sims)
+    ring.refresh_guards()
+    steps = 4
+    ring.pic_steps(steps)
+    ring.sync()
+    before = [s.num_particles for s in sims]
+    handles = [s.h.value for s in sims]
+    changed, rows = ring.rebalance(w_cell=0.25)
+    assert changed and [s.h.value for s in sims] == handles
+    assert rows[0][0] == 0 and all(rows[k][0] + rows[k][1] == rows[k + 1][0] for k in range(world - 1)) and rows[-1][0] + rows[-1][1] == ny // g["tny"]
+    assert max(s.num_particles for s in sims) < 0.85 * max(before) and sum(s.num_particles for s in sims) == sum(before)
+    again, rows2 = ring.rebalance(w_cell=0.25)
+    assert not again and rows2 == rows
+    ring.pic_steps(steps)
+    ring.sync()
+    lib = ob.load_oracle()
+    P = ob.make_params(lib, nx, ny, tn, g["tny"], dx, dy, dt)
+    want, wf = copy_parts(parts), [a.copy() for a in planes]
+    counts, _ = ob.pic_steps(lib, P, wf, want, 2 * steps)
+    got = by_tag({k: np.concatenate([s.download_particles()[k] for s in sims]) for k in ("x", "y", "ux", "uy", "uz", "q", "tag")})
+    want = by_tag(want)
+    assert np.array_equal(got["tag"], want["tag"])
+    for k in ("x", "y", "ux", "uy", "uz", "q"):
+        assert np.array_equal(got[k], want[k]), k
+    for k in range(6):
+        assert np.array_equal(np.concatenate([s.download_planes()[k] for s in sims]), wf[k]), k
+    assert np.array_equal(np.concatenate([s.tile_counts() for s in sims]), counts)
+    own = sims[0].owner().reshape(-1, sims[0].gtc)
+    for r, (r0, nr) in enumerate(rows):
+        assert (own[r0:r0 + nr] == r).all()
+
+
+def test_reslab_rejects_bad_parcels():
+    """mpic_reslab_apply validates before it frees anything: parcels must tile the new rows exactly."""
+    m = pkg()
+    nx, ny, tn, ppc, u_th = 32, 64, 16, 2, 0.3
+    dx, dy, dt, parts, planes = _problem(nx, ny, tn, ppc, u_th, seed=5)
+    sims = [m.Sim(nx, ny, tn, tn, dx, dy, dt, max_particles=parts["x"].shape[0], rank=r, nranks=2, device=0) for r in range(2)]
+    for s in sims:
+        r0, r1 = s.row0 * tn, (s.row0 + s.nrows) * tn
+        s.upload_planes([a[r0:r1] for a in planes])
+        s.upload_particles(parts)
+    a = sims[0].reslab_pack(0, 1)
+    with pytest.raises(m.MpicError):
+        sims[0].reslab_pack(1, 3)                        # row 2 is not on slab 0
+    with pytest.raises(m.MpicError):
+        sims[0].reslab_apply(0, 2, [a])                  # rows [0,2) are not covered by one parcel of row 0
+    with pytest.raises(m.MpicError):
+        sims[0].reslab_apply(0, 1, [a, a])               # overlap
+    assert sims[0].num_particles > 0                     # the handle survived the rejected calls
+    got = sims[0].download_planes()
+    for k in range(6):
+        assert np.array_equal(got[k], planes[k][:sims[0].nyl])
+    sims[0].reslab_finish()

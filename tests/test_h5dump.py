@@ -51,6 +51,27 @@ def test_many_tiles_multi_level_btree(tmp_path, ntiles):
         assert np.array_equal(np.stack([d[n] for n in GRID_DTYPE.names], axis=-1), grid[k])
 
 
+def test_65536_tiles_three_level_btree(tmp_path):
+    """The tile count of BASELINE.json configs[2] (8192^2 cells in 32^2 tiles = 65 536 groups) with small patches: the group
+    B-tree needs three levels; every group is found again, in strcmp order, with its attributes and data."""
+    m = pkg()
+    nt, tnx, tny, g = 65536, 4, 4, 2
+    rng = np.random.default_rng(65536)
+    gids = np.arange(nt)
+    grid = rng.standard_normal((nt, tny + 2 * g, tnx + 2 * g, 6))
+    path = str(tmp_path / "f.h5")
+    m.save_rank_data(path, gids, gids // 256, gids % 256, gids % 9, tnx, tny, g, grid)
+    h = H5Mini(path)
+    assert h.eof == os.path.getsize(path)
+    links = h.links()
+    assert [n for n, _ in links] == sorted(f"Tile_{i}" for i in gids)
+    for name, ohdr in links[::997] + links[-1:]:
+        gid = int(name[5:])
+        d = h.dataset(dict(h.links(ohdr))["fields"])
+        assert h.attrs(ohdr) == {"tileRow": gid // 256, "tileCol": gid % 256, "currentRank": gid % 9}
+        assert np.array_equal(np.stack([d[n] for n in GRID_DTYPE.names], axis=-1), grid[gid])
+
+
 def test_assemble_like_file_reader(tmp_path):
     """The consumer contract (File_reader.py:82-117): interiors placed by tileRow/tileCol rebuild the global planes."""
     m = pkg()
