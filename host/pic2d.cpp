@@ -44,6 +44,7 @@ struct Options {
     int ppc = 0;                            // particles per cell (0: field solver only, like the reference)
     double u_th = 0.05, two_stream = 0.0, drift_x = 0.0;
     double beam_density = 0.0, beam_lo = 0.45, beam_hi = 0.55, beam_drift = 0.5, beam_uth = 0.01;
+    int deposit = 0;                        // 0: charge-conserving zigzag; 1: direct CIC (SURVEY.md B.5 option a)
     unsigned long long seed = 12345;
     int diag_every = 0;
     int rebalance_every = 0;                // > 0: every K steps re-partition the tile rows over the GPUs when it pays (mpic_ring_rebalance)
@@ -57,7 +58,7 @@ void usage() {
               "      [--sim-time t | --steps n] [--cfl f] [--save-frequency k] [--ic test1|test2|test3|zero] [--out dir]\n"
               "      [--gpus N] [--scheme 0|1 --fma 0|1] [--no-migrate-demo]\n"
               "      [--ppc n --uth u --two-stream u0 --drift-x u | --beam-density d --beam-lo f --beam-hi f --beam-drift u --beam-uth u]\n"
-              "      [--seed s] [--diag-every k] [--rebalance-every k --rebalance-w-cell w --rebalance-min-gain f] [--async-dump] [--quiet]\n"
+              "      [--deposit zigzag|cic] [--seed s] [--diag-every k] [--rebalance-every k --rebalance-w-cell w --rebalance-min-gain f] [--async-dump] [--quiet]\n"
               "defaults = the literals of the reference's PIC_2D.cpp (450x450, 9 ranks x 36 tiles of 25x25, Test-3 pulse, t=500)");
 }
 
@@ -79,6 +80,7 @@ bool parse(int argc, char** argv, Options& o) {
         else if (a == "--beam-density") o.beam_density = atof(val()); else if (a == "--beam-lo") o.beam_lo = atof(val());
         else if (a == "--beam-hi") o.beam_hi = atof(val()); else if (a == "--beam-drift") o.beam_drift = atof(val());
         else if (a == "--beam-uth") o.beam_uth = atof(val());
+        else if (a == "--deposit") { std::string v = val(); if (v != "zigzag" && v != "cic") { std::fprintf(stderr, "--deposit zigzag|cic\n"); return false; } o.deposit = v == "cic"; }
         else if (a == "--seed") o.seed = strtoull(val(), nullptr, 10); else if (a == "--diag-every") o.diag_every = atoi(val());
         else if (a == "--rebalance-every") o.rebalance_every = atoi(val()); else if (a == "--rebalance-w-cell") o.rebalance_w_cell = atof(val());
         else if (a == "--rebalance-min-gain") o.rebalance_min_gain = atof(val());
@@ -175,7 +177,7 @@ int main(int argc, char** argv) {
         mpic_params p;
         std::memset(&p, 0, sizeof p);
         p.nx = o.nx; p.ny = o.ny; p.tnx = interior_nx; p.tny = interior_ny; p.guard = o.guard; p.scheme = o.scheme; p.fma_mode = o.fma;
-        p.rank = r; p.nranks = N; p.device = r % ndev; p.dx = dx; p.dy = dy; p.dt = dt; p.qm = -1.0;
+        p.rank = r; p.nranks = N; p.device = r % ndev; p.dx = dx; p.dy = dy; p.dt = dt; p.qm = -1.0; p.deposit = o.deposit;
         mpic_slab_rows(globalTileRows, N, r, &p.row0, &p.nrows);
         if (o.ppc > 0) {
             const double cells = (double)o.nx * p.nrows * interior_ny;

@@ -78,8 +78,15 @@ typedef struct mpic_params {
     int device;            /* CUDA device ordinal */
     double dx, dy, dt;
     double qm;             /* species charge/mass (electrons: -1) */
-    int64_t max_particles; /* capacity of each particle array (0: fields only) */
+    int64_t max_particles; /* capacity of each particle array (0: fields only); < 2^31 - 64 (32-bit slots; int32 tags) */
+    int deposit;           /* 0: charge-conserving zigzag for Jx, Jy + CIC Jz (default; Gauss's law holds to round-off);
+                              1: direct CIC of q v at the time-centred position on the E_k lattices (SURVEY.md B.5 option a, the
+                                 literal reading of north_star; NOT charge conserving -- a selectable mode, not a tuned kernel) */
+    int reserved;          /* 0 */
 } mpic_params;
+/* Fixed-point current: J is accumulated as int64 (value * 2^52), which makes the deposit order-independent and hence
+ * bit-reproducible on any number of GPUs.  Range: |J| < 1024 code units per node and step; a step that comes within a factor
+ * two of it raises an error that the next mpic_sync / mpic_upload_* returns as MPIC_EINVAL. */
 
 int mpic_create(const mpic_params* p, mpic_sim** out);
 int mpic_destroy(mpic_sim* s);
@@ -209,6 +216,9 @@ int mpic_get_particle_tile_index(mpic_sim* s, int* gid_of_particle);
 int mpic_cell_crossers(mpic_sim* s, int64_t* n_out);
 /* J accumulators of the last push as int64 fixed point (value * 2^52), three (nyl,nx) planes */
 int mpic_download_current(mpic_sim* s, int64_t* const jplanes[3]);
+/* rho of the stored particles as int64 fixed point (value * 2^52; node weights of the Ez lattice), one (nyl,nx)
+ * plane; guard contributions folded (x always; y on a single slab -- a slab's first row misses the lower neighbour's part). */
+int mpic_download_rho(mpic_sim* s, int64_t* rho);
 /* out[0] field energy 1/2 sum dx dy (E^2+B^2) over the slab; out[1] kinetic energy sum m_p (gamma-1);
  * out[2] max |div E - rho + <rho>| (Gauss residual); out[3] total charge; out[4] number of particles */
 int mpic_diagnostics(mpic_sim* s, double out[5]);

@@ -30,7 +30,7 @@ class Params(C.Structure):
                 ("scheme", C.c_int), ("fma_mode", C.c_int), ("rank", C.c_int), ("nranks", C.c_int),
                 ("row0", C.c_int), ("nrows", C.c_int), ("device", C.c_int),
                 ("dx", C.c_double), ("dy", C.c_double), ("dt", C.c_double), ("qm", C.c_double),
-                ("max_particles", C.c_int64)]
+                ("max_particles", C.c_int64), ("deposit", C.c_int), ("reserved", C.c_int)]
 
 
 class HaloDesc(C.Structure):
@@ -82,6 +82,7 @@ def lib():
     L.mpic_get_particle_tile_index.argtypes = [C.c_void_p, c_ip]
     L.mpic_download_current.argtypes = [C.c_void_p, C.POINTER(c_lp)]
     L.mpic_diagnostics.argtypes = [C.c_void_p, c_dp]
+    L.mpic_download_rho.argtypes = [C.c_void_p, c_lp]
     L.mpic_gauss_residual.argtypes = [C.c_void_p, C.c_double, c_dp]
     L.mpic_get_owner.argtypes = [C.c_void_p, c_ip]
     L.mpic_migrate_tile.argtypes = [C.c_void_p, C.c_int, C.c_int]
@@ -188,14 +189,14 @@ class Sim:
     """Device-resident simulation (L1 API).  Mirrors the phases of the reference loop PIC_2D.cpp:171-420."""
 
     def __init__(self, nx, ny, tnx, tny, dx, dy, dt, guard=2, scheme=0, fma_mode=0, qm=-1.0, max_particles=0,
-                 rank=0, nranks=1, device=0, rows=None):
+                 rank=0, nranks=1, device=0, rows=None, deposit="zigzag"):
         """rows=(row0, nrows): this rank's tile rows (default: the even split of mpic_slab_rows; the rebalancer in slab.py
-        passes uneven ones)."""
+        passes uneven ones).  deposit: "zigzag" (charge conserving, default) or "cic" (direct CIC, SURVEY.md B.5 option a)."""
         L = lib()
         gtr = ny // tny
         row0, nrows = rows if rows is not None else slab_rows(gtr, nranks, rank)
         self.p = Params(nx, ny, tnx, tny, guard, scheme, fma_mode, rank, nranks, row0, nrows, device, dx, dy, dt, qm,
-                        max_particles)
+                        max_particles, {"zigzag": 0, "cic": 1}[deposit], 0)
         self.h = C.c_void_p()
         _chk(L.mpic_create(C.byref(self.p), C.byref(self.h)))
         self.nx, self.ny, self.tnx, self.tny, self.guard = nx, ny, tnx, tny, guard
@@ -432,6 +433,12 @@ class Sim:
         out = np.empty((3, self.nyl, self.nx), dtype=np.int64)
         ptrs = (c_lp * 3)(*[out[k].ctypes.data_as(c_lp) for k in range(3)])
         _chk(lib().mpic_download_current(self.h, ptrs))
+        return out
+
+    def download_rho(self):
+        """rho of the stored particles, int64 fixed point (value * 2^52), node lattice."""
+        out = np.empty((self.nyl, self.nx), dtype=np.int64)
+        _chk(lib().mpic_download_rho(self.h, out.ctypes.data_as(c_lp)))
         return out
 
     def diagnostics(self):

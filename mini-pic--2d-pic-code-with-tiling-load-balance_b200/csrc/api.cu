@@ -181,6 +181,7 @@ static int validate_params(const mpic_params* p) {
     REQUIRE(p->max_particles == 0 || (p->dt <= p->dx && p->dt <= p->dy), MPIC_EINVAL,
             "dt = %g exceeds min(dx, dy) = %g: a particle could cross more than one cell per step", p->dt, p->dx < p->dy ? p->dx : p->dy);
     REQUIRE(p->nranks >= 1 && p->rank >= 0 && p->rank < p->nranks, MPIC_EINVAL, "bad rank/nranks");
+    REQUIRE(p->deposit == 0 || p->deposit == 1, MPIC_EINVAL, "deposit must be 0 (zigzag) or 1 (direct CIC)");
     const int gtr = p->ny / p->tny;
     REQUIRE(p->row0 >= 0 && p->nrows >= 1 && p->row0 + p->nrows <= gtr, MPIC_EINVAL, "bad slab rows");
     REQUIRE(p->nranks > 1 || (p->row0 == 0 && p->nrows == gtr), MPIC_EINVAL, "single rank must own every tile row");
@@ -206,6 +207,7 @@ int mpic_set_geometry(mpic_sim* s) {
     P.h = 0.5 * p->dt * p->qm;
     P.cjx = 1.0 / (p->dy * p->dt); P.cjy = 1.0 / (p->dx * p->dt); P.cjz = 1.0 / (p->dx * p->dy);
     P.sjx = P.cjx * MPIC_JSCALE; P.sjy = P.cjy * MPIC_JSCALE; P.sjz = P.cjz * MPIC_JSCALE; P.dnx = (double)p->nx; P.dny = (double)p->ny;
+    P.deposit = p->deposit;
     YeeCoef& c = s->cf;
     c.bx = p->scheme ? p->dt / p->dx : p->dt / (2 * p->dx);
     c.by = p->scheme ? p->dt / p->dy : p->dt / (2 * p->dy);
@@ -959,6 +961,16 @@ static int deposit_rho_plane(mpic_sim* s) {
     TRY(launch_deposit_rho(s->P, G, s->pa[s->cur], s->n, s->rho, s->st));
     TRY(launch_fold_current(G, s->rho, 1, G.ywrap, s->st));
     s->launches += 3;
+    return 0;
+}
+int mpic_download_rho(mpic_sim* s, int64_t* rho) {
+    if (s) cudaSetDevice(s->prm.device);
+    REQUIRE(s && rho && s->cap > 0, MPIC_EINVAL, "bad argument");
+    const FieldGeom& G = s->G;
+    TRY(deposit_rho_plane(s));
+    CUDA_TRY(cudaMemcpy2DAsync(rho, (size_t)G.nx * 8, s->rho + (int64_t)G.g * G.pitch + MPIC_X0, (size_t)G.pitch * 8, (size_t)G.nx * 8,
+                               G.nyl, cudaMemcpyDeviceToHost, s->st));
+    CUDA_TRY(cudaStreamSynchronize(s->st));
     return 0;
 }
 int mpic_diagnostics(mpic_sim* s, double out[5]) {

@@ -80,6 +80,7 @@ struct PicConst {
     double cjx, cjy, cjz; // 1/(dy*dt), 1/(dx*dt), 1/(dx*dy)
     double sjx, sjy, sjz; // the same times 2^52 (exact): fixed-point scale folded into the charge factor
     double dnx, dny;      // (double)nx, (double)ny
+    int deposit;          // 0: charge-conserving zigzag (default); 1: direct CIC (SURVEY.md B.5 option a)
 };
 
 struct Particles {

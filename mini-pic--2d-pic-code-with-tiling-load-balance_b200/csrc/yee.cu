@@ -476,8 +476,8 @@ __global__ void halo_unpack_kernel(FieldGeom G, unsigned long long* __restrict__
 template <int TO_TILES>
 __global__ void tiles_kernel(FieldGeom G, double* __restrict__ f, double* __restrict__ grid6,
                              const int* __restrict__ lrow, const int* __restrict__ lcol, int tnx, int tny) {
-    const int t = blockIdx.y, jj = blockIdx.x;                       // jj: patch row 0..TY-1
     const int g = G.g, TX = tnx + 2 * g, TY = tny + 2 * g;
+    const int t = blockIdx.x / TY, jj = blockIdx.x - t * TY;         // jj: patch row 0..TY-1 (1-D grid: 65 536 tiles exceed gridDim.y)
     const int j = lrow[t] * tny + jj - g;                            // slab cell row (may be in the guard ring)
     const int i0 = lcol[t] * tnx - g;
     double* out = grid6 + ((int64_t)t * TY + jj) * TX * 6;
@@ -649,14 +649,14 @@ int launch_halo_unpack(const FieldGeom& G, double* base3, int is_current, const 
 int launch_planes_to_tiles(const FieldGeom& G, const double* planes, double* grid6, const int* lrow, const int* lcol,
                            int ntiles, int tnx, int tny, cudaStream_t st) {
     if (ntiles == 0) return 0;
-    tiles_kernel<1><<<dim3(tny + 2 * G.g, ntiles), 128, 0, st>>>(G, const_cast<double*>(planes), grid6, lrow, lcol, tnx, tny);
+    tiles_kernel<1><<<(unsigned)((int64_t)ntiles * (tny + 2 * G.g)), 128, 0, st>>>(G, const_cast<double*>(planes), grid6, lrow, lcol, tnx, tny);
     LAUNCH_CHECK();
     return 0;
 }
 int launch_tiles_to_planes(const FieldGeom& G, double* planes, const double* grid6, const int* lrow, const int* lcol,
                            int ntiles, int tnx, int tny, cudaStream_t st) {
     if (ntiles == 0) return 0;
-    tiles_kernel<0><<<dim3(tny + 2 * G.g, ntiles), 128, 0, st>>>(G, planes, const_cast<double*>(grid6), lrow, lcol, tnx, tny);
+    tiles_kernel<0><<<(unsigned)((int64_t)ntiles * (tny + 2 * G.g)), 128, 0, st>>>(G, planes, const_cast<double*>(grid6), lrow, lcol, tnx, tny);
     LAUNCH_CHECK();
     return 0;
 }

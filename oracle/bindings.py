@@ -45,7 +45,8 @@ class PicParams(C.Structure):
     _fields_ = [("nx", C.c_int), ("ny", C.c_int), ("tnx", C.c_int), ("tny", C.c_int),
                 ("dx", C.c_double), ("dy", C.c_double), ("dt", C.c_double),
                 ("inv_dx", C.c_double), ("inv_dy", C.c_double), ("box_x", C.c_double), ("box_y", C.c_double),
-                ("h", C.c_double), ("cjx", C.c_double), ("cjy", C.c_double), ("cjz", C.c_double)]
+                ("h", C.c_double), ("cjx", C.c_double), ("cjy", C.c_double), ("cjz", C.c_double),
+                ("deposit", C.c_int), ("reserved", C.c_int)]
 
 
 _cache = {}
@@ -165,9 +166,10 @@ def ref_run_loop(ref, global6, R, C_, tile_rows, tile_cols, g, dt, dx, dy, steps
 
 
 # ------------------------------------------------------------------------------------------ oracle wrappers
-def make_params(lib, nx, ny, tnx, tny, dx, dy, dt, qm=-1.0):
+def make_params(lib, nx, ny, tnx, tny, dx, dy, dt, qm=-1.0, deposit="zigzag"):
     p = PicParams()
     lib.orc_pic_make_params(C.byref(p), nx, ny, tnx, tny, dx, dy, dt, qm)
+    p.deposit = {"zigzag": 0, "cic": 1}[deposit]
     return p
 
 

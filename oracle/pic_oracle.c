@@ -38,6 +38,8 @@ typedef struct {
     double box_x, box_y;      /* nx*dx, ny*dy */
     double h;                 /* 0.5*dt*(q/m) */
     double cjx, cjy, cjz;     /* 1/(dy*dt), 1/(dx*dt), 1/(dx*dy) */
+    int deposit;              /* 0: charge-conserving zigzag (default); 1: direct CIC (SURVEY.md B.5 option a) */
+    int reserved;
 } orc_pic_params;
 
 void orc_pic_make_params(orc_pic_params* p, int nx, int ny, int tnx, int tny, double dx, double dy, double dt, double qm) {
@@ -46,6 +48,7 @@ void orc_pic_make_params(orc_pic_params* p, int nx, int ny, int tnx, int tny, do
     p->box_x = nx * dx; p->box_y = ny * dy;
     p->h = 0.5 * dt * qm;
     p->cjx = 1.0 / (dy * dt); p->cjy = 1.0 / (dx * dt); p->cjz = 1.0 / (dx * dy);
+    p->deposit = 0; p->reserved = 0;
 }
 
 static inline int wrapi(int i, int n) { return i < 0 ? i + n : i >= n ? i - n : i; }
@@ -161,10 +164,30 @@ void orc_push_deposit(const orc_pic_params* P, const double* ex, const double* e
         double ign = 1.0 / sqrt(g2n);
         double vx = unx * ign, vy = uny * ign, vz = unz * ign;
         double xn = fma(vx, dt, x[p]), yn = fma(vy, dt, y[p]);      /* unwrapped */
-        /* ---- charge-conserving zigzag deposit (Umeda et al. 2003), grid units */
         double X2 = xn * P->inv_dx, Y2 = yn * P->inv_dy;
         double fi2 = floor(X2), fj2 = floor(Y2);
         int i2 = (int)fi2, j2 = (int)fj2;
+        if (P->deposit == 1) {
+            /* ---- direct CIC (SURVEY.md B.5 option a): q v_k /(dx dy) at the time-centred position, weights of the E_k lattice:
+               Jx on Ex points (i+1/2, j), Jy on Ey points (i, j+1/2), Jz on nodes.  Not charge conserving. */
+            double Xm = 0.5 * (X1 + X2), Ym = 0.5 * (Y1 + Y2);
+            double fim = floor(Xm), fjm = floor(Ym);
+            double wxm = Xm - fim, wym = Ym - fjm;
+            double Xmh = Xm - 0.5, Ymh = Ym - 0.5;
+            double fimh = floor(Xmh), fjmh = floor(Ymh);
+            double wxmh = Xmh - fimh, wymh = Ymh - fjmh;
+            int im = (int)fim, jm = (int)fjm, imh = (int)fimh, jmh = (int)fjmh;
+            double qc = q[p] * P->cjz;
+            int64_t* pl[3] = { jx, jy, jz };
+            int ci[3] = { imh, im, im }, cj[3] = { jm, jmh, jm };
+            double qv[3] = { qc * vx, qc * vy, qc * vz }, wxx[3] = { wxmh, wxm, wxm }, wyy[3] = { wym, wymh, wym };
+            for (int c = 0; c < 3; c++) {
+                double a0 = qv[c] * (1.0 - wxx[c]), a1 = qv[c] * wxx[c], b0 = 1.0 - wyy[c];
+                jadd(pl[c], nx, ny, ci[c], cj[c], a0 * b0);          jadd(pl[c], nx, ny, ci[c] + 1, cj[c], a1 * b0);
+                jadd(pl[c], nx, ny, ci[c], cj[c] + 1, a0 * wyy[c]);  jadd(pl[c], nx, ny, ci[c] + 1, cj[c] + 1, a1 * wyy[c]);
+            }
+        } else {
+        /* ---- charge-conserving zigzag deposit (Umeda et al. 2003), grid units */
         double xr = fmin(fmin(fi1, fi2) + 1.0, fmax(fmax(fi1, fi2), 0.5 * (X1 + X2)));
         double yr = fmin(fmin(fj1, fj2) + 1.0, fmax(fmax(fj1, fj2), 0.5 * (Y1 + Y2)));
         double qjx = q[p] * P->cjx, qjy = q[p] * P->cjy;
@@ -185,6 +208,7 @@ void orc_push_deposit(const orc_pic_params* P, const double* ex, const double* e
         double qa0 = qz * (1.0 - wxm), qa1 = qz * wxm, b0 = 1.0 - wym;
         jadd(jz, nx, ny, im, jm, qa0 * b0);      jadd(jz, nx, ny, im + 1, jm, qa1 * b0);
         jadd(jz, nx, ny, im, jm + 1, qa0 * wym); jadd(jz, nx, ny, im + 1, jm + 1, qa1 * wym);
+        }
         /* ---- store, wrapped */
         ux[p] = unx; uy[p] = uny; uz[p] = unz;
         x[p] = wrap_pos(xn, P->box_x, P->inv_dx, nx);

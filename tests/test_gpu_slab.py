@@ -330,7 +330,7 @@ def test_single_process_ring_rebalance_in_place(world, kind):
     nx, ny, tn, dx, dy, dt = g["nx"], g["ny"], g["tnx"], g["dx"], g["dy"], g["dt"]
     ndev = max(1, torch.cuda.device_count())
     cap = parts["x"].shape[0]
-    sims = [m.Sim(nx, ny, tn, g["tny"], dx, dy, dt, max_particles=cap // world + 64, rank=r, nranks=world, device=r % ndev) for r in range(world)]
+    sims = [m.Sim(nx, ny, tn, g["tny"], dx, dy, dt, max_particles=cap, rank=r, nranks=world, device=r % ndev) for r in range(world)]
     for s in sims:
         r0, r1 = s.row0 * g["tny"], (s.row0 + s.nrows) * g["tny"]
         s.upload_planes([a[r0:r1] for a in planes])

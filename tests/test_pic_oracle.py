@@ -185,3 +185,117 @@ def test_cell_key_sort_is_a_stable_refinement_of_the_tile_sort():
         perm = np.argsort(ob.cell_keys(lib, P, c["x"], c["y"]), kind="stable")
         c = {k: np.ascontiguousarray(v[perm]) for k, v in c.items()}
     assert np.array_equal(c["tag"], b["tag"]) and np.array_equal(c["x"], b["x"])
+
+
+def test_relativistic_gyration_gamma_10():
+    """gamma = 10 (|u| = sqrt(99)): the Boris rotation conserves |u| to round-off, turns by 2 atan(h B / gamma) per step --
+    the relativistic gyro-frequency omega_c / gamma to second order -- and the particle moves |v| dt = (|u|/gamma) dt per step."""
+    nx = ny = 16; dx = dy = 0.1; dt = 0.03
+    P = ob.make_params(lib, nx, ny, 8, 8, dx, dy, dt)
+    pl = _zero_planes(nx, ny); pl[5][:] = 2.0
+    u0 = np.sqrt(99.0)
+    p = _one(0.8, 0.8, u0, 0.0, 0.0)
+    gam = np.sqrt(1 + u0**2)
+    assert abs(gam - 10.0) < 1e-14
+    ang, step_len = [], []
+    prev = (p["x"][0], p["y"][0])
+    for _ in range(400):
+        ob.push_deposit(lib, P, pl, p)
+        assert abs(np.sqrt(p["ux"][0]**2 + p["uy"][0]**2 + p["uz"][0]**2) - u0) < 5e-14 * u0
+        ang.append(np.arctan2(p["uy"][0], p["ux"][0]))
+        d = np.array([p["x"][0] - prev[0], p["y"][0] - prev[1]])
+        d -= np.array([P.box_x, P.box_y]) * np.round(d / np.array([P.box_x, P.box_y]))
+        step_len.append(np.hypot(*d)); prev = (p["x"][0], p["y"][0])
+    dphi = np.diff(np.unwrap(ang))
+    want = 2 * np.arctan(P.h * 2.0 / gam)
+    assert np.allclose(dphi, -want, rtol=0, atol=1e-12)
+    assert abs(abs(want) / dt - 2.0 / gam) < 1e-5 * 2.0 / gam          # omega_c / gamma, up to the O(dt^2) phase error of Boris
+    assert np.allclose(step_len, u0 / gam * dt, rtol=0, atol=1e-13)
+
+
+def test_oblique_drift_continuity_with_corner_crossers():
+    """A fast oblique beam at the CFL limit: most particles cross a cell face every step and many cross two (through a corner
+    region) -- the zigzag split must still satisfy the discrete continuity equation at every node, and the total current must
+    equal sum q v in all three components."""
+    nx, ny, tnx, tny = 16, 24, 8, 8; dx, dy = 0.1, 0.1
+    dt = 1.0 / np.sqrt(1 / dx**2 + 1 / dy**2)                           # cfl = 1: |v| dt up to 0.7 cells per axis
+    P = ob.make_params(lib, nx, ny, tnx, tny, dx, dy, dt)
+    parts = plasma.load_uniform(nx, ny, tnx, tny, dx, dy, 12, u_th=0.05, seed=21, drift=(3.0, -2.5, 1.0))
+    pl = _zero_planes(nx, ny)
+    crossed_both = 0
+    for _ in range(6):
+        rho0 = ob.deposit_rho(lib, P, parts).astype(np.float64) / 2.0**52
+        c0 = (np.floor(parts["x"] / dx).astype(int), np.floor(parts["y"] / dy).astype(int))
+        J = ob.push_deposit(lib, P, pl, parts).astype(np.float64) / 2.0**52
+        rho1 = ob.deposit_rho(lib, P, parts).astype(np.float64) / 2.0**52
+        c1 = (np.floor(parts["x"] / dx).astype(int), np.floor(parts["y"] / dy).astype(int))
+        crossed_both += int(((c0[0] != c1[0]) & (c0[1] != c1[1])).sum())
+        div = (J[0] - np.roll(J[0], 1, axis=1)) / dx + (J[1] - np.roll(J[1], 1, axis=0)) / dy
+        res = (rho1 - rho0) / dt + div
+        assert np.abs(res).max() < 1e-12 * np.abs(rho0).max() / dt
+        g = np.sqrt(1 + parts["ux"]**2 + parts["uy"]**2 + parts["uz"]**2)
+        for c, k in enumerate(("ux", "uy", "uz")):
+            assert abs(J[c].sum() * dx * dy - (parts["q"] * parts[k] / g).sum()) < 1e-12
+    print("corner crossers per step:", crossed_both / 6 / parts["x"].shape[0])
+    assert crossed_both > 0.2 * 6 * parts["x"].shape[0]
+
+
+def test_two_stream_total_momentum_stays_zero():
+    """Counter-streaming beams exchange momentum only with each other (the fields stay electrostatic: no E x B momentum).  The
+    scheme is charge-conserving, not momentum-conserving, so the net particle momentum is only nearly constant: through growth
+    AND saturation it drifts by 3e-3 of the momentum of one beam (bound: 1e-2), while each beam loses most of its own."""
+    nx, ny, tn, ppc, dx = 64, 8, 8, 64, 0.1
+    dt = 0.5 / np.sqrt(2) * dx
+    P = ob.make_params(lib, nx, ny, tn, tn, dx, dx, dt)
+    parts = plasma.load_uniform(nx, ny, tn, tn, dx, dx, ppc, u_th=0.01, two_stream=0.2, seed=77)   # thermal spread: no mirror symmetry
+    k = 2 * np.pi * 3 / P.box_x
+    parts["ux"] = parts["ux"] + 1e-5 * np.sin(k * parts["x"]) * (parts["ux"] > 0)                    # only one beam is seeded
+    beam = parts["ux"] > 0
+    tags_beam = parts["tag"][beam].copy()
+    mass = -parts["q"]                                                  # q/m = -1
+    p_beam0 = (mass[beam] * parts["ux"][beam]).sum()
+    pl = _zero_planes(nx, ny)
+    net0 = np.array([(mass * parts["ux"]).sum(), (mass * parts["uy"]).sum()])      # sampling noise of the thermal spread
+    worst = 0.0
+    for s in range(1300):
+        ob.pic_steps(lib, P, pl, parts, 1)
+        if s % 10 == 0:
+            net = np.array([(mass * parts["ux"]).sum(), (mass * parts["uy"]).sum()])
+            worst = max(worst, np.abs(net - net0).max() / p_beam0)
+    sel = np.isin(parts["tag"], tags_beam)                             # the same particles after 1300 sorts
+    p_beam1 = (mass[sel] * parts["ux"][sel]).sum()
+    print("net momentum / beam momentum, worst:", worst, " beam momentum kept:", p_beam1 / p_beam0)
+    assert worst < 1e-2, worst
+    assert p_beam1 < 0.9 * p_beam0                                      # saturation really happened: the beams slowed down
+
+
+def test_direct_cic_mode_total_current_and_no_continuity():
+    """deposit = 1 (SURVEY.md B.5 option a): the summed current still equals sum q v exactly (the weights of each lattice sum
+    to one), one resting-cell particle lands on the four Ex points around it with the bilinear weights, and -- unlike the
+    zigzag default -- the discrete continuity equation is violated (this is why the default is the charge-conserving one)."""
+    nx, ny, tnx, tny = 24, 16, 8, 8; dx, dy = 0.1, 0.125
+    dt = 0.5 / np.sqrt(1 / dx**2 + 1 / dy**2)
+    P = ob.make_params(lib, nx, ny, tnx, tny, dx, dy, dt, deposit="cic")
+    parts = plasma.load_uniform(nx, ny, tnx, tny, dx, dy, 9, u_th=0.6, seed=5)
+    pl = _zero_planes(nx, ny)
+    rho0 = ob.deposit_rho(lib, P, parts).astype(np.float64) / 2.0**52
+    J = ob.push_deposit(lib, P, pl, parts).astype(np.float64) / 2.0**52
+    rho1 = ob.deposit_rho(lib, P, parts).astype(np.float64) / 2.0**52
+    g = np.sqrt(1 + parts["ux"]**2 + parts["uy"]**2 + parts["uz"]**2)
+    for c, k in enumerate(("ux", "uy", "uz")):
+        assert abs(J[c].sum() * dx * dy - (parts["q"] * parts[k] / g).sum()) < 1e-13
+    div = (J[0] - np.roll(J[0], 1, axis=1)) / dx + (J[1] - np.roll(J[1], 1, axis=0)) / dy
+    res = (rho1 - rho0) / dt + div
+    assert np.abs(res).max() > 1e-6 * np.abs(rho0).max() / dt
+    # one particle, no fields: x_mid = (3.3 + v dt / 2) dx ... weights on the Ex lattice (i + 1/2, j)
+    p = _one(0.33 * 1.0, 0.40, 0.5, 0.0, 0.0, q=-2e-3)
+    x0, y0 = p["x"][0], p["y"][0]
+    J1 = ob.push_deposit(lib, P, pl, p).astype(np.float64) / 2.0**52
+    v = 0.5 / np.sqrt(1.25)
+    Xm, Ym = (x0 + 0.5 * v * dt) / dx, y0 / dy
+    i, j = int(np.floor(Xm - 0.5)), int(np.floor(Ym))
+    wx, wy = Xm - 0.5 - i, Ym - j
+    want = np.zeros((ny, nx))
+    amp = -2e-3 * v / (dx * dy)
+    want[j, i], want[j, i + 1], want[j + 1, i], want[j + 1, i + 1] = amp * (1 - wx) * (1 - wy), amp * wx * (1 - wy), amp * (1 - wx) * wy, amp * wx * wy
+    assert np.allclose(J1[0], want, rtol=0, atol=1e-15) and not J1[1].any()

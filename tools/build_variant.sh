@@ -9,5 +9,5 @@ OUT="$ROOT/build/variants"; mkdir -p "$OUT"
 /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -fmad=false -Xcompiler -fPIC -Xptxas -v "$@" \
     -c "$SRC/particles.cu" -o "$OUT/particles_$NAME.o" 2> "$OUT/particles_$NAME.ptxas.log"
 /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -shared -o "$OUT/libminipic_$NAME.so" "$SRC/api.o" "$SRC/yee.o" \
-    "$OUT/particles_$NAME.o" "$SRC/ring.o" "$SRC/peer.o" "$SRC/h5dump.o"
+    "$OUT/particles_$NAME.o" "$SRC/ring.o" "$SRC/peer.o" "$SRC/reslab.o" "$SRC/h5dump.o"
 grep -A2 "push_packed_kernelILi16ELi16E" "$OUT/particles_$NAME.ptxas.log" | grep "Used\|spill" | head -4
