@@ -56,8 +56,10 @@ WORKLOADS = {
 PUSH_BYTES_SURVEY = 90.0
 PUSH_BYTES_FUSED_REORDER = 104.0
 # constant, NOT measured by the run that prints it: dram__bytes_read+write of one push launch in the saturated regime,
-# ncu --set full, profiles/r02q_ncu_full_push_packed_saturated_raw.csv: 1.045 GB + 0.869 GB over 16 777 216 particles
-NCU_TRAFFIC_BYTES_PER_PARTICLE = 114.1
+# ncu --set full, profiles/r02z_ncu_full_push_packed_saturated_raw.csv: 1.094 GB + 0.871 GB over 16 777 216 particles
+NCU_TRAFFIC_BYTES_PER_PARTICLE = 117.2
+# ncu --set full, profiles/r02z_ncu_full_fused_yee_8192_raw.csv: 3.238 GB + 3.179 GB over 8192^2 cells (algorithmic: 96 B/cell)
+NCU_YEE_TRAFFIC_BYTES_PER_CELL = 95.6
 SORT_BYTES_PER_PARTICLE = 5.0      # what is left of the sort: direction codes read (1) + permutation written (4); the rest is per cell
 YEE_BYTES_3SWEEP = 216.0           # reference-faithful half-B, E, half-B: 3 x 72 B per cell
 YEE_BYTES_ALGO = 144.0             # SURVEY.md section 8(d) algorithmic figure (2 sweeps)
@@ -333,7 +335,10 @@ def yee_bench(m, torch, steps, warmup, n=8192):
            "config": {"workload": f"vacuum pulse {n}x{n}, half-B/E/half-B per step in one fused kernel", "fields_bytes": 48 * n * n},
            "gpu_launches": launches,
            "roofline": {"bound": "hbm", "kernel": "fused_yee_kernel", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
-                        "traffic": None, "bytes_per_cell_update": YEE_BYTES_FUSED,
+                        "traffic": NCU_YEE_TRAFFIC_BYTES_PER_CELL * float(n) * n,
+                        "traffic_source": "CONSTANT from one ncu --set full capture of this kernel at 8192^2 (profiles/r02z_ncu_full_fused_yee_8192_raw.csv: "
+                                          "95.6 B/cell), per launch; not measured by this run",
+                        "bytes_per_cell_update": YEE_BYTES_FUSED,
                         "frac_of_144B_figure": cells * YEE_BYTES_ALGO / (ms * 1e-3) / 1e9 / peak, "peak_source": how,
                         "note": "96 B/cell: six planes read once + written once (halo ring re-reads are served by L2); SURVEY's 144 B "
                                 "figure assumes two sweeps, so its fraction exceeds 1"},
@@ -391,8 +396,8 @@ def push_roofline(n, t, peak, peak_how):
             "bytes_per_particle": PUSH_BYTES_SURVEY,
             "frac_104B": gbs / peak * PUSH_BYTES_FUSED_REORDER / PUSH_BYTES_SURVEY,
             "traffic": NCU_TRAFFIC_BYTES_PER_PARTICLE * n,
-            "traffic_source": "CONSTANT from one ncu --set full capture of this kernel in the saturated regime (profiles/r02q_ncu_full_push_packed_saturated_raw.csv: "
-                              "114.1 B/particle), scaled by the particle count; not measured by this run",
+            "traffic_source": "CONSTANT from one ncu --set full capture of this kernel in the saturated regime (profiles/r02z_ncu_full_push_packed_saturated_raw.csv: "
+                              "117.2 B/particle), scaled by the particle count; not measured by this run",
             "pushes_per_s_kernel_only": n / (t["push_ms"] * 1e-3), "peak_source": peak_how,
             "sort_gbs": n * SORT_BYTES_PER_PARTICLE / (t["sort_ms"] * 1e-3) / 1e9,
             "note": "frac: SURVEY.md 8(d)'s 88 B push + 2.3 B grid = 90 B/particle.  frac_104B: what this kernel must move, since it is also the "

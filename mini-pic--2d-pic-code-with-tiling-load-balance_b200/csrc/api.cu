@@ -155,6 +155,8 @@ static int make_tensor_map(mpic_sim* s) {
     int pw, ph;
     push_box_dims(s->P.tnx, s->P.tny, &pw, &ph);
     TRY(encode_box_map(s, s->planes, pw, ph, &s->tmap));
+    pack_box_dims(s->P.tnx, s->P.tny, &pw, &ph);
+    TRY(encode_box_map(s, s->planes, pw, ph, &s->tmap_pack));
     s->has_tmap = true;
     return 0;
 }
@@ -316,7 +318,7 @@ int mpic_create(const mpic_params* p, mpic_sim** out) {
     CUDA_TRY(cudaGetDeviceProperties(&prop, p->device));
     s->nsm = prop.multiProcessorCount;
     CUDA_TRY(cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking));
-    if (p->nranks == 1 && !getenv("MPIC_NO_SORT_OVERLAP")) {
+    if (!getenv("MPIC_NO_SORT_OVERLAP")) {   // single slab: every step; slabs: the peer-ring step (mpic_peer_step_end)
         CUDA_TRY(cudaStreamCreateWithFlags(&s->st_sort, cudaStreamNonBlocking));
         CUDA_TRY(cudaEventCreateWithFlags(&s->ev_push, cudaEventDisableTiming));
         CUDA_TRY(cudaEventCreateWithFlags(&s->ev_sort, cudaEventDisableTiming));
@@ -501,6 +503,8 @@ int mpic_fused_setup(mpic_sim* s) {
     if (s->has_tmap) {
         push_box_dims(s->P.tnx, s->P.tny, &pw, &ph);
         TRY(encode_box_map(s, s->planes_alt, pw, ph, &s->tmap_alt));
+        pack_box_dims(s->P.tnx, s->P.tny, &pw, &ph);
+        TRY(encode_box_map(s, s->planes_alt, pw, ph, &s->tmap_pack_alt));
     }
     s->fused_ready = true;
     return 0;
@@ -508,7 +512,7 @@ int mpic_fused_setup(mpic_sim* s) {
 void mpic_fused_swap(mpic_sim* s) {
     std::swap(s->planes, s->planes_alt);
     std::swap(s->ftmap, s->ftmap_alt);
-    if (s->has_tmap) std::swap(s->tmap, s->tmap_alt);
+    if (s->has_tmap) { std::swap(s->tmap, s->tmap_alt); std::swap(s->tmap_pack, s->tmap_pack_alt); }
     for (int side = 0; side < 2; side++) std::swap(s->peer[side].planes, s->peer[side].planes_alt);
 }
 // one fused half-B / E / half-B step of a single slab (periodic in y inside the kernel's images)
@@ -629,7 +633,7 @@ static int materialise(mpic_sim* s) {
 //   scan -> offsets -> perm_stable (+ arrivals appended); no particle data moves, the next push gathers through perm.
 // otherwise (uploads, loads, appends: arbitrary storage order): keys from the stored positions, histogram, scan, provisional
 //   permutation, per-cell ascending sort of the permutation (== stable order), physical gather.
-static int sort_all(mpic_sim* s, bool counted) {
+static int sort_all(mpic_sim* s, bool counted, cudaStream_t force = nullptr) {
     counted = counted && s->counts_valid;
     s->counts_valid = false;
     const int64_t total = s->n + s->arrived;
@@ -637,8 +641,11 @@ static int sort_all(mpic_sim* s, bool counted) {
         // single slab: on the sort stream, behind the push only -- whatever was queued on the main stream since (the field
         // update: it touches the planes and the current, the sort the move counts and the permutation) runs next to it; the
         // main stream continues once both are done
+        // (peer-ring slabs: mpic_peer_step_end forces the sort stream -- already ordered behind the migration counts -- so that
+        // the absorb of the arrivals and the sort run next to the E and second half-B sweeps)
         cudaStream_t st = s->st;
-        if (s->st_sort && s->arrived == 0) { st = s->st_sort; CUDA_TRY(cudaStreamWaitEvent(st, s->ev_push, 0)); }
+        if (force) st = force;
+        else if (s->st_sort && s->prm.nranks == 1 && s->arrived == 0) { st = s->st_sort; CUDA_TRY(cudaStreamWaitEvent(st, s->ev_push, 0)); }
         if (!s->moves_counted) { TRY(launch_count_moves(s->P, s->G.ywrap, s->mcnt, s->cell_count, st)); s->launches++; }
         s->moves_counted = false;
         TRY(launch_scan_cells(s->cell_count, s->cell_start_alt, s->n_entries, s->scan_tmp, st));
@@ -735,7 +742,7 @@ int mpic_push_deposit(mpic_sim* s) {
     REQUIRE(s->arrived == 0, MPIC_ESTATE, "arrivals absorbed but not sorted in: call mpic_sort_tiles before the next push");
     REQUIRE(!s->counts_valid, MPIC_ESTATE, "particles moved but not re-sorted: call mpic_sort_tiles between pushes");
     s->left = s->prm.nranks > 1 ? -1 : 0;
-    TRY(launch_push_deposit(s->P, s->G, &s->tmap, s->jacc, s->pa[s->cur], s->pa[s->cur ^ 1], s->perm,
+    TRY(launch_push_deposit(s->P, s->G, &s->tmap, &s->tmap_pack, s->jacc, s->pa[s->cur], s->pa[s->cur ^ 1], s->perm,
                             s->cell_start, s->mcnt, s->dirs, s->push_split, s->lv, s->st, s->n));
     s->cur ^= 1;                    // the push wrote the other buffer in slot order
     s->perm_valid = false;
@@ -743,7 +750,8 @@ int mpic_push_deposit(mpic_sim* s) {
     // slot order into the send buffers, their counts into lv.count and the two leaver bins of the histogram
     s->launches++;
     s->moves_counted = false;
-    if (s->st_sort) CUDA_TRY(cudaEventRecord(s->ev_push, s->st));     // single slab: the histogram is formed by the sort, on its stream
+    // single slab, and the peer-ring step on slabs: the histogram is formed by the sort, on its stream
+    if (s->st_sort && (s->prm.nranks == 1 || s->defer_count)) CUDA_TRY(cudaEventRecord(s->ev_push, s->st));
     else { TRY(launch_count_moves(s->P, s->G.ywrap, s->mcnt, s->cell_count, s->st)); s->launches++; s->moves_counted = true; }
     if (s->prm.nranks > 1) {
         TRY(launch_leavers(s->P, s->pa[s->cur], s->cell_start, s->dirs, s->mcnt, s->lv_off, s->cell_count, s->lv, s->st));
@@ -753,6 +761,7 @@ int mpic_push_deposit(mpic_sim* s) {
     return 0;
 }
 int mpic_sort_after_push(mpic_sim* s) { return sort_all(s, true); }
+int mpic_sort_after_push_on(mpic_sim* s, void* stream) { return sort_all(s, true, (cudaStream_t)stream); }
 int mpic_sort_uploaded(mpic_sim* s) { s->perm_valid = false; s->counts_valid = false; s->arrived = 0; return sort_all(s, false); }
 int mpic_sort_tiles(mpic_sim* s) {
     if (s) cudaSetDevice(s->prm.device);
@@ -847,7 +856,7 @@ static int pic_step_host_pipelined(mpic_sim* s, double* const planes[6], int64_t
         TRY(launch_scan_cells(s->pipe_count, s->pipe_start, s->n_entries, s->scan_tmp, s->st));
         TRY(launch_perm_build(s->P, s->keys + lo, m, s->pipe_count, s->perm + lo, s->st));
         TRY(launch_segsort(s->pipe_start, s->P.ncells, s->perm + lo, s->keys + lo, s->st));
-        TRY(launch_push_deposit(s->P, s->G, &s->tmap, s->jacc, Ac, Bc, s->perm + lo, s->pipe_start, s->mcnt, s->dirs + lo,
+        TRY(launch_push_deposit(s->P, s->G, &s->tmap, &s->tmap_pack, s->jacc, Ac, Bc, s->perm + lo, s->pipe_start, s->mcnt, s->dirs + lo,
                                 s->push_split, s->lv, s->st, 0));      // chunk occupancy unknown: adaptive lane groups
         s->launches += 8;
         CUDA_TRY(cudaEventRecord(s->pipe_ev_done[c], s->st));

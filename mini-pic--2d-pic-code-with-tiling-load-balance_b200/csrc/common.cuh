@@ -139,8 +139,8 @@ int launch_gauss_residual(const FieldGeom& G, const double* planes, const int64_
                           double inv_dy, double* out_max, int j_first, cudaStream_t st);
 
 // ---- kernel launchers implemented in particles.cu
-int launch_push_deposit(const PicConst& P, const FieldGeom& G, const CUtensorMap* tmap, int64_t* jacc, Particles src,
-                        Particles dst, const int* perm, const int* cell_start, int* mcnt, unsigned char* dirs, int split,
+int launch_push_deposit(const PicConst& P, const FieldGeom& G, const CUtensorMap* tmap, const CUtensorMap* tmap_pack, int64_t* jacc,
+                        Particles src, Particles dst, const int* perm, const int* cell_start, int* mcnt, unsigned char* dirs, int split,
                         LeaveBufs lv, cudaStream_t st, int64_t n_hint);   // n_hint: particles in the slab (picks the sparse-cell variant)
 int launch_count_moves(const PicConst& P, int ywrap, const int* mcnt, int* cell_count, cudaStream_t st);
 int launch_offsets(const PicConst& P, int ywrap, const int* mcnt, const int* start_new, int* offtab, int* cursor, cudaStream_t st);
@@ -166,6 +166,7 @@ int launch_load_uniform(const PicConst& P, Particles p, int64_t first, int64_t n
                         cudaStream_t st);
 size_t push_smem_bytes(int tnx, int tny);
 void push_box_dims(int tnx, int tny, int* pw, int* ph);
+void pack_box_dims(int tnx, int tny, int* pw, int* ph);   // packed-walk kernel: (PW, PACK_ROWS + 2)
 int launch_sum_i64(const int64_t* a, int64_t n, double* out, cudaStream_t st);
 int launch_selftest_math(int64_t n, uint64_t seed, unsigned long long* bad, cudaStream_t st);
 int yee_preload();

@@ -441,7 +441,9 @@ int mpic_peer_step_begin(mpic_sim* s) {
         s->lv.wait_err = s->ctl + CTL_ERROR; s->lv.wait_timeout_ns = timeout_ns(); s->lv.wait_phase = s->pending_ph;
     }
     tp(s, 1);
+    s->defer_count = s->st_sort != nullptr;              // the destination histogram is formed on the sort stream in step_end
     const int rc = mpic_push_deposit(s);
+    s->defer_count = false;
     s->lv.wait_want = 0;
     TRY(rc);
     tp(s, 2);
@@ -477,14 +479,24 @@ int mpic_peer_step_end(mpic_sim* s) {
     s->left = (int64_t)leave[0] + leave[1];
     s->migrated_total += s->left;
     REQUIRE(s->n + (int64_t)arr[0] + (int64_t)arr[1] <= s->cap, MPIC_ENOMEM, "particle capacity exceeded by arrivals");
+    // The counts are known once the first half-B is done; the E sweep and the second half-B are still running on the main stream.
+    // Histogram, absorb and the stable sort touch particle arrays and cell tables only, the sweeps planes and current only: they
+    // go to the sort stream, ordered behind the counts kernel, and the main stream waits for them at the end.
+    cudaStream_t ss = s->st_sort ? s->st_sort : s->st;
+    if (ss != s->st) CUDA_TRY(cudaStreamWaitEvent(ss, s->ev_counts, 0));
+    if (!s->moves_counted) {
+        TRY(launch_count_moves(s->P, s->G.ywrap, s->mcnt, s->cell_count, ss));
+        s->launches++;
+        s->moves_counted = true;
+    }
     for (int side = 0; side < 2; side++) {               // appended in (lower, upper) order -- SURVEY.md B.8
         const int n = (int)arr[side];
         TRY(launch_absorb(s->P, s->pa[s->cur], s->n + s->arrived, s->arrive_blk + (int64_t)(par * 2 + side) * s->lv.cap * MPIC_REC_DOUBLES,
-                          n, s->cell_count, s->keys, s->G.err, s->st));
+                          n, s->cell_count, s->keys, s->G.err, ss));
         s->arrived += n;
         s->launches += n > 0;
     }
-    TRY(mpic_sort_after_push(s));
+    TRY(mpic_sort_after_push_on(s, ss));
     tp(s, 11);
     trace_collect(s);
     return 0;

@@ -31,6 +31,7 @@ struct mpic_sim {
     // blocks (and every map / peer pointer bound to them) are swapped, so `planes` always names the current fields
     double* planes_alt = nullptr;
     CUtensorMap tmap_alt, ftmap, ftmap_alt;   // push box on planes_alt; fused-step box on planes / planes_alt
+    CUtensorMap tmap_pack, tmap_pack_alt;     // packed-walk push: part-row box on planes / planes_alt
     bool fused_ready = false;
     double* d_scratch = nullptr;   // 8 doubles
     int64_t tag_base = 0;
@@ -82,6 +83,7 @@ struct mpic_sim {
     // single slab: the sort after a push runs on its own stream, next to the field update (neither reads what the other writes)
     cudaStream_t st_sort = nullptr;
     cudaEvent_t ev_push = nullptr, ev_sort = nullptr;
+    bool defer_count = false;      // slabs, peer-ring step: count_moves is left to the sort stream (mpic_peer_step_end)
     bool moves_counted = false;    // cell_count already holds the destination histogram of the last push (count_moves ran)
     cudaEvent_t pipe_ev_up[MPIC_PIPE_MAX] = {}, pipe_ev_done[MPIC_PIPE_MAX] = {}, pipe_ev_free = nullptr;
     int* pipe_count = nullptr;     // per-chunk cell histogram / scatter cursor
@@ -108,6 +110,7 @@ int mpic_fused_setup(mpic_sim* s);                   // api.cu: second plane blo
 void mpic_fused_swap(mpic_sim* s);                   // api.cu: planes <-> planes_alt (+ maps, + peer pointers)
 void mpic_peer_release(mpic_sim* s);
 extern "C" int mpic_sort_after_push(mpic_sim* s);   // api.cu: sort_all(counted)
+extern "C" int mpic_sort_after_push_on(mpic_sim* s, void* stream);   // the same, every launch on `stream`; the main stream then waits for it
 #define HALO_HDR 16                /* values (128 B) of header in front of each halo message; [0] = leaver count to that side */
 #define REQUIRE(cond, code, ...) do { if (!(cond)) { mpic_set_error(__VA_ARGS__); return code; } } while (0)
 #define TRY(expr) do { int _r = (expr); if (_r) return _r; } while (0)

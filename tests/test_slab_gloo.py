@@ -192,3 +192,35 @@ def test_policy_reproduces_the_measured_beam_partition():
     load = [costs[r0:r0 + nr].sum() for r0, nr in parts]
     even = [costs[r * 32:(r + 1) * 32].sum() for r in range(8)]
     assert max(load) / np.mean(load) < 1.01 and max(even) / np.mean(even) > 1.9
+
+
+def test_partition_is_optimal_against_brute_force():
+    """mpic_partition_rows (host C behind slab.balanced_slab_rows): on random small problems the bottleneck equals the minimum
+    over ALL contiguous partitions with non-empty slabs; mpic_rebalance_plan keeps the old partition unless the gain is real."""
+    import itertools
+    m = importlib.import_module(PKG)
+    rng = np.random.default_rng(12)
+    for _ in range(200):
+        n = int(rng.integers(2, 11))
+        k = int(rng.integers(1, min(n, 5) + 1))
+        c = rng.integers(0, 50, n).astype(np.float64) + (rng.random(n) < 0.2) * 500.0
+        parts = m.partition_rows(c, k)
+        assert len(parts) == k and parts[0][0] == 0 and parts[-1][0] + parts[-1][1] == n
+        assert all(nr >= 1 for _, nr in parts) and all(parts[i][0] + parts[i][1] == parts[i + 1][0] for i in range(k - 1))
+        got = max(c[r0:r0 + nr].sum() for r0, nr in parts)
+        best = min(max(c[a:b].sum() for a, b in zip((0,) + cut, cut + (n,))) for cut in itertools.combinations(range(1, n), k - 1))
+        assert got == best, (c, k, parts)
+    with pytest.raises(m.MpicError):
+        m.partition_rows(np.ones(3), 4)
+    # plan: occupancy -> cost = particles + w_cell * cells; a balanced slab set stays, an imbalanced one moves
+    even = [(0, 4), (4, 4), (8, 4), (12, 4)]
+    changed, rows, cost = m.rebalance_plan(np.full(16, 1000), 256, even, 8.0)
+    assert not changed and rows == even and cost[0] == cost[1]
+    occ = np.full(16, 100)
+    occ[:4] = 50000
+    changed, rows, cost = m.rebalance_plan(occ, 256, even, 8.0)
+    assert changed and rows[0][1] < 4 and cost[1] < 0.95 * cost[0]
+    changed2, rows2, _ = m.rebalance_plan(occ, 256, rows, 8.0)
+    assert not changed2 and rows2 == rows                       # the plan is a fixed point
+    changed3, rows3, _ = m.rebalance_plan(occ, 256, even, 8.0, min_gain=0.99)
+    assert not changed3 and rows3 == even                       # gain threshold
