@@ -279,11 +279,13 @@ def test_upload_rejects_positions_outside_the_box():
     assert rc == -1 and b"null" in m.lib().mpic_last_error()
 
 
-@pytest.mark.parametrize("cfg", [(32, 32, 16, 16, 8, 0.3, 0.0), (48, 32, 8, 8, 40, 0.6, 0.2), (64, 32, 16, 16, 3, 0.9, 0.0)])
+@pytest.mark.parametrize("cfg", [(32, 32, 16, 16, 8, 0.3, 0.0), (48, 32, 8, 8, 40, 0.6, 0.2), (64, 32, 16, 16, 3, 0.9, 0.0),
+                                 (16, 16, 8, 8, 300, 0.7, 0.0)])
 def test_sort_is_stable_and_reproducible(cfg):
     """SURVEY.md B.8 / VERDICT r1 item 7: after 10 steps the slot order (the order a download returns) equals the oracle's
     STABLE sort by (tile, cell) element-wise -- tag[] and every component --, and two identical runs return identical arrays.
-    Covers dense cells (two chunks per cell), sparse ones (lane groups of 8) and many cell crossers per step."""
+    Covers dense cells (two chunks per cell; packed 8-bit running mover counts), sparse ones (lane groups of 8), many cell
+    crossers per step, and cells of 300 particles (running counts in shared memory)."""
     nx, ny, tnx, tny, ppc, u_th, ts = cfg
     outs = []
     for rep in range(2):
