@@ -432,7 +432,8 @@ def pic_record(m, torch, name, w, K, W, local, peak, peak_how, clocks=True, keep
         rec["clocks"] = clk.summary()
     # self-check: nothing lost, charge conserved, Gauss's law at round-off (charge-conserving deposit)
     q0 = -1.0 * dx * dy / w["ppc"] * n if "beam_ppc" not in w else diag["charge"]
-    ok = diag["particles"] == n and abs(diag["charge"] - q0) <= 1e-9 * abs(q0) and diag["gauss_residual"] < 1e-9
+    # (the beam load is not a solution of Gauss's law at t = 0 -- a dense band on zero fields --, so only the neutral loads are held to it)
+    ok = diag["particles"] == n and abs(diag["charge"] - q0) <= 1e-9 * abs(q0) and (diag["gauss_residual"] < 1e-9 or "beam_ppc" in w)
     rec["self_check"] = {"ok": bool(ok), "particles": diag["particles"], "charge_error": float(diag["charge"] - q0),
                          "gauss_residual": float(diag["gauss_residual"])}
     if not ok:

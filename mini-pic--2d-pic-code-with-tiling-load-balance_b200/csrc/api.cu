@@ -224,9 +224,9 @@ int mpic_alloc_state(mpic_sim* s) {
     CUDA_TRY(cudaMemsetAsync(s->planes, 0, (size_t)6 * G.plane * 8, s->st));
     CUDA_TRY(cudaMalloc(&s->jacc, (size_t)3 * G.plane * 8));
     CUDA_TRY(cudaMemsetAsync(s->jacc, 0, (size_t)3 * G.plane * 8, s->st));
-    CUDA_TRY(cudaMalloc(&s->d_scratch, 64 + 8));
+    CUDA_TRY(cudaMalloc(&s->d_scratch, (size_t)(16 + MPIC_DIAG_WORK) * 8));   // [0,8) results, [8] error word, [16..) reduction work space
     G.err = (unsigned int*)(s->d_scratch + 8);            // the handle's device error word
-    CUDA_TRY(cudaMemsetAsync(s->d_scratch, 0, 64 + 8, s->st));
+    CUDA_TRY(cudaMemsetAsync(s->d_scratch, 0, (size_t)(16 + MPIC_DIAG_WORK) * 8, s->st));
     s->cap = p->max_particles;
     if (s->cap > 0) {
         TRY(alloc_particles(&s->pa[0], s->cap));
@@ -988,13 +988,13 @@ int mpic_diagnostics(mpic_sim* s, double out[5]) {
     const FieldGeom& G = s->G;
     if (s->peer_on) TRY(mpic_sync(s));
     CUDA_TRY(cudaMemsetAsync(s->d_scratch, 0, 64, s->st));
-    TRY(launch_field_energy(G, s->planes, s->d_scratch, s->st));
+    TRY(launch_field_energy(G, s->planes, s->d_scratch, s->d_scratch + 16, s->st));
     s->launches++;
     double h[8] = { 0 };
     double mean_rho = 0.0;
     if (s->cap > 0 && s->n > 0) {
         TRY(materialise(s));
-        TRY(launch_kinetic(s->pa[s->cur], s->n, s->d_scratch + 1, s->st));
+        TRY(launch_kinetic(s->pa[s->cur], s->n, s->d_scratch + 1, s->d_scratch + 16, s->st));
         s->launches++;
         TRY(deposit_rho_plane(s));
     }

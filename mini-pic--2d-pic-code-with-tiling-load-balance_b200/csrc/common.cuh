@@ -134,7 +134,7 @@ int launch_tiles_to_planes(const FieldGeom& G, double* planes, const double* gri
 int launch_tile_b_half(const double* E3, const double* Bo3, double* Bn3, int tnx, int tny, int g, double cx, double cy, cudaStream_t st);
 int launch_tile_e_full(double* E3, const double* B3, int tnx, int tny, int g, double cx, double cy, cudaStream_t st);
 int launch_strip_copy(const double* src6, double* dst6, int TX, int r0, int c0, int nr, int nc, int to_strip, cudaStream_t st);
-int launch_field_energy(const FieldGeom& G, const double* planes, double* out, cudaStream_t st);
+int launch_field_energy(const FieldGeom& G, const double* planes, double* out, double* work, cudaStream_t st);   // work: MPIC_DIAG_WORK doubles
 int launch_gauss_residual(const FieldGeom& G, const double* planes, const int64_t* rho, double mean_rho, double inv_dx,
                           double inv_dy, double* out_max, int j_first, cudaStream_t st);
 
@@ -159,7 +159,8 @@ int launch_scan_cells(int* cell_count, int* cell_start, int n_entries, int* bloc
 int launch_crossers(const unsigned char* dirs, int64_t n, unsigned long long* out, cudaStream_t st);
 int launch_tile_counts(const PicConst& P, const int* cell_start, int* counts, cudaStream_t st);
 int launch_particle_tiles(const PicConst& P, Particles p, int64_t n, int row0, int* gid, cudaStream_t st);
-int launch_kinetic(Particles p, int64_t n, double* out2, cudaStream_t st);
+int launch_kinetic(Particles p, int64_t n, double* out2, double* work, cudaStream_t st);
+#define MPIC_DIAG_WORK (2 + 296 + 2 * 592)             /* two tickets + block partials of the energy reductions */
 int launch_deposit_rho(const PicConst& P, const FieldGeom& G, Particles p, int64_t n, int64_t* rho, cudaStream_t st);
 int launch_load_uniform(const PicConst& P, Particles p, int64_t first, int64_t nsel, int cy_lo, int64_t tag0, int ppc,
                         double u_th, double d0, double d1, double d2, double two_stream, double qp, uint64_t seed,

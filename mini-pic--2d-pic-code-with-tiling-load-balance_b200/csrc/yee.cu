@@ -521,7 +521,10 @@ __global__ void strip_kernel(const double* __restrict__ src, double* __restrict_
 }
 
 // ---- diagnostics
-__global__ void field_energy_kernel(FieldGeom G, const double* __restrict__ f, double* __restrict__ out) {
+// Diagnostics are REPRODUCIBLE: every block writes its partial sum, the last block to finish (ticket) adds the partials in block
+// order -- no floating-point atomics, so two runs (or two code paths that produce the same fields) print the same digits.
+__global__ void field_energy_kernel(FieldGeom G, const double* __restrict__ f, double* __restrict__ out, double* __restrict__ part,
+                                    unsigned int* __restrict__ ticket) {
     __shared__ double sh[256];
     double s = 0.0;
     const int64_t n = (int64_t)G.nx * G.nyl;
@@ -533,7 +536,17 @@ __global__ void field_energy_kernel(FieldGeom G, const double* __restrict__ f, d
     sh[threadIdx.x] = s;
     __syncthreads();
     for (int w = 128; w > 0; w >>= 1) { if (threadIdx.x < w) sh[threadIdx.x] += sh[threadIdx.x + w]; __syncthreads(); }
-    if (threadIdx.x == 0) atomicAdd(out, sh[0]);
+    if (threadIdx.x == 0) {
+        part[blockIdx.x] = sh[0];
+        __threadfence();
+        if (atomicAdd(ticket, 1u) == gridDim.x - 1) {
+            __threadfence();
+            double t = 0.0;
+            for (unsigned b = 0; b < gridDim.x; b++) t += ((volatile double*)part)[b];
+            *out = t;
+            *ticket = 0u;
+        }
+    }
 }
 __global__ void gauss_kernel(FieldGeom G, const double* __restrict__ f, const int64_t* __restrict__ rho, double mean_rho,
                              double inv_dx, double inv_dy, double* __restrict__ out_max, int j_first) {
@@ -677,8 +690,8 @@ int launch_strip_copy(const double* src6, double* dst6, int TX, int r0, int c0, 
     LAUNCH_CHECK();
     return 0;
 }
-int launch_field_energy(const FieldGeom& G, const double* planes, double* out, cudaStream_t st) {
-    field_energy_kernel<<<296, 256, 0, st>>>(G, planes, out);
+int launch_field_energy(const FieldGeom& G, const double* planes, double* out, double* work, cudaStream_t st) {
+    field_energy_kernel<<<296, 256, 0, st>>>(G, planes, out, work + 2, (unsigned int*)work);
     LAUNCH_CHECK();
     return 0;
 }

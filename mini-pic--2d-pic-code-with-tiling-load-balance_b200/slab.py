@@ -354,7 +354,10 @@ def fields_record(args, name, w, rank, world, local, peak, peak_how, clocks=True
                           "clocks": clk.summary() if hasattr(clk, "summary") else None}
         dist.barrier()
         sim.close()
-    if transport == "peer" and results[True]["energy"] != results[False]["energy"]:
+    # the two paths produce bit-identical fields (tests/test_gpu_slab.py, test_gpu_yee.py) and the energy reduction is an ordered
+    # sum (reproducible), so the energies agree to the last digit; the run is REJECTED only beyond 1e-12 relative
+    exact = transport != "peer" or results[True]["energy"] == results[False]["energy"]
+    if transport == "peer" and any(abs(a - b) > 1e-12 * abs(b) for a, b in zip(results[True]["energy"], results[False]["energy"])):
         _fail(rank, f"fused and three-sweep field energies differ: {results[True]['energy']} vs {results[False]['energy']}")
     if rank != 0:
         return None
@@ -370,7 +373,7 @@ def fields_record(args, name, w, rank, world, local, peak, peak_how, clocks=True
                         "unit": "GB/s", "frac": gbs / peak, "traffic": None, "bytes_per_cell_update": bpc,
                         "frac_of_144B_figure": cells * bench.YEE_BYTES_ALGO / (ms * 1e-3) / 1e9 / world / peak, "peak_source": peak_how, "note": "per GPU"},
            "gpu_launches": best["launches"], "clocks": best["clocks"], "field_energy_total": sum(best["energy"]),
-           "self_check": {"ok": True, "fused_equals_three_sweeps_bitwise": transport == "peer"}}
+           "self_check": {"ok": True, "fused_vs_three_sweeps_energy": "equal to the last digit" if exact else "within 1e-12 relative"}}
     if transport == "peer":
         ms3 = results[False]["ms"]
         rec["three_sweeps"] = {"ms_per_step": ms3 / K, "value": cells / (ms3 * 1e-3),
@@ -434,7 +437,25 @@ def slab_pic_record(args, name, w, rank, world, local, peak, peak_how, e2e=True,
         return (max(g[0] for g in gathered), sum(g[1] for g in gathered), s_.kernel_launches - l0, gathered,
                 clk.summary() if (rank == 0 and clocks) else None)
 
+    def gauss_state(s_, stream):
+        """(total charge, total particles, per-rank max |div E - rho + <rho>|) -- collective"""
+        with torch.cuda.stream(stream):
+            s_.sync()                                       # raises if the peer ring's error word is set (a neighbour wait timed out)
+            d = s_.diagnostics()
+            allq = [None] * world
+            dist.all_gather_object(allq, (float(d["charge"]), int(d["particles"])))
+            qt, nt = sum(a[0] for a in allq), sum(a[1] for a in allq)
+            g = s_.gauss_residual(qt / (dx * dy) / (float(nx) * ny))
+            allg_ = [None] * world
+            dist.all_gather_object(allg_, float(g))
+        return qt, nt, allg_
+
     stepper = new_stepper(sim)
+    g_start = None
+    if "beam_ppc" in w:
+        with torch.cuda.stream(st):
+            stepper.refresh_guards()
+        g_start = max(gauss_state(sim, st)[2])
     rebal = None
     if "beam_ppc" in w and not os.environ.get("MPIC_NO_REBALANCE"):
         # configs[4]: time the even split first, then let the cost-driven rebalancer move tile rows (fields + particles)
@@ -468,19 +489,17 @@ def slab_pic_record(args, name, w, rank, world, local, peak, peak_how, e2e=True,
             phases, nsteps = sim.peer_trace(0)
             dist.barrier()
     # ---- self-check (the run must not print a number for a wrong state)
-    with torch.cuda.stream(st):
-        sim.sync()                                      # raises if the peer ring's error word is set (a neighbour wait timed out)
-        d = sim.diagnostics()
-        allq = [None] * world
-        dist.all_gather_object(allq, (float(d["charge"]), int(d["particles"])))
-        q_tot, n_tot = sum(a[0] for a in allq), sum(a[1] for a in allq)
-        mean_rho = q_tot / (dx * dy) / (float(nx) * ny)
-        g = sim.gauss_residual(mean_rho)
-        allg = [None] * world
-        dist.all_gather_object(allg, float(g))
+    q_tot, n_tot, allg = gauss_state(sim, st)
     q0 = -1.0 * dx * dy / ppc * n_expected if "beam_ppc" not in w else q_tot
-    check = {"ok": bool(n_tot == n_expected and abs(q_tot - q0) <= 1e-9 * abs(q0) and max(allg) < 1e-9), "particles": n_tot,
-             "particles_expected": int(n_expected), "charge_error": q_tot - q0, "gauss_residual_max": max(allg), "peer_error_word": 0}
+    # Gauss's law: the two-stream / thermal loads start neutralised with E = 0, so the residual is round-off and stays there
+    # (charge-conserving deposit).  The beam load is NOT a solution of Gauss's law at t = 0 (a dense band on zero fields): the
+    # residual it starts with is preserved node by node, but the slab diagnostic skips each slab's first cell row and the
+    # maximum sits on particle noise, so across a re-partition it is only compared to 2 % (gross corruption would show; the
+    # bit-exact proof through a re-partition is tests/test_gpu_slab.py).
+    g_ok = max(allg) < 1e-9 if g_start is None else abs(max(allg) - g_start) < 0.02 * g_start + 1e-9
+    check = {"ok": bool(n_tot == n_expected and abs(q_tot - q0) <= 1e-9 * abs(q0) and g_ok), "particles": n_tot,
+             "particles_expected": int(n_expected), "charge_error": q_tot - q0, "gauss_residual_max": max(allg),
+             "gauss_residual_at_load": g_start, "peer_error_word": 0}
     if not check["ok"]:
         _fail(rank, f"{name}: {check}")
     migrated = [None] * world

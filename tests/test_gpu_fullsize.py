@@ -194,6 +194,10 @@ def test_c5_beam_plasma_occupancy_and_policy():
     rowc = slab.tile_row_costs(counts, nx // tn, tn * tn)
     even = [rowc[r * 32:(r + 1) * 32].sum() for r in range(8)]
     bal = [rowc[r0:r0 + nr].sum() for r0, nr in slab.balanced_slab_rows(rowc, 8)]
+    # Imbalance of the even split under the cost model: with cost = particles only the two middle slabs carry 8 + 80 * 0.4 = 40 vs
+    # 8 per cell -> max/mean = 40 / 16 = 2.5; the calibrated model adds W_CELL = 8 particle-equivalents per cell to every slab
+    # ((40 + 8) / (16 + 8) = 2.0, measured 1.98 after five steps of beam spreading), hence the bound 1.7 (was 2.5 for the
+    # particles-only model of early round 1)
     assert max(even) / np.mean(even) > 1.7
     assert max(bal) / np.mean(bal) < 1.25
     s.close()
