@@ -753,7 +753,7 @@ int mpic_push_deposit(mpic_sim* s) {
     // single slab, and the peer-ring step on slabs: the histogram is formed by the sort, on its stream
     if (s->st_sort && (s->prm.nranks == 1 || s->defer_count)) CUDA_TRY(cudaEventRecord(s->ev_push, s->st));
     else { TRY(launch_count_moves(s->P, s->G.ywrap, s->mcnt, s->cell_count, s->st)); s->launches++; s->moves_counted = true; }
-    if (s->prm.nranks > 1) {
+    if (s->prm.nranks > 1 && !(s->st_sort && s->defer_count)) {     // (peer-ring step: queued on the side stream by mpic_peer_step_begin)
         TRY(launch_leavers(s->P, s->pa[s->cur], s->cell_start, s->dirs, s->mcnt, s->lv_off, s->cell_count, s->lv, s->st));
         s->launches += 2;
     }

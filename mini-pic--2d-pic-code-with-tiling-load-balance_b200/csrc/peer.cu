@@ -169,11 +169,11 @@ unsigned long long timeout_ns() {
 
 // signal phase `ph` with the next epoch to both neighbours and/or wait for theirs.  Signal and wait may be issued apart
 // (B2: signalled after the sweep, awaited only before the next push, so the tile sort in between absorbs any skew).
-int phase_launch(mpic_sim* s, int ph, bool signal, bool wait, bool counts = false, int par = 0) {
+int phase_launch(mpic_sim* s, int ph, bool signal, bool wait, bool counts = false, int par = 0, cudaStream_t on = nullptr) {
     if (signal) ++s->epoch[ph];
     const unsigned long long e = s->epoch[ph];
     // I am the lower neighbour's UPPER side (word 1) and the upper neighbour's LOWER side (word 0)
-    peer_sync_kernel<<<1, 32, 0, s->st>>>(s->peer[0].ctl + ph * 2 + 1, s->peer[1].ctl + ph * 2 + 0, signal ? e : 0ull, s->ctl + ph * 2,
+    peer_sync_kernel<<<1, 32, 0, on ? on : s->st>>>(s->peer[0].ctl + ph * 2 + 1, s->peer[1].ctl + ph * 2 + 0, signal ? e : 0ull, s->ctl + ph * 2,
                                           wait ? e : 0ull, s->ctl + CTL_ERROR, ph, timeout_ns(), counts ? s->lv.count : nullptr,
                                           s->ctl + CTL_ARRIVE + par * 2, counts ? (volatile long long*)s->h_counts : nullptr);
     LAUNCH_CHECK();
@@ -255,6 +255,7 @@ void mpic_peer_release(mpic_sim* s) {
     s->trace = false;
     if (s->h_counts) { cudaFreeHost(s->h_counts); s->h_counts = nullptr; }
     if (s->ev_counts) { cudaEventDestroy(s->ev_counts); s->ev_counts = nullptr; }
+    if (s->ev_hand) { cudaEventDestroy(s->ev_hand); s->ev_hand = nullptr; }
     if (s->ctl) { cudaFree(s->ctl); s->ctl = nullptr; }
 }
 
@@ -269,6 +270,7 @@ int mpic_peer_export(mpic_sim* s, mpic_peer_info* out) {
         CUDA_TRY(cudaMemset(s->ctl, 0, CTL_WORDS * 8));
         CUDA_TRY(cudaMallocHost(&s->h_counts, 16 * sizeof(long long)));
         CUDA_TRY(cudaEventCreateWithFlags(&s->ev_counts, cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&s->ev_hand, cudaEventDisableTiming));
     }
     memset(out, 0, sizeof *out);
     PeerBlob b;
@@ -378,12 +380,9 @@ static int yee_phases(mpic_sim* s, int with_j, int par = -1) {
     // in a PIC step the first half-B awaits the neighbours' J phase (they pushed, shipped, added their current -- and hence
     // finished reading the guard rows this sweep overwrites); in a field-only step, their last E sweep
     TRY(launch_b_sweep(s->G, s->planes, s->cf, h, sweep_sync(s, par >= 0 ? PH_J : PH_E, PH_B1), s->st));
-    if (par >= 0) {
-        peer_counts_kernel<<<1, 32, 0, s->st>>>(s->lv.count, s->ctl + CTL_ARRIVE + par * 2, s->ctl + CTL_ERROR, (volatile long long*)s->h_counts);
-        LAUNCH_CHECK();
-        CUDA_TRY(cudaEventRecord(s->ev_counts, s->st));    // the one host wait of the step is taken on this event in step_end
-        s->launches++;
-    }
+    // PIC step: the E sweep reads the current -- complete once this rank's own hand-off (side stream) has zeroed / shipped the
+    // guard rows and the neighbours' adds have landed (their J flags: acquired by the edge CTAs of the half-B just queued)
+    if (par >= 0 && s->ev_hand && s->st_sort) CUDA_TRY(cudaStreamWaitEvent(s->st, s->ev_hand, 0));
     tp(s, 6); tp(s, 7);
     TRY(launch_e_sweep(s->G, s->planes, s->jacc, with_j, s->cf, h, sweep_sync(s, PH_B1, PH_E), s->st));
     tp(s, 8); tp(s, 9);
@@ -441,24 +440,39 @@ int mpic_peer_step_begin(mpic_sim* s) {
         s->lv.wait_err = s->ctl + CTL_ERROR; s->lv.wait_timeout_ns = timeout_ns(); s->lv.wait_phase = s->pending_ph;
     }
     tp(s, 1);
-    s->defer_count = s->st_sort != nullptr;              // the destination histogram is formed on the sort stream in step_end
+    // Main stream: push -> half-B -> E -> half-B.  Side stream (the sort stream), behind the push: leaver records -> hand-off
+    // (J guard rows added into the neighbours, leavers shipped, J flag raised) -> wait for the neighbours' J flags and hand the
+    // migration counts to the host -> (mpic_peer_step_end) histogram, absorb, stable sort.  Only the E sweep waits for the
+    // hand-off; everything that concerns particles runs next to the three field sweeps.
+    cudaStream_t side = s->st_sort ? s->st_sort : s->st;
+    s->defer_count = s->st_sort != nullptr;              // push: no histogram / leaver launches on the main stream
     const int rc = mpic_push_deposit(s);
     s->defer_count = false;
     s->lv.wait_want = 0;
     TRY(rc);
     tp(s, 2);
+    if (side != s->st) {
+        CUDA_TRY(cudaStreamWaitEvent(side, s->ev_push, 0));
+        TRY(launch_leavers(s->P, s->pa[s->cur], s->cell_start, s->dirs, s->mcnt, s->lv_off, s->cell_count, s->lv, side));
+        s->launches += 2;
+    }
     const int64_t rec = MPIC_REC_DOUBLES;
     // ONE launch hands over the current guard rows (remote adds) and the leaver records, and its last CTA raises the J flag.
     // My leavers going DOWN arrive at the lower neighbour "from above" (side 1); going UP: at the upper neighbour's side 0.
     const int gx = ceil_div(G.pitch, 256) > 16 ? ceil_div(G.pitch, 256) : 16;
     const unsigned long long ej = ++s->epoch[PH_J];
-    peer_handoff_kernel<<<dim3(gx, 6 * G.g + 2), 256, 0, s->st>>>(G, (unsigned long long*)s->jacc, s->peer[0].jacc, s->peer[0].plane,
+    peer_handoff_kernel<<<dim3(gx, 6 * G.g + 2), 256, 0, side>>>(G, (unsigned long long*)s->jacc, s->peer[0].jacc, s->peer[0].plane,
         s->peer[0].nyl, s->peer[1].jacc, s->peer[1].plane, s->lv,
         s->peer[0].arrive + (int64_t)(par * 2 + 1) * s->peer[0].lcap * rec, s->peer[0].ctl + CTL_ARRIVE + par * 2 + 1, s->peer[0].lcap,
         s->peer[1].arrive + (int64_t)(par * 2 + 0) * s->peer[1].lcap * rec, s->peer[1].ctl + CTL_ARRIVE + par * 2 + 0, s->peer[1].lcap,
         (unsigned int*)(s->ctl + CTL_DONE) + 2, s->peer[0].ctl + PH_J * 2 + 1, s->peer[1].ctl + PH_J * 2 + 0, ej);
     LAUNCH_CHECK();
     s->launches++;
+    if (side != s->st) CUDA_TRY(cudaEventRecord(s->ev_hand, side));
+    // both neighbours' hand-offs (their J flags) -> leaver / arrival counts to the host; the one host wait of the step is taken
+    // on this event in mpic_peer_step_end
+    TRY(phase_launch(s, PH_J, false, true, true, par, side));
+    CUDA_TRY(cudaEventRecord(s->ev_counts, side));
     tp(s, 3); tp(s, 4); tp(s, 5);
     return yee_phases(s, 1, par);
 }

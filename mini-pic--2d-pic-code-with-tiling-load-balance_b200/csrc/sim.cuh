@@ -78,6 +78,7 @@ struct mpic_sim {
     int pending_ph = 3;
     bool b2_pending = false;               // B2 signalled, neighbours' B2 not awaited yet
     cudaEvent_t ev_counts = nullptr;
+    cudaEvent_t ev_hand = nullptr;         // own hand-off finished (recorded on the side stream, awaited by the E sweep)
     // ---- pipelined host-buffer step (api.cu: pic_step_host_pipelined)
     cudaStream_t pipe_up = nullptr, pipe_down = nullptr;
     // single slab: the sort after a push runs on its own stream, next to the field update (neither reads what the other writes)
