@@ -229,15 +229,18 @@ int mpic_alloc_state(mpic_sim* s) {
     CUDA_TRY(cudaMemsetAsync(s->d_scratch, 0, (size_t)(16 + MPIC_DIAG_WORK) * 8, s->st));
     s->cap = p->max_particles;
     if (s->cap > 0) {
-        TRY(alloc_particles(&s->pa[0], s->cap));
-        TRY(alloc_particles(&s->pa[1], s->cap));
+        if (!(s->kept_cap == s->cap && s->pa[0].x)) {        // (a re-partition keeps the capacity-sized arrays when the capacity stays)
+            TRY(alloc_particles(&s->pa[0], s->cap));
+            TRY(alloc_particles(&s->pa[1], s->cap));
+            CUDA_TRY(cudaMalloc(&s->keys, (size_t)s->cap * 4));
+            CUDA_TRY(cudaMalloc(&s->perm, (size_t)s->cap * 4));
+            CUDA_TRY(cudaMalloc(&s->dirs, (size_t)s->cap));
+        }
+        s->kept_cap = 0;
         s->n_entries = P.ncells + 2;
         CUDA_TRY(cudaMalloc(&s->cell_start, (size_t)(s->n_entries + 1) * 4));
         CUDA_TRY(cudaMalloc(&s->cell_count, (size_t)s->n_entries * 4));
         CUDA_TRY(cudaMalloc(&s->scan_tmp, (size_t)(s->n_entries / 2048 + 2) * 4));
-        CUDA_TRY(cudaMalloc(&s->keys, (size_t)s->cap * 4));
-        CUDA_TRY(cudaMalloc(&s->perm, (size_t)s->cap * 4));
-        CUDA_TRY(cudaMalloc(&s->dirs, (size_t)s->cap));
         CUDA_TRY(cudaMalloc(&s->cell_start_alt, (size_t)(s->n_entries + 1) * 4));
         CUDA_TRY(cudaMalloc(&s->mcnt, (size_t)9 * P.ncells * 4));
         CUDA_TRY(cudaMalloc(&s->offtab, (size_t)9 * P.ncells * 4));
@@ -277,9 +280,16 @@ int mpic_alloc_state(mpic_sim* s) {
 }
 // frees layer 2 and resets every flag that describes it (the peer / ring mappings into OTHER handles are released first; the
 // caller guarantees that no other handle still maps THIS one's memory)
-void mpic_free_state(mpic_sim* s) {
+void mpic_free_state(mpic_sim* s, int64_t keep_cap) {
     mpic_ring_release(s);
     mpic_peer_release(s);
+    // capacity-sized arrays (both particle buffers, keys, perm, dirs: nearly all of the memory) survive a re-partition that
+    // keeps the capacity: freeing and re-allocating tens of GB dominated the first measured rebalance (profiles/r02af)
+    const bool keep = keep_cap > 0 && keep_cap == s->cap && s->pa[0].x;
+    Particles kp[2] = { s->pa[0], s->pa[1] };
+    int *kkeys = s->keys, *kperm = s->perm;
+    unsigned char* kdirs = s->dirs;
+    if (keep) { s->pa[0] = s->pa[1] = Particles(); s->keys = s->perm = nullptr; s->dirs = nullptr; }
     cudaFree(s->planes); cudaFree(s->planes_alt); cudaFree(s->jacc); cudaFree(s->rho); cudaFree(s->d_scratch);
     s->planes = s->planes_alt = nullptr; s->jacc = s->rho = nullptr; s->d_scratch = nullptr;
     for (int k = 0; k < 2; k++) { cudaFree(s->pa[k].x); cudaFree(s->pa[k].tag); s->pa[k] = Particles(); }
@@ -302,6 +312,8 @@ void mpic_free_state(mpic_sim* s) {
     s->counts_valid = s->perm_valid = s->moves_counted = false;
     for (int k = 0; k < 8; k++) s->epoch[k] = 0;
     s->step_no = 0; s->b2_pending = false; s->pending_ph = 3;
+    s->kept_cap = 0;
+    if (keep) { s->pa[0] = kp[0]; s->pa[1] = kp[1]; s->keys = kkeys; s->perm = kperm; s->dirs = kdirs; s->kept_cap = keep_cap; }
 }
 extern "C" {
 
@@ -342,7 +354,7 @@ int mpic_destroy(mpic_sim* s) {
     if (s->st) cudaStreamSynchronize(s->st);
     dump_release(s);
     mpic_reslab_finish(s);
-    mpic_free_state(s);
+    mpic_free_state(s, 0);
     if (s->st_sort) { cudaStreamDestroy(s->st_sort); cudaEventDestroy(s->ev_push); cudaEventDestroy(s->ev_sort); }
     if (s->pipe_up) {
         cudaStreamDestroy(s->pipe_up); cudaStreamDestroy(s->pipe_down);

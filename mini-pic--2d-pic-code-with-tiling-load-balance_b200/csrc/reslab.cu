@@ -199,7 +199,7 @@ int mpic_reslab_apply(mpic_sim* s, int new_row0, int new_nrows, int64_t new_max_
     CUDA_TRY(cudaStreamSynchronize(s->st));
     if (s->dump) TRY(mpic_dump_wait(s));
     const int64_t launches = s->launches;
-    mpic_free_state(s);
+    mpic_free_state(s, cap);
     // ---- ... and the new one comes
     s->prm = np_;
     TRY(mpic_set_geometry(s));

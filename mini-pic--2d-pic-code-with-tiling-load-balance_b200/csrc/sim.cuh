@@ -95,6 +95,7 @@ struct mpic_sim {
     void* tile_stage = nullptr; size_t tile_stage_bytes = 0;   // tile patches with guards
     // run-time re-partition (reslab.cu): parcels this handle packed and exported, freed by mpic_reslab_finish
     std::vector<void*> parcels;
+    int64_t kept_cap = 0;          // capacity of the particle arrays kept across mpic_free_state (0: none)
     // asynchronous field dumps (dump.cu): side stream, pinned staging, writer thread
     struct DumpState* dump = nullptr;
     void* ring_events = nullptr;   // ring.cu: per-handle events of the single-process peer-copy ring
@@ -103,7 +104,8 @@ struct mpic_sim {
 void mpic_ring_release(mpic_sim* s);
 int mpic_set_geometry(mpic_sim* s);                  // api.cu: G, P, cf from prm
 int mpic_alloc_state(mpic_sim* s);                   // api.cu: every device array sized by the slab rows / particle capacity
-void mpic_free_state(mpic_sim* s);                   // api.cu: ... and back (releases the peer / ring mappings first)
+void mpic_free_state(mpic_sim* s, int64_t keep_cap); // api.cu: ... and back (releases the peer / ring mappings first); keep_cap > 0:
+                                                     // keep the capacity-sized particle arrays if the capacity is exactly this
 int mpic_scratch(void** buf, size_t* have, size_t need);   // api.cu: grow-only device scratch
 extern "C" int mpic_sort_uploaded(mpic_sim* s);      // api.cu: sort_all(false) -- keys from the stored positions
 int mpic_refresh_x_guards(mpic_sim* s);              // api.cu: periodic x images (and y on a single slab) of the six planes
