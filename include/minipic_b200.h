@@ -203,7 +203,10 @@ int mpic_load_uniform(mpic_sim* s, int ppc, double u_th, double drift_x, double 
 int mpic_push_deposit(mpic_sim* s);
 /* P3: fold the guard ring of the J accumulators into the interior (x always; y when nranks==1). */
 int mpic_fold_current(mpic_sim* s);
-/* S: per-cell count, prefix scan, scatter into (tile gid, cell) order. */
+/* S: per-cell count, prefix scan, STABLE sort into (tile gid, cell) order: inside a cell particles keep their
+ * previous relative order, arrivals from the neighbour slabs follow in (lower, upper) neighbour order, each in the sender's
+ * slot order -- no atomic decides a slot, so the order (what mpic_download_particles returns) is reproducible run to run and
+ * equals a stable sort by cell key.  After a push only a permutation is built (9 B/particle); the next push gathers through it. */
 int mpic_sort_tiles(mpic_sim* s);
 /* nsteps full PIC iterations: push_deposit, J guard fold, A..F field phases with -dt*J, sort. */
 int mpic_pic_steps(mpic_sim* s, int nsteps);

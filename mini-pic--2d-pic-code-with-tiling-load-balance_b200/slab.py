@@ -159,7 +159,7 @@ def balanced_slab_rows(row_costs, nranks):
         raise ValueError(str(e))
 
 
-def rebalance_device(sim, rank, world, dist=None, group=None, w_cell=None, min_gain=0.05):
+def rebalance_device(sim, rank, world, dist=None, group=None, w_cell=None, min_gain=0.05, timings=None):
     """Cost-driven re-partition of the tile rows ON THE DEVICE through the C ABI (csrc/reslab.cu): policy
     mpic_rebalance_plan, mechanism mpic_reslab_pack / _apply / _finish.  Replaces removeTileFromRank / addTileToRank
     (Auxiliar_functions.cpp:242-272) and the hard-coded trigger PIC_2D.cpp:399-412.
@@ -168,10 +168,17 @@ def rebalance_device(sim, rank, world, dist=None, group=None, w_cell=None, min_g
     blobs -- the second one is also the barrier after which no rank maps another's memory); fields and particles move as
     device-to-device copies over NVLink from the old owner's parcel into the new owner's arrays, and the handle changes its
     rows IN PLACE.  Returns ([(row0, nrows)] per rank, changed); the caller re-connects its PeerStepper (new IPC handles)
-    and refreshes the guards."""
+    and refreshes the guards.  `timings` (dict, optional) receives this rank's host seconds per stage."""
     if dist is None:
         import torch.distributed as dist
     m = importlib.import_module(__package__)
+    t = [time.perf_counter()]
+
+    def lap(name):
+        t.append(time.perf_counter())
+        if timings is not None:
+            timings[name] = timings.get(name, 0.0) + t[-1] - t[-2]
+
     allr = [None] * world
     dist.all_gather_object(allr, (int(sim.row0), int(sim.nrows), sim.tile_row_counts().tolist()), group=group)
     old = [(a[0], a[1]) for a in allr]
@@ -180,6 +187,7 @@ def rebalance_device(sim, rank, world, dist=None, group=None, w_cell=None, min_g
     for r0, nr, c in allr:
         rowp[r0:r0 + nr] = c
     changed, new, _ = m.rebalance_plan(rowp, sim.nx * sim.tny, old, W_CELL if w_cell is None else w_cell, min_gain)
+    lap("occupancy_allgather_plan")
     if not changed:
         return old, False
     mine = {}
@@ -187,12 +195,16 @@ def rebalance_device(sim, rank, world, dist=None, group=None, w_cell=None, min_g
         lo, hi = max(old[rank][0], new[d][0]), min(old[rank][0] + old[rank][1], new[d][0] + new[d][1])
         if hi > lo:
             mine[d] = sim.reslab_pack(lo, hi)
+    lap("pack_parcels")
     sim.peer_disconnect()                                    # nobody may map memory that is about to be freed
     posted = [None] * world
     dist.all_gather_object(posted, mine, group=group)
+    lap("disconnect_blob_allgather")
     sim.reslab_apply(new[rank][0], new[rank][1], [posted[src][rank] for src in range(world) if rank in posted[src]], all_rows=new)
+    lap("apply_in_place")
     dist.barrier(group=group)                                # every parcel has been pulled
     sim.reslab_finish()
+    lap("barrier_free_parcels")
     return new, True
 
 
@@ -400,7 +412,9 @@ def slab_pic_record(args, name, w, rank, world, local, peak, peak_how, e2e=True,
     n_expected = bench.expected_particles(w, ny, 0, ny)
     make = lambda r0, nr, n=0: m.Sim(nx, ny, tn, tn, dx, dy, dt, max_particles=int(max(n, 1) * 1.05) + 4096, rank=rank,
                                      nranks=world, device=local, rows=(r0, nr))
-    sim = make(row0, nrows, n_local)
+    # (a run that will be re-partitioned sizes every rank for 1.6 x the mean population: the balanced slabs then fit the particle
+    # arrays a rank already has, and mpic_reslab_apply keeps them instead of freeing and allocating tens of GB)
+    sim = make(row0, nrows, max(n_local, int(1.6 * n_expected / world)) if "beam_ppc" in w else n_local)
     bench.load_workload(sim, w)
     sim.sync()
     st = sim.torch_stream()
@@ -462,14 +476,19 @@ def slab_pic_record(args, name, w, rank, world, local, peak, peak_how, e2e=True,
         ms0, np0, _, per0, _ = timed(stepper, sim, st)
         torch.cuda.synchronize()
         tr0 = time.perf_counter()
-        rows, changed = rebalance_device(sim, rank, world, dist)
+        stages = {}
+        rows, changed = rebalance_device(sim, rank, world, dist, timings=stages)
         if changed:
+            tq = time.perf_counter()
             stepper = new_stepper(sim)           # new IPC handles: the handle itself (and its stream) stayed
+            stages["reconnect_peer_ring"] = time.perf_counter() - tq
         torch.cuda.synchronize()
         dist.barrier()
         tr = [None] * world
-        dist.all_gather_object(tr, time.perf_counter() - tr0)
-        rebal = {"changed": bool(changed), "rebalance_ms": 1e3 * max(tr),
+        dist.all_gather_object(tr, (time.perf_counter() - tr0, stages))
+        stages_max = {k: 1e3 * max(x[1].get(k, 0.0) for x in tr) for k in stages}
+        tr = [x[0] for x in tr]
+        rebal = {"changed": bool(changed), "rebalance_ms": 1e3 * max(tr), "rebalance_stages_ms_max_over_ranks": stages_max,
                  "even_split": {"ms_per_step": ms0 / K, "particles_per_rank": [g[1] for g in per0],
                                 "tile_rows_per_rank": [g[2] for g in per0], "pushes_per_s": float(np0) * K / (ms0 * 1e-3)},
                  "mechanism": "C ABI, on the device: mpic_rebalance_plan -> mpic_reslab_pack -> parcels pulled over NVLink (CUDA IPC) -> mpic_reslab_apply rebuilds the handle in place (csrc/reslab.cu)",

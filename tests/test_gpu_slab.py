@@ -330,13 +330,19 @@ def test_single_process_ring_rebalance_in_place(world, kind):
     nx, ny, tn, dx, dy, dt = g["nx"], g["ny"], g["tnx"], g["dx"], g["dy"], g["dt"]
     ndev = max(1, torch.cuda.device_count())
     cap = parts["x"].shape[0]
-    sims = [m.Sim(nx, ny, tn, g["tny"], dx, dy, dt, max_particles=cap, rank=r, nranks=world, device=r % ndev) for r in range(world)]
-    for s in sims:
+    # capacities: own population + 10 % -- after the re-partition the heavy rank fits (its arrays are kept), the light ones grow
+    cy = np.floor(parts["y"] * (1.0 / dy)).astype(np.int64)
+    gtr = ny // g["tny"]
+    own = []
+    for r in range(world):
+        r0, nr = m.slab_rows(gtr, world, r)
+        own.append((cy >= r0 * g["tny"]) & (cy < (r0 + nr) * g["tny"]))
+    sims = [m.Sim(nx, ny, tn, g["tny"], dx, dy, dt, max_particles=int(1.1 * own[r].sum()) + 64, rank=r, nranks=world, device=r % ndev)
+            for r in range(world)]
+    for r, s in enumerate(sims):
         r0, r1 = s.row0 * g["tny"], (s.row0 + s.nrows) * g["tny"]
         s.upload_planes([a[r0:r1] for a in planes])
-        cy = np.floor(parts["y"] * (1.0 / dy)).astype(np.int64)
-        sel = (cy >= r0) & (cy < r1)
-        s.upload_particles({k: np.ascontiguousarray(v[sel]) for k, v in parts.items()})
+        s.upload_particles({k: np.ascontiguousarray(v[own[r]]) for k, v in parts.items()})
     ring = m.SlabRing(sims) if kind == "copy" else m.PeerRing(sims)
     ring.refresh_guards()
     steps = 4
