@@ -3,7 +3,7 @@
 set -x
 mkdir -p gpurun_out
 T=${TAG:-r02z}
-V=build/variants/libminipic_base.so
+V=build/variants/libminipic_none.so
 if [ -f $V ]; then for k in 1 2; do for r in sat quiet thermal c4; do
   timeout 300 python tools/push_ab.py $r | sed 's/^{/{"build": "this", /' >> gpurun_out/${T}_push_ab.jsonl
   MPIC_LIB=$V timeout 300 python tools/push_ab.py $r | sed 's/^{/{"build": "previous commit", /' >> gpurun_out/${T}_push_ab.jsonl
