@@ -392,7 +392,7 @@ def time_pic(sim, torch, K, W):
 
 def push_roofline(n, t, peak, peak_how):
     gbs = n * PUSH_BYTES_SURVEY / (t["push_ms"] * 1e-3) / 1e9
-    return {"bound": "hbm", "kernel": "push_packed_kernel (dense slabs; push_deposit_kernel for sparse ones) + the 9 us count_moves launch timed with it", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
+    return {"bound": "hbm", "kernel": "push_packed_kernel (dense slabs; push_deposit_kernel, the lane-group cell walk, for sparse ones)", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
             "bytes_per_particle": PUSH_BYTES_SURVEY,
             "frac_104B": gbs / peak * PUSH_BYTES_FUSED_REORDER / PUSH_BYTES_SURVEY,
             "traffic": NCU_TRAFFIC_BYTES_PER_PARTICLE * n,

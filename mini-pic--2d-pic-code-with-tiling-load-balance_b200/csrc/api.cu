@@ -309,7 +309,7 @@ void mpic_free_state(mpic_sim* s, int64_t keep_cap) {
     s->tile_tmp = nullptr; s->tile_stage = nullptr; s->tile_tmp_bytes = s->tile_stage_bytes = 0;
     s->has_tmap = s->fused_ready = false;
     s->cur = 0; s->n = 0; s->cap = 0; s->n_entries = 0; s->arrived = 0; s->left = -1;
-    s->counts_valid = s->perm_valid = s->moves_counted = false;
+    s->counts_valid = s->perm_valid = s->moves_counted = s->sort_pending = false;
     for (int k = 0; k < 8; k++) s->epoch[k] = 0;
     s->step_no = 0; s->b2_pending = false; s->pending_ph = 3;
     s->kept_cap = 0;
@@ -630,8 +630,17 @@ int mpic_migration_absorb(mpic_sim* s, int n_from_lo, int n_from_hi) {
 }
 
 // ------------------------------------------------------------------------------------------ particles
+static int sort_all(mpic_sim* s, bool counted, cudaStream_t force = nullptr);
+// The pipelined host-buffer step leaves the resident particles chunk by chunk and defers the tile sort to the first call that
+// needs sorted resident state (a loop of host-buffer steps overwrites that state every call and never pays for the sort).
+static int ensure_sorted(mpic_sim* s) {
+    if (!s->sort_pending) return 0;
+    s->sort_pending = false;
+    return sort_all(s, false, nullptr);
+}
 // physical reorder on demand: after this pa[cur][0..n) is itself in sorted order
 static int materialise(mpic_sim* s) {
+    TRY(ensure_sorted(s));
     if (!s->perm_valid) return 0;
     TRY(launch_gather(s->pa[s->cur], s->pa[s->cur ^ 1], s->perm, s->n, nullptr, s->st));
     s->launches++;
@@ -645,7 +654,8 @@ static int materialise(mpic_sim* s) {
 //   scan -> offsets -> perm_stable (+ arrivals appended); no particle data moves, the next push gathers through perm.
 // otherwise (uploads, loads, appends: arbitrary storage order): keys from the stored positions, histogram, scan, provisional
 //   permutation, per-cell ascending sort of the permutation (== stable order), physical gather.
-static int sort_all(mpic_sim* s, bool counted, cudaStream_t force = nullptr) {
+static int sort_all(mpic_sim* s, bool counted, cudaStream_t force) {
+    TRY(ensure_sorted(s));
     counted = counted && s->counts_valid;
     s->counts_valid = false;
     const int64_t total = s->n + s->arrived;
@@ -700,7 +710,7 @@ int mpic_upload_particles(mpic_sim* s, int64_t n, const double* x, const double*
     REQUIRE(s && n >= 0, MPIC_EINVAL, "bad argument");
     REQUIRE(n == 0 || (x && y && ux && uy && uz && q && tag), MPIC_EINVAL, "mpic_upload_particles: null particle array");
     REQUIRE(n <= s->cap, MPIC_ENOMEM, "particle capacity %lld exceeded (%lld)", (long long)s->cap, (long long)n);
-    s->perm_valid = false; s->counts_valid = false; s->arrived = 0;
+    s->perm_valid = false; s->counts_valid = false; s->arrived = 0; s->sort_pending = false;
     Particles& p = s->pa[s->cur];
     const double* src[6] = { x, y, ux, uy, uz, q };
     double* dst[6] = { p.x, p.y, p.ux, p.uy, p.uz, p.q };
@@ -733,7 +743,7 @@ int mpic_load_uniform(mpic_sim* s, int ppc, double u_th, double d0, double d1, d
     int lo = (int)nearbyint(band_lo * P.ny), hi = (int)nearbyint(band_hi * P.ny);
     REQUIRE(lo >= 0 && hi <= P.ny && lo <= hi, MPIC_EINVAL, "bad band");
     const int64_t tag0 = append ? s->tag_base : 0;
-    if (!append) { s->n = 0; s->tag_base = 0; s->perm_valid = false; }
+    if (!append) { s->n = 0; s->tag_base = 0; s->perm_valid = false; s->sort_pending = false; }
     TRY(materialise(s));
     s->counts_valid = false;
     const int slo = lo > P.cy0 ? lo : P.cy0, shi = hi < P.cy0 + P.nyl ? hi : P.cy0 + P.nyl;
@@ -751,6 +761,7 @@ int mpic_load_uniform(mpic_sim* s, int ppc, double u_th, double d0, double d1, d
 int mpic_push_deposit(mpic_sim* s) {
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && s->cap > 0, MPIC_ESTATE, "no particle storage");
+    TRY(ensure_sorted(s));
     REQUIRE(s->arrived == 0, MPIC_ESTATE, "arrivals absorbed but not sorted in: call mpic_sort_tiles before the next push");
     REQUIRE(!s->counts_valid, MPIC_ESTATE, "particles moved but not re-sorted: call mpic_sort_tiles between pushes");
     s->left = s->prm.nranks > 1 ? -1 : 0;
@@ -774,7 +785,8 @@ int mpic_push_deposit(mpic_sim* s) {
 }
 int mpic_sort_after_push(mpic_sim* s) { return sort_all(s, true); }
 int mpic_sort_after_push_on(mpic_sim* s, void* stream) { return sort_all(s, true, (cudaStream_t)stream); }
-int mpic_sort_uploaded(mpic_sim* s) { s->perm_valid = false; s->counts_valid = false; s->arrived = 0; return sort_all(s, false); }
+int mpic_sort_uploaded(mpic_sim* s) { s->perm_valid = false; s->counts_valid = false; s->arrived = 0; s->sort_pending = false; return sort_all(s, false); }
+int mpic_ensure_sorted(mpic_sim* s) { return ensure_sorted(s); }
 int mpic_sort_tiles(mpic_sim* s) {
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && s->cap > 0, MPIC_ESTATE, "no particle storage");
@@ -840,7 +852,7 @@ static int pic_step_host_pipelined(mpic_sim* s, double* const planes[6], int64_t
     int nchunk = (int)((n + chunk - 1) / chunk);
     if (nchunk < 2) nchunk = 2;
     if (nchunk > MPIC_PIPE_MAX) nchunk = MPIC_PIPE_MAX;
-    s->perm_valid = false; s->counts_valid = false; s->arrived = 0;
+    s->perm_valid = false; s->counts_valid = false; s->arrived = 0; s->sort_pending = false;   // the resident particles are replaced
     Particles& A = s->pa[s->cur];
     Particles& B = s->pa[s->cur ^ 1];
     // everything enqueued earlier on the main stream (it may still read A/B) precedes the first upload
@@ -890,8 +902,8 @@ static int pic_step_host_pipelined(mpic_sim* s, double* const planes[6], int64_t
     for (int p = 0; p < 6; p++)
         CUDA_TRY(cudaMemcpy2DAsync(planes[p], (size_t)G.nx * 8, s->planes + p * G.plane + (int64_t)G.g * G.pitch + MPIC_X0,
                                    (size_t)G.pitch * 8, (size_t)G.nx * 8, G.nyl, cudaMemcpyDeviceToHost, s->st));
-    TRY(sort_all(s, false));           // resident state stays usable: one stable sort by position over all chunks (B -> A; the
-                                       // downloads above only read B)
+    s->sort_pending = true;            // resident state stays usable: one stable sort by position over all chunks, run by the first
+                                       // call that needs it (ensure_sorted) -- a loop of host-buffer steps never does
     CUDA_TRY(cudaStreamSynchronize(s->pipe_down));
     CUDA_TRY(cudaStreamSynchronize(s->st));
     if (n_out) *n_out = n;
@@ -938,6 +950,7 @@ int mpic_cell_crossers(mpic_sim* s, int64_t* n_out) {
 int mpic_get_tile_counts(mpic_sim* s, int* counts) {
     if (s) cudaSetDevice(s->prm.device);
     REQUIRE(s && counts && s->cap > 0, MPIC_EINVAL, "bad argument");
+    TRY(ensure_sorted(s));
     const int nt = s->P.ltr * s->P.gtc;
     TRY(mpic_scratch(&s->tile_tmp, &s->tile_tmp_bytes, (size_t)nt * 4));
     int* d = (int*)s->tile_tmp;

@@ -120,6 +120,7 @@ int mpic_reslab_pack(mpic_sim* s, int row_lo, int row_hi, mpic_parcel_info* out)
     REQUIRE(s && out, MPIC_EINVAL, "bad argument");
     REQUIRE(row_lo >= s->prm.row0 && row_hi <= s->prm.row0 + s->prm.nrows && row_lo < row_hi, MPIC_EINVAL,
             "rows [%d,%d) are not on this slab [%d,%d)", row_lo, row_hi, s->prm.row0, s->prm.row0 + s->prm.nrows);
+    TRY(mpic_ensure_sorted(s));
     REQUIRE(s->arrived == 0 && !s->counts_valid, MPIC_ESTATE, "re-partition between steps only (after the tile sort)");
     const FieldGeom& G = s->G;
     const PicConst& P = s->P;

@@ -84,6 +84,7 @@ struct mpic_sim {
     // single slab: the sort after a push runs on its own stream, next to the field update (neither reads what the other writes)
     cudaStream_t st_sort = nullptr;
     cudaEvent_t ev_push = nullptr, ev_sort = nullptr;
+    bool sort_pending = false;     // pa[cur][0..n) is in arbitrary order (left by the pipelined host-buffer step): sort before use
     bool defer_count = false;      // slabs, peer-ring step: count_moves is left to the sort stream (mpic_peer_step_end)
     bool moves_counted = false;    // cell_count already holds the destination histogram of the last push (count_moves ran)
     cudaEvent_t pipe_ev_up[MPIC_PIPE_MAX] = {}, pipe_ev_done[MPIC_PIPE_MAX] = {}, pipe_ev_free = nullptr;
@@ -107,6 +108,7 @@ int mpic_alloc_state(mpic_sim* s);                   // api.cu: every device arr
 void mpic_free_state(mpic_sim* s, int64_t keep_cap); // api.cu: ... and back (releases the peer / ring mappings first); keep_cap > 0:
                                                      // keep the capacity-sized particle arrays if the capacity is exactly this
 int mpic_scratch(void** buf, size_t* have, size_t need);   // api.cu: grow-only device scratch
+extern "C" int mpic_ensure_sorted(mpic_sim* s);     // api.cu: run the deferred sort of the pipelined host-buffer step, if any
 extern "C" int mpic_sort_uploaded(mpic_sim* s);      // api.cu: sort_all(false) -- keys from the stored positions
 int mpic_refresh_x_guards(mpic_sim* s);              // api.cu: periodic x images (and y on a single slab) of the six planes
 int mpic_fused_setup(mpic_sim* s);                   // api.cu: second plane block + tensor maps (idempotent)

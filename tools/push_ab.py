@@ -11,7 +11,7 @@ regime = sys.argv[1]
 K = int(sys.argv[2]) if len(sys.argv) > 2 else 20
 nx = int(sys.argv[3]) if len(sys.argv) > 3 else (4096 if regime == "c4" else 512)
 ny = int(sys.argv[4]) if len(sys.argv) > 4 else 512
-ppc, dx = 64, 0.1
+ppc, dx = int(os.environ.get("PPC", "64")), 0.1
 sim = m.Sim(nx, ny, 16, 16, dx, dx, m.courant_dt(dx, dx), max_particles=nx * ny * ppc + 1024)
 if regime in ("quiet", "sat"):
     sim.load_uniform(ppc, u_th=0.001, two_stream=0.2, seed=12345)
@@ -28,6 +28,6 @@ for e in evs:
 sim.sync()
 f = lambda a, b: float(np.mean([e[a].elapsed_time(e[b]) for e in evs]))
 n = sim.num_particles
-print(json.dumps({"regime": regime, "gl": os.environ.get("MPIC_PUSH_GL", "auto"), "n": n, "push_ms": round(f(0, 1), 4), "yee_ms": round(f(1, 2), 4),
+print(json.dumps({"regime": regime, "ppc": ppc, "gl": os.environ.get("MPIC_PUSH_GL", "auto"), "n": n, "push_ms": round(f(0, 1), 4), "yee_ms": round(f(1, 2), 4),
                   "sort_ms": round(f(2, 3), 4), "step_ms": round(f(0, 3), 4), "push_frac104": round(n * 104 / (f(0, 1) * 1e-3) / 6446e9, 4),
                   "push_frac90": round(n * 90 / (f(0, 1) * 1e-3) / 6446e9, 4)}))
