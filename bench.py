@@ -56,9 +56,9 @@ WORKLOADS = {
 PUSH_BYTES_SURVEY = 90.0
 PUSH_BYTES_FUSED_REORDER = 104.0
 # constant, NOT measured by the run that prints it: dram__bytes_read+write of one push launch in the saturated regime,
-# ncu --set full, profiles/r02ah_ncu_full_push_packed_saturated_raw.csv: 1.093 GB + 0.871 GB over 16 777 216 particles
+# ncu --set full, profiles/r02an_ncu_full_push_packed_saturated_raw.csv: 1.094 GB + 0.872 GB over 16 777 216 particles
 NCU_TRAFFIC_BYTES_PER_PARTICLE = 117.2
-# ncu --set full, profiles/r02ah_ncu_full_fused_yee_8192_raw.csv: 3.238 GB + 3.179 GB over 8192^2 cells (algorithmic: 96 B/cell)
+# ncu --set full, profiles/r02an_ncu_full_fused_yee_8192_raw.csv: 3.238 GB + 3.179 GB over 8192^2 cells (algorithmic: 96 B/cell)
 NCU_YEE_TRAFFIC_BYTES_PER_CELL = 95.6
 SORT_BYTES_PER_PARTICLE = 5.0      # what is left of the sort: direction codes read (1) + permutation written (4); the rest is per cell
 YEE_BYTES_3SWEEP = 216.0           # reference-faithful half-B, E, half-B: 3 x 72 B per cell
@@ -336,7 +336,7 @@ def yee_bench(m, torch, steps, warmup, n=8192):
            "gpu_launches": launches,
            "roofline": {"bound": "hbm", "kernel": "fused_yee_kernel", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
                         "traffic": NCU_YEE_TRAFFIC_BYTES_PER_CELL * float(n) * n,
-                        "traffic_source": "CONSTANT from one ncu --set full capture of this kernel at 8192^2 (profiles/r02ah_ncu_full_fused_yee_8192_raw.csv: "
+                        "traffic_source": "CONSTANT from one ncu --set full capture of this kernel at 8192^2 (profiles/r02an_ncu_full_fused_yee_8192_raw.csv: "
                                           "95.6 B/cell), per launch; not measured by this run",
                         "bytes_per_cell_update": YEE_BYTES_FUSED,
                         "frac_of_144B_figure": cells * YEE_BYTES_ALGO / (ms * 1e-3) / 1e9 / peak, "peak_source": how,
@@ -396,7 +396,7 @@ def push_roofline(n, t, peak, peak_how):
             "bytes_per_particle": PUSH_BYTES_SURVEY,
             "frac_104B": gbs / peak * PUSH_BYTES_FUSED_REORDER / PUSH_BYTES_SURVEY,
             "traffic": NCU_TRAFFIC_BYTES_PER_PARTICLE * n,
-            "traffic_source": "CONSTANT from one ncu --set full capture of this kernel in the saturated regime (profiles/r02ah_ncu_full_push_packed_saturated_raw.csv: "
+            "traffic_source": "CONSTANT from one ncu --set full capture of this kernel in the saturated regime (profiles/r02an_ncu_full_push_packed_saturated_raw.csv: "
                               "117.2 B/particle), scaled by the particle count; not measured by this run",
             "pushes_per_s_kernel_only": n / (t["push_ms"] * 1e-3), "peak_source": peak_how,
             "sort_gbs": n * SORT_BYTES_PER_PARTICLE / (t["sort_ms"] * 1e-3) / 1e9,
