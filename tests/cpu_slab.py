@@ -61,6 +61,40 @@ class CpuSlabSim:
     def upload_particles(self, parts):
         self.set_particles(parts)
 
+    # ---- the re-partition interface slab.rebalance_device() drives (product: csrc/reslab.cu).  Here a parcel is a pickled blob
+    # of the packed rows instead of a CUDA-IPC handle; the protocol -- who packs which rows for whom, which blobs a rank applies,
+    # rows changing in place -- is the product's.
+    def tile_row_counts(self):
+        return self.tile_counts().reshape(self.nrows, self.gtc).sum(axis=1).astype(np.int64)
+
+    def reslab_pack(self, row_lo, row_hi):
+        import pickle
+        assert self.row0 <= row_lo < row_hi <= self.row0 + self.nrows
+        cy = np.floor(self.parts["y"] * (1.0 / self.dy)).astype(np.int64) // self.tny
+        sel = (cy >= row_lo) & (cy < row_hi)
+        rows = np.arange(row_lo * self.tny, row_hi * self.tny)
+        return pickle.dumps({"rows": (row_lo, row_hi), "f": [a[rows].copy() for a in self.planes],
+                             "p": {k: v[sel].copy() for k, v in self.parts.items()}})
+
+    def peer_disconnect(self):
+        pass
+
+    def reslab_apply(self, row0, nrows, parcels, all_rows=None, max_particles=0):
+        import pickle
+        ps = sorted((pickle.loads(b) for b in parcels), key=lambda d: d["rows"][0])
+        assert ps[0]["rows"][0] == row0 and ps[-1]["rows"][1] == row0 + nrows
+        assert all(a["rows"][1] == b["rows"][0] for a, b in zip(ps, ps[1:])), "parcels must tile the new rows"
+        self.__init__(self.nx, self.ny, self.tnx, self.tny, self.dx, self.dy, self.dt, 0, 0, row0, nrows)   # in place: same object
+        for d in ps:
+            rows = np.arange(d["rows"][0] * self.tny, d["rows"][1] * self.tny)
+            for a, b in zip(self.planes, d["f"]):
+                a[rows] = b
+        self.parts = {k: np.concatenate([d["p"][k] for d in ps]) for k in ps[0]["p"]}
+        self.all_rows = all_rows
+
+    def reslab_finish(self):
+        pass
+
     # ---- state in / out
     def set_interior(self, global_planes):
         for a, b in zip(self.planes, global_planes):

@@ -128,6 +128,75 @@ def _rebalance_worker(rank, world, port, steps, outdir):
         dist.destroy_process_group()
 
 
+def _rebalance_device_worker(rank, world, port, steps, outdir):
+    for p in (ROOT, os.path.join(ROOT, "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import torch.distributed as dist
+    from cpu_slab import CpuSlabSim
+    slab = importlib.import_module(PKG + ".slab")
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        g, parts, planes = _beam_problem()
+        gtr = g["ny"] // g["tny"]
+        base, rem = divmod(gtr, world)
+        sim = CpuSlabSim(g["nx"], g["ny"], g["tnx"], g["tny"], g["dx"], g["dy"], g["dt"], rank, world,
+                         rank * base + min(rank, rem), base + (rank < rem))
+        sim.set_interior(planes)
+        sim.set_particles(parts)
+        st = slab.SlabStepper(sim, slab.Ring(rank, world))
+        st.refresh_guards()
+        for _ in range(steps):
+            st.step()
+        before = int(sim.parts["x"].shape[0])
+        ident = id(sim)
+        timings = {}
+        rows, changed = slab.rebalance_device(sim, rank, world, dist, w_cell=0.25, timings=timings)
+        assert id(sim) == ident and (sim.row0, sim.nrows) == tuple(rows[rank])          # same handle, new rows
+        rows2, again = slab.rebalance_device(sim, rank, world, dist, w_cell=0.25)        # the plan is a fixed point
+        assert not again and rows2 == rows
+        st = slab.SlabStepper(sim, slab.Ring(rank, world))
+        st.refresh_guards()
+        for _ in range(steps):
+            st.step()
+        np.savez(os.path.join(outdir, f"rank{rank}.npz"), rows=sim.rows_int, changed=changed, before=before,
+                 after=int(sim.parts["x"].shape[0]), new_rows=np.array(rows), stages=np.array(sorted(timings)),
+                 **{f"f{k}": sim.planes[k][sim.rows_int] for k in range(6)}, **sim.parts)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_device_rebalance_protocol_over_gloo(world):
+    """The PRODUCT's collective re-partition (slab.rebalance_device: occupancy all-gather -> mpic_rebalance_plan in the C
+    library -> one parcel per new owner -> blob all-gather -> apply in place -> barrier -> finish) on world_size 2 and 3 over
+    gloo, with the CPU stand-in playing the device: bit-exact versus the single-rank oracle through the re-partition, the
+    most loaded rank gets lighter, every rank keeps its handle."""
+    from oracle import bindings as ob
+    steps = 3
+    with tempfile.TemporaryDirectory() as d:
+        mp.spawn(_rebalance_device_worker, args=(world, _free_port(), steps, d), nprocs=world, join=True)
+        outs = [np.load(os.path.join(d, f"rank{r}.npz")) for r in range(world)]
+        g, parts, planes = _beam_problem()
+        lib = ob.load_oracle()
+        P = ob.make_params(lib, g["nx"], g["ny"], g["tnx"], g["tny"], g["dx"], g["dy"], g["dt"])
+        want, wf = copy_parts(parts), [a.copy() for a in planes]
+        ob.pic_steps(lib, P, wf, want, 2 * steps)
+        got = by_tag({k: np.concatenate([o[k] for o in outs]) for k in ("x", "y", "ux", "uy", "uz", "q", "tag")})
+        want = by_tag(want)
+        assert np.array_equal(got["tag"], want["tag"])
+        for k in ("x", "y", "ux", "uy", "uz", "q"):
+            assert np.array_equal(got[k], want[k]), k
+        for o in outs:
+            for k in range(6):
+                assert np.array_equal(o[f"f{k}"], wf[k][o["rows"]]), k
+        assert all(bool(o["changed"]) for o in outs)
+        assert max(int(o["after"]) for o in outs) < 0.8 * max(int(o["before"]) for o in outs)
+        assert list(outs[0]["stages"]) == ["apply_in_place", "barrier_free_parcels", "disconnect_blob_allgather",
+                                           "occupancy_allgather_plan", "pack_parcels"]
+
+
 @pytest.mark.parametrize("world", [2, 3])
 def test_runtime_rebalance_is_bit_exact_and_evens_the_load(world):
     """slab.rebalance (cost-driven re-partition of tile rows with their fields AND particles) in the
