@@ -22,7 +22,7 @@ namespace {
 constexpr unsigned long long PARCEL_MAGIC = 0x4d5049435041524bull;   // "MPICPARK"
 struct ParcelBlob {                   // what travels inside mpic_parcel_info
     unsigned long long magic;
-    int pid, device, row_lo, row_hi, nx, tny, pad0, pad1;
+    int pid, device, row_lo, row_hi, nx, tny, has_ipc, pad1;   // has_ipc: h is valid (a process that cannot export still serves handles of its own process)
     int64_t np;                       // particles in the parcel
     int64_t bytes;
     void* raw;                        // valid inside the packing process
@@ -160,7 +160,8 @@ int mpic_reslab_pack(mpic_sim* s, int row_lo, int row_hi, mpic_parcel_info* out)
     }
     CUDA_TRY(cudaStreamSynchronize(s->st));              // the parcel is complete before its handle leaves this call
     b.raw = buf;
-    CUDA_TRY(cudaIpcGetMemHandle(&b.h, buf));
+    if (cudaIpcGetMemHandle(&b.h, buf) == cudaSuccess) b.has_ipc = 1;
+    else cudaGetLastError();                              // single-process rings only need the raw pointer
     memset(out, 0, sizeof *out);
     memcpy(out->bytes, &b, sizeof b);
     return 0;
@@ -213,6 +214,7 @@ int mpic_reslab_apply(mpic_sim* s, int new_row0, int new_nrows, int64_t new_max_
     for (const ParcelBlob& b : bl) {
         const void* src = b.raw;
         if (b.pid != (int)getpid()) {
+            if (!b.has_ipc) { mpic_set_error("parcel rows %d..%d come from another process that could not export a CUDA IPC handle", b.row_lo, b.row_hi); rc = MPIC_ECUDA; break; }
             void* ptr = nullptr;
             cudaError_t e = cudaIpcOpenMemHandle(&ptr, b.h, cudaIpcMemLazyEnablePeerAccess);
             if (e != cudaSuccess) { mpic_set_error("cudaIpcOpenMemHandle(parcel rows %d..%d): %s", b.row_lo, b.row_hi, cudaGetErrorString(e)); rc = MPIC_ECUDA; break; }
