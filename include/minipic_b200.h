@@ -229,6 +229,32 @@ int mpic_diagnostics(mpic_sim* s, double out[5]);
  * (a slab's first cell row is skipped: its node charge needs the lower neighbour's particles). */
 int mpic_gauss_residual(mpic_sim* s, double mean_rho, double* out);
 
+/* ---- for callers that must not allocate device memory.  (No counterpart in the reference: it has no particles, no
+ * diagnostics and no GPU.)
+ * mpic_kinetic_energy_static computes what mpic_diagnostics reports as out[1] and out[3] -- out[0] = sum |q_p / qm| (gamma_p - 1),
+ * the kinetic energy, and out[1] = sum q_p, the total charge, with the same reproducible ordered block sum and therefore the same
+ * digits for the same particle order -- but WITHOUT a handle and without a single cudaMalloc / cudaFree, in this call or any
+ * earlier one.  It is for the two kinds of caller that cannot afford mpic_create + mpic_diagnostics: a code whose particle
+ * arrays live in its own device arena (own pool, torch's caching allocator, all of HBM reserved at start-up for a 1e9-particle
+ * slab) with nothing left for the planes and sort tables a handle allocates; and a diagnostics hook between the steps of a
+ * running peer ring, where cudaMalloc's device-wide synchronisation would stall every rank spinning on this rank's flags.
+ *   ux, uy, uz, q   DEVICE pointers (memory of the device that is current in the calling thread), n doubles each;
+ *   out             HOST array of two doubles;  qm: charge/mass ratio of the species (non-zero; electrons -1);
+ *   stream          cudaStream_t to run on (NULL = the default stream); the call returns after that stream has drained.
+ * The reduction's work area (block partials, ticket, result slots) is a static device array inside the library image,
+ * MPIC_KINETIC_STATIC_SCRATCH_BYTES long, resident on every GPU that loads the library until the process exits.  It does not
+ * grow with n; the one size limit is n <= MPIC_KINETIC_STATIC_MAX_PARTICLES (the library's 32-bit particle-slot range), beyond
+ * which the call returns MPIC_EINVAL and says so -- reduce a larger population in pieces and add the results.
+ * The first call on each device looks up the array's device address (cudaGetSymbolAddress; this may load the library's device
+ * code): make that first call at set-up time, before any stream capture is begun on that device.
+ * ALL calls on a device share the one work area, and it keeps the previous call's contents (the call clears the slots that must
+ * start at zero itself).  Two calls that overlap on the GPU -- two host threads, or two streams -- race on it and both results
+ * are garbage: serialise them. */
+#define MPIC_KINETIC_STATIC_SCRATCH_BYTES 9728
+#define MPIC_KINETIC_STATIC_MAX_PARTICLES 2147483584LL   /* 2^31 - 64 */
+int mpic_kinetic_energy_static(const double* ux, const double* uy, const double* uz, const double* q, int64_t n, double qm,
+                               double out[2], void* stream);
+
 /* ---- tile ownership (owner[] map, PIC_2D.cpp:55,144-148; removeTileFromRank/addTileToRank, Auxiliar_functions.cpp:242-272).
  * On one GPU ownership is bookkeeping only (fields never change); it drives currentRank in the dumps. */
 int mpic_get_owner(mpic_sim* s, int* owner /* global tiles */);

@@ -121,6 +121,7 @@ def lib():
     L.mpic_ring_rebalance.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_double, C.c_double, c_ip, c_ip]
     L.mpic_dump_fields_async.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
     L.mpic_dump_wait.argtypes = [C.c_void_p]
+    L.mpic_kinetic_energy_static.argtypes = [C.c_void_p] * 4 + [C.c_int64, C.c_double, c_dp, C.c_void_p]
     _lib = L
     return L
 
@@ -163,6 +164,22 @@ def rebalance_plan(row_particles, cells_per_tile_row, old_rows, w_cell, min_gain
     rc = _chk(lib().mpic_rebalance_plan(int(rp.shape[0]), old.shape[0] // 2, rp.ctypes.data_as(c_lp), int(cells_per_tile_row),
                                         float(w_cell), float(min_gain), _ip(old), _ip(new), _dp(cost)))
     return bool(rc), [(int(new[2 * k]), int(new[2 * k + 1])) for k in range(old.shape[0] // 2)], (float(cost[0]), float(cost[1]))
+
+
+KINETIC_STATIC_SCRATCH_BYTES = 9728          # MPIC_KINETIC_STATIC_SCRATCH_BYTES
+KINETIC_STATIC_MAX_PARTICLES = 2**31 - 64    # MPIC_KINETIC_STATIC_MAX_PARTICLES
+
+
+def kinetic_energy_static(ux_ptr, uy_ptr, uz_ptr, q_ptr, n, qm=-1.0, stream=None):
+    """mpic_kinetic_energy_static: (kinetic energy, total charge) of n particles whose ux, uy, uz, q arrays sit in device
+    memory the CALLER owns (raw device addresses, e.g. tensor.data_ptr()).  For callers that cannot allocate on the GPU --
+    all of it is in their own pool, or a cudaMalloc between ring steps would stall the neighbours: the library allocates
+    nothing, the reduction's work area is a 9.5 KB static device array shared by every call on the device, so do not overlap
+    two calls.  Blocks until `stream` (a cudaStream_t address; None = default stream) has drained."""
+    out = np.zeros(2)
+    _chk(lib().mpic_kinetic_energy_static(C.c_void_p(ux_ptr), C.c_void_p(uy_ptr), C.c_void_p(uz_ptr), C.c_void_p(q_ptr),
+                                          int(n), float(qm), _dp(out), C.c_void_p(stream)))
+    return float(out[0]), float(out[1])
 
 
 def courant_dt(dx, dy, factor=0.5):
