@@ -312,6 +312,45 @@ def test_sort_is_stable_and_reproducible(cfg):
         assert np.array_equal(outs[0][k], want[k]), k
 
 
+def test_cell_of_70000_particles_keeps_exact_move_counts():
+    """the packed push counts movers per (cell, direction) in 16-bit fields.  One cell with 70 000 particles
+    that all cross its +x face in the first step (into the next TILE) overflows such a field; the kernel re-counts cells of
+    65 536 or more from the direction codes, so slot order, phase space and tile occupancy still equal the oracle's bit for bit."""
+    nx = ny = 32
+    s, P, parts, pl = _setup(nx, ny, 16, 16, 2, 0.1, seed=21, fields=0.01)
+    dx = dy = 0.1
+    rng = np.random.default_rng(22)
+    nf = 70000
+    fat = {"x": (15 + 0.70 + 0.29 * rng.random(nf)) * dx, "y": (7 + 0.2 + 0.6 * rng.random(nf)) * dy,
+           "ux": 3.0 + 0.1 * rng.standard_normal(nf), "uy": 0.2 * rng.standard_normal(nf), "uz": 0.1 * rng.standard_normal(nf),
+           "q": np.full(nf, -1e-7), "tag": (np.arange(nf) + 10_000_000).astype(np.int32)}
+    allp = {k: np.ascontiguousarray(np.concatenate([parts[k], fat[k]])) for k in parts}
+    n = allp["x"].shape[0]
+    assert n >= 6 * nx * ny                                                # dense enough for the packed walk
+    s.close()
+    s = pkg().Sim(nx, ny, 16, 16, dx, dy, pkg().courant_dt(dx, dy), max_particles=n + 64)
+    s.upload_planes(pl)
+    s.upload_particles(allp)
+    k0 = ob.cell_keys(lib, P, allp["x"], allp["y"])
+    o0 = np.argsort(k0, kind="stable")
+    assert np.bincount(k0).max() >= 70000
+    s.pic_steps(1)
+    moved = s.download_particles()
+    assert (np.floor(moved["x"][moved["tag"] >= 10_000_000] / dx) == 16).sum() > 65536      # they did cross, into the next tile
+    s.pic_steps(3)
+    s.sync()
+    got = s.download_particles()
+    want = {k: np.ascontiguousarray(v[o0]) for k, v in allp.items()}
+    wf = [a.copy() for a in pl]
+    counts, _ = ob.pic_steps(lib, P, wf, want, 4, do_sort=2)
+    for k in ("tag", "x", "y", "ux", "uy", "uz", "q"):
+        assert np.array_equal(got[k], want[k]), k
+    assert np.array_equal(s.tile_counts(), counts)
+    gf = s.download_planes()
+    for k in range(6):
+        assert np.array_equal(gf[k], wf[k]), k
+
+
 @pytest.mark.parametrize("cfg", [(32, 32, 16, 16, 40, 0.6, 0.0), (64, 32, 16, 16, 64, 0.05, 0.2), (48, 30, 8, 6, 30, 0.9, 0.0),
                                  (64, 64, 32, 32, 26, 0.7, 0.0)])
 def test_packed_walk_bit_exact(cfg):
