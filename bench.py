@@ -60,7 +60,6 @@ PUSH_BYTES_FUSED_REORDER = 104.0
 NCU_TRAFFIC_BYTES_PER_PARTICLE = 117.2
 # ncu --set full, profiles/r02an_ncu_full_fused_yee_8192_raw.csv: 3.238 GB + 3.179 GB over 8192^2 cells (algorithmic: 96 B/cell)
 NCU_YEE_TRAFFIC_BYTES_PER_CELL = 95.6
-SORT_BYTES_PER_PARTICLE = 5.0      # what is left of the sort: direction codes read (1) + permutation written (4); the rest is per cell
 YEE_BYTES_3SWEEP = 216.0           # reference-faithful half-B, E, half-B: 3 x 72 B per cell
 YEE_BYTES_ALGO = 144.0             # SURVEY.md section 8(d) algorithmic figure (2 sweeps)
 YEE_BYTES_FUSED = 96.0             # fused step: every plane read once, written once
@@ -399,7 +398,6 @@ def push_roofline(n, t, peak, peak_how):
             "traffic_source": "CONSTANT from one ncu --set full capture of this kernel in the saturated regime (profiles/r02an_ncu_full_push_packed_saturated_raw.csv: "
                               "117.2 B/particle), scaled by the particle count; not measured by this run",
             "pushes_per_s_kernel_only": n / (t["push_ms"] * 1e-3), "peak_source": peak_how,
-            "sort_gbs": n * SORT_BYTES_PER_PARTICLE / (t["sort_ms"] * 1e-3) / 1e9,
             "note": "frac: SURVEY.md 8(d)'s 88 B push + 2.3 B grid = 90 B/particle.  frac_104B: what this kernel must move, since it is also the "
                     "sort's reorder (52 B read + 52 B written per particle); the sort that remains (scan + permutation build) moves 8 B/particle"}
 
@@ -425,7 +423,11 @@ def pic_record(m, torch, name, w, K, W, local, peak, peak_how, clocks=True, keep
            "ms_per_step": t["ms"] / K, "particles": n,
            "regime": (f"saturated: timed after {sat} untimed steps + {W} warm-up steps" if sat else f"thermal u_th={w['u_th']}: timed after {W} warm-up steps"),
            "cell_crossing_fraction": t["movers"] / float(n),
-           "phases_ms": {"push_deposit": t["push_ms"], "fields_fused": t["fields_ms"], "sort": t["sort_ms"]},
+           # the sort chain runs on its own stream NEXT TO the fused field kernel; the events sit on the main stream, so the
+           # second entry is the field kernel with part of the sort beside it and the third is only what is left of the sort
+           # after the fields have finished -- not the duration of the sort kernels (no bandwidth figure is derived from it)
+           "phases_ms": {"push_deposit": t["push_ms"], "fields_fused": t["fields_ms"], "sort": t["sort_ms"],
+                         "note": "sort = tail of the sort chain left after the concurrent field kernel, not the sort's own duration"},
            "roofline": push_roofline(n, t, peak, peak_how), "gpu_launches": t["launches"],
            "diagnostics_after": {k: float(v) for k, v in diag.items()}}
     if clocks:
