@@ -17,6 +17,25 @@ void mpic_set_error(const char* fmt, ...) {
     va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof g_err, fmt, ap); va_end(ap);
 }
 
+#include <unistd.h>
+#include <time.h>
+#include <mutex>
+unsigned long long mpic_process_nonce() {
+    static std::once_flag once;
+    static unsigned long long nonce = 0;
+    std::call_once(once, [] {
+        unsigned long long v = 0;
+        if (FILE* f = fopen("/dev/urandom", "rb")) { if (fread(&v, sizeof v, 1, f) != 1) v = 0; fclose(f); }
+        if (!v) {                                         // no urandom: clock, pid and an address of this mapping, mixed
+            struct timespec ts; clock_gettime(CLOCK_REALTIME, &ts);
+            v = (unsigned long long)ts.tv_nsec * 0x9E3779B97F4A7C15ull ^ (unsigned long long)ts.tv_sec << 20 ^
+                (unsigned long long)getpid() << 44 ^ (unsigned long long)(uintptr_t)&nonce;
+        }
+        nonce = v | 1ull;                                 // never zero: a zeroed blob matches nobody
+    });
+    return nonce;
+}
+
 #include "sim.cuh"
 static void dump_release(mpic_sim* s);
 

@@ -103,6 +103,10 @@ struct LeaveBufs {
 };
 
 void mpic_set_error(const char* fmt, ...);
+// Identity of this process for "may I use the raw device pointers in this blob?": the pid alone is not enough (ranks in separate
+// PID namespaces -- one container per rank -- can share a pid), so blobs also carry a random 64-bit value drawn once per library
+// load, and both must match.
+unsigned long long mpic_process_nonce();
 
 #define CUDA_TRY(expr)                                                                          \
     do {                                                                                        \

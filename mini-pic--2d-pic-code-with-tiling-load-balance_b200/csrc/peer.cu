@@ -30,6 +30,7 @@ constexpr unsigned long long PEER_MAGIC = 0x4d50494350454552ull;   // "MPICPEER"
 struct PeerBlob {                     // what travels inside mpic_peer_info
     unsigned long long magic;
     int pid, device, rank, nyl, lcap, pad;
+    unsigned long long nonce;         // mpic_process_nonce() of the exporter: raw[] is trusted only when pid AND nonce are ours
     int64_t plane;
     void* raw[5];                     // planes, jacc, arrive block, control block, planes_alt (valid inside the exporting process)
     cudaIpcMemHandle_t h[5];
@@ -215,7 +216,7 @@ int open_side(mpic_sim* s, int side, const PeerBlob& b, const mpic_sim::PeerSide
     p.plane = b.plane; p.nyl = b.nyl; p.lcap = b.lcap;
     if (same) { p.planes = same->planes; p.planes_alt = same->planes_alt; p.jacc = same->jacc; p.arrive = same->arrive; p.ctl = same->ctl; p.ipc = false; return 0; }
     void* ptr[5] = { nullptr, nullptr, nullptr, nullptr, nullptr };
-    if (b.pid == (int)getpid()) {                       // same process: plain pointers (+ peer access across devices)
+    if (b.pid == (int)getpid() && b.nonce == mpic_process_nonce()) {   // same process: plain pointers (+ peer access across devices)
         if (b.device != s->prm.device) {
             int can = 0;
             CUDA_TRY(cudaDeviceCanAccessPeer(&can, s->prm.device, b.device));
@@ -275,7 +276,7 @@ int mpic_peer_export(mpic_sim* s, mpic_peer_info* out) {
     memset(out, 0, sizeof *out);
     PeerBlob b;
     memset(&b, 0, sizeof b);
-    b.magic = PEER_MAGIC; b.pid = (int)getpid(); b.device = s->prm.device; b.rank = s->prm.rank; b.nyl = s->G.nyl;
+    b.magic = PEER_MAGIC; b.pid = (int)getpid(); b.nonce = mpic_process_nonce(); b.device = s->prm.device; b.rank = s->prm.rank; b.nyl = s->G.nyl;
     b.lcap = s->lv.cap; b.plane = s->G.plane;
     TRY(mpic_fused_setup(s));                            // the second plane block of the fused step is peer-visible too
     b.raw[0] = s->planes; b.raw[1] = s->jacc; b.raw[2] = s->arrive_blk; b.raw[3] = s->ctl; b.raw[4] = s->planes_alt;

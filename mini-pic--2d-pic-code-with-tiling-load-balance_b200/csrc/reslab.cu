@@ -23,6 +23,7 @@ constexpr unsigned long long PARCEL_MAGIC = 0x4d5049435041524bull;   // "MPICPAR
 struct ParcelBlob {                   // what travels inside mpic_parcel_info
     unsigned long long magic;
     int pid, device, row_lo, row_hi, nx, tny, has_ipc, pad1;   // has_ipc: h is valid (a process that cannot export still serves handles of its own process)
+    unsigned long long nonce;         // mpic_process_nonce() of the packer: raw is trusted only when pid AND nonce are ours
     int64_t np;                       // particles in the parcel
     int64_t bytes;
     void* raw;                        // valid inside the packing process
@@ -126,7 +127,7 @@ int mpic_reslab_pack(mpic_sim* s, int row_lo, int row_hi, mpic_parcel_info* out)
     const PicConst& P = s->P;
     ParcelBlob b;
     memset(&b, 0, sizeof b);
-    b.magic = PARCEL_MAGIC; b.pid = (int)getpid(); b.device = s->prm.device; b.row_lo = row_lo; b.row_hi = row_hi; b.nx = G.nx; b.tny = P.tny;
+    b.magic = PARCEL_MAGIC; b.pid = (int)getpid(); b.nonce = mpic_process_nonce(); b.device = s->prm.device; b.row_lo = row_lo; b.row_hi = row_hi; b.nx = G.nx; b.tny = P.tny;
     int64_t s_lo = 0;
     if (s->cap > 0 && s->n > 0) {
         if (s->perm_valid) {                             // physical tile/cell order (one gather pass), cell offsets stay valid
@@ -213,7 +214,7 @@ int mpic_reslab_apply(mpic_sim* s, int new_row0, int new_nrows, int64_t new_max_
     int rc = 0;
     for (const ParcelBlob& b : bl) {
         const void* src = b.raw;
-        if (b.pid != (int)getpid()) {
+        if (b.pid != (int)getpid() || b.nonce != mpic_process_nonce()) {
             if (!b.has_ipc) { mpic_set_error("parcel rows %d..%d come from another process that could not export a CUDA IPC handle", b.row_lo, b.row_hi); rc = MPIC_ECUDA; break; }
             void* ptr = nullptr;
             cudaError_t e = cudaIpcOpenMemHandle(&ptr, b.h, cudaIpcMemLazyEnablePeerAccess);

@@ -397,3 +397,27 @@ def test_reslab_rejects_bad_parcels():
     for k in range(6):
         assert np.array_equal(got[k], planes[k][:sims[0].nyl])
     sims[0].reslab_finish()
+
+
+def test_blob_with_our_pid_but_a_foreign_nonce_is_not_trusted():
+    """'same process' was decided from the pid alone, and two ranks in separate PID namespaces (one container per
+    rank) can share a pid -- the raw device pointers of ANOTHER process would have been dereferenced.  Blobs now carry a random
+    per-process value as well.  A blob of this process whose nonce is altered must go down the CUDA-IPC road (which refuses to
+    open a handle inside the process that exported it) instead of being trusted; the untouched blob still connects."""
+    m = pkg()
+    nx, ny, tn = 32, 64, 16
+    dx = dy = 0.1
+    dt = m.courant_dt(dx, dy)
+    sims = [m.Sim(nx, ny, tn, tn, dx, dy, dt, rank=r, nranks=2, device=0) for r in range(2)]
+    blobs = [s.peer_export() for s in sims]
+    NONCE = slice(32, 40)                                # PeerBlob: magic (8 bytes), six ints, then the nonce
+    assert blobs[0][NONCE] == blobs[1][NONCE] and blobs[1][NONCE] != bytes(8)
+    forged = bytearray(blobs[1])
+    forged[32] ^= 0x5A
+    with pytest.raises(m.MpicError):
+        sims[0].peer_connect(bytes(forged), bytes(forged))
+    sims[0].peer_connect(blobs[1], blobs[1])
+    sims[1].peer_connect(blobs[0], blobs[0])
+    for s in sims:
+        s.peer_disconnect()
+        s.close()
