@@ -112,6 +112,7 @@ unsigned long long mpic_process_nonce();
     do {                                                                                        \
         cudaError_t _e = (expr);                                                                \
         if (_e != cudaSuccess) {                                                                \
+            cudaGetLastError(); /* reported here: it must not surface again at a later launch check */ \
             mpic_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e)); \
             return _e == cudaErrorNoDevice || _e == cudaErrorInsufficientDriver ? MPIC_ENODEV : MPIC_ECUDA; \
         }                                                                                       \

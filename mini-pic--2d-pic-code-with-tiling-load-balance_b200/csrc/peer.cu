@@ -278,8 +278,16 @@ int mpic_peer_export(mpic_sim* s, mpic_peer_info* out) {
     memset(&b, 0, sizeof b);
     b.magic = PEER_MAGIC; b.pid = (int)getpid(); b.nonce = mpic_process_nonce(); b.device = s->prm.device; b.rank = s->prm.rank; b.nyl = s->G.nyl;
     b.lcap = s->lv.cap; b.plane = s->G.plane;
-    TRY(mpic_fused_setup(s));                            // the second plane block of the fused step is peer-visible too
-    b.raw[0] = s->planes; b.raw[1] = s->jacc; b.raw[2] = s->arrive_blk; b.raw[3] = s->ctl; b.raw[4] = s->planes_alt;
+    // The second plane block of the fused field step is peer-visible too -- when there is one.  It is only of use to scheme 0
+    // (mpic_peer_field_step_fused refuses the others), it costs another six planes of HBM (3.2 GB on an 8192^2 slab), and a ring
+    // that never takes a fused step does not need it: MPIC_PEER_NO_FUSED=1 leaves it out.  If it cannot be set up (out of memory,
+    // tensor-map encoding) the plain ring must still work: the block is then simply not exported, connect copes with has[4] == 0
+    // and mpic_peer_field_step_fused says "neighbours exported no second plane block".
+    if (s->prm.scheme == 0 && !getenv("MPIC_PEER_NO_FUSED") && mpic_fused_setup(s) != 0) {
+        cudaGetLastError();
+        if (s->planes_alt && !s->fused_ready) { cudaFree(s->planes_alt); s->planes_alt = nullptr; }
+    }
+    b.raw[0] = s->planes; b.raw[1] = s->jacc; b.raw[2] = s->arrive_blk; b.raw[3] = s->ctl; b.raw[4] = s->fused_ready ? s->planes_alt : nullptr;
     for (int k = 0; k < 5; k++)
         if (b.raw[k]) { CUDA_TRY(cudaIpcGetMemHandle(&b.h[k], b.raw[k])); b.has[k] = 1; }
     memcpy(out->bytes, &b, sizeof b);

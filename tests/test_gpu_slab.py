@@ -421,3 +421,31 @@ def test_blob_with_our_pid_but_a_foreign_nonce_is_not_trusted():
     for s in sims:
         s.peer_disconnect()
         s.close()
+
+
+def test_peer_ring_without_the_fused_plane_block(monkeypatch):
+    """mpic_peer_export used to allocate the fused step's second plane block (six more planes) for every ring and a
+    failure there made the plain ring unusable.  With MPIC_PEER_NO_FUSED=1 -- the same state a failed set-up now leaves -- no
+    second block is exported: the three-sweep ring still equals the single-slab loop bit for bit and the fused step says why
+    it cannot run."""
+    m = pkg()
+    monkeypatch.setenv("MPIC_PEER_NO_FUSED", "1")
+    nx, ny, tn = 64, 64, 16
+    dx, dy, dt, parts, planes = _problem(nx, ny, tn, 2, 0.3, seed=31)
+    sims = [m.Sim(nx, ny, tn, tn, dx, dy, dt, rank=r, nranks=2, device=0) for r in range(2)]
+    for s in sims:
+        r0, r1 = s.row0 * tn, (s.row0 + s.nrows) * tn
+        s.upload_planes([a[r0:r1] for a in planes])
+    ring = m.PeerRing(sims)
+    ring.refresh_guards()
+    ring.field_steps(7)
+    ring.sync()
+    one = m.Sim(nx, ny, tn, tn, dx, dy, dt)
+    one.upload_planes(planes)
+    one.field_steps(7)
+    ref = one.download_planes()
+    for k in range(6):
+        assert np.array_equal(np.concatenate([s.download_planes()[k] for s in sims]), ref[k]), k
+    with pytest.raises(m.MpicError, match="no second plane block"):
+        sims[0].peer_field_step(fused=True)
+
