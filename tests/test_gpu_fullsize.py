@@ -249,3 +249,75 @@ def test_c3_dump_of_65536_tiles_off_the_step_path(tmp_path):
         d = h.dataset(dict(h.links(ohdr))["fields"])
         for k, nm in enumerate(GRID_DTYPE.names):
             assert np.array_equal(d[nm], pad(want[k], r, c)), (gid, nm)
+
+
+def test_c1_reference_default_200_steps_bit_exact_with_dumps(tmp_path):
+    """configs[0] at its stated shape -- 128 x 128 cells, 16 x 16 tiles, 16 ppc thermal plasma (u_th = 0.05), periodic, 200 steps,
+    a field dump every 25 steps (loop edge PIC_2D.cpp:74,414-419; dump layout HDF5_output.cpp:10-79) -- is the one named config
+    the oracle can run IN FULL, so it is compared in full: at every dump step the particles in slot order (== the oracle's stable
+    cell sort), the six planes, the tile occupancy and the per-particle tile index are array_equal to the oracle's, and the
+    .h5 file written by mpic_dump_fields_async parses back to the oracle's tiles WITH their periodic guard cells.  The same
+    configuration through the C++ driver host/pic2d writes the same dumps."""
+    import glob
+    import os
+    import subprocess
+    from h5mini import H5Mini, GRID_DTYPE, assemble
+    from util import ROOT
+    m = pkg()
+    lib = ob.load_oracle()
+    nx = ny = 128
+    tn, ppc, u_th, steps, every = 16, 16, 0.05, 200, 25
+    dx = dy = 0.1
+    dt = m.courant_dt(dx, dy)
+    P = ob.make_params(lib, nx, ny, tn, tn, dx, dy, dt)
+    parts = plasma().load_uniform(nx, ny, tn, tn, dx, dy, ppc, u_th=u_th, seed=12345)
+    n = parts["x"].shape[0]
+    assert n == nx * ny * ppc
+    planes = [np.zeros((ny, nx)) for _ in range(6)]
+    s = m.Sim(nx, ny, tn, tn, dx, dy, dt, max_particles=n + 64)
+    s.upload_planes(planes)
+    s.upload_particles(parts)
+    o0 = np.argsort(ob.cell_keys(lib, P, parts["x"], parts["y"]), kind="stable")
+    want = {k: np.ascontiguousarray(v[o0]) for k, v in parts.items()}
+    wf = [a.copy() for a in planes]
+    gtc = nx // tn
+    pad = lambda a, r, c: np.take(np.take(a, np.arange(r * tn - 2, (r + 1) * tn + 2) % ny, axis=0), np.arange(c * tn - 2, (c + 1) * tn + 2) % nx, axis=1)
+    oracle_planes = {}
+    for st in range(every, steps + 1, every):
+        s.pic_steps(every)
+        counts, _ = ob.pic_steps(lib, P, wf, want, every, do_sort=2)
+        path = str(tmp_path / f"fields_rank_0_step_{st}.h5")
+        s.dump_fields_async(path)
+        got = s.download_particles()
+        for k in ("tag", "x", "y", "ux", "uy", "uz", "q"):
+            assert np.array_equal(got[k], want[k]), (st, k)
+        gf = s.download_planes()
+        for k in range(6):
+            assert np.array_equal(gf[k], wf[k]), (st, k)
+        assert np.array_equal(s.tile_counts(), counts) and counts.sum() == n
+        assert np.array_equal(s.particle_tile_index(), ob.tile_keys(lib, P, want["x"], want["y"]))
+        s.dump_wait()
+        tiles = H5Mini(path).tiles()
+        assert sorted(tiles) == list(range(gtc * gtc))
+        for gid, (attrs, d) in tiles.items():
+            r, c = divmod(gid, gtc)
+            assert attrs == {"tileRow": r, "tileCol": c, "currentRank": 0}
+            for k, nm in enumerate(GRID_DTYPE.names):
+                assert np.array_equal(d[nm], pad(wf[k], r, c)), (st, gid, nm)
+        oracle_planes[st] = [a.copy() for a in wf]
+    assert max(np.abs(a).max() for a in wf) > 0                      # thermal noise did excite fields
+    s.close()
+    # the same run through the C++ driver (device loader, seed 12345 == plasma.load_uniform's default): same dumps
+    pic2d = os.path.join(ROOT, "host", "pic2d")
+    if not os.path.exists(pic2d):
+        pytest.skip("host/pic2d not built (the library half of this test passed)")
+    r = subprocess.run([pic2d, "--nx", "128", "--ny", "128", "--box-x", "12.8", "--box-y", "12.8", "--tile-nx", "16", "--tile-ny", "16",
+                        "--ranks", "1", "--ic", "zero", "--ppc", "16", "--uth", "0.05", "--steps", "200", "--save-frequency", "25",
+                        "--no-migrate-demo", "--quiet"], cwd=str(tmp_path), capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    for st in range(every, steps + 1, every):
+        pa = sorted(glob.glob(str(tmp_path / "Simulation" / "Fields" / f"fields_rank_*_step_{st}.h5")))
+        assert len(pa) == 1
+        A, _, _ = assemble(pa, nx, ny, tn, tn, 2)
+        for k, nm in enumerate(GRID_DTYPE.names):
+            assert np.array_equal(A[nm], oracle_planes[st][k]), (st, nm)
